@@ -1,0 +1,144 @@
+/* rca_b200.h - C ABI of the B200 path engine (librca_b200.so).
+ *
+ * This is the boundary a maintainer of freiris/k8s-llm-rca binds instead of the bolt connection
+ * to Neo4j.  In the reference every graph operation is
+ *     Neo4jQueryExecutor.run_query(query, parameters)      common/neo4j_query_executor.py:15-24
+ * which ships Cypher text to a Neo4j server.  Here the Cypher text is translated to a plan on
+ * the host (Python, cold path) and the plan is executed by the entry points below against a
+ * CSR / typed-edge snapshot resident in HBM.  Plain pointers and sizes only; integer status
+ * codes; no C++ exceptions cross this boundary; INTEGRATION.md shows the ctypes stub.
+ *
+ * Status codes: 0 = ok, <0 = error (rca_last_error gives the text).
+ */
+#ifndef RCA_B200_H
+#define RCA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RCA_MAX_HOPS 8          /* longest path (relationships) a plan may ask for            */
+#define RCA_MAX_KINDS 256       /* kinds (entity + state) a snapshot may hold                  */
+#define RCA_STATE_LIMIT 10      /* 'LIMIT 10' of the state query, analyze_root_cause.py:77     */
+
+#define RCA_OK 0
+#define RCA_ERR_ARG (-1)
+#define RCA_ERR_CUDA (-2)
+#define RCA_ERR_NOMEM (-3)
+#define RCA_ERR_NODEVICE (-4)
+
+/* Direction of one hop relative to the walk. */
+#define RCA_DIR_OUT 0           /* (a)-[r]->(b), a bound                                       */
+#define RCA_DIR_IN 1            /* (b)<-[r]-(a), a bound: the reference's "reversed" steps,
+                                   test_generate_query.py:38                                   */
+#define RCA_DIR_UND 2           /* (a)-[r]-(b)                                                 */
+
+#define RCA_PLAN_VARLEN 0       /* find_metapath/find_srckind_metapath_neo4j.py:95-129         */
+#define RCA_PLAN_CHAIN 1        /* generate_query/generate_query.py:241-260                    */
+
+typedef struct rca_engine rca_engine_t;
+
+/* Host view of a snapshot (k8s-llm-rca_b200/snapshot.py documents every array).  All pointers
+ * are HOST pointers; rca_open copies them to the device and keeps nothing of the host memory. */
+typedef struct {
+    int32_t n_nodes, n_kinds, n_etypes, reserved;
+    int64_t n_rels;                 /* rows of out_dst / in_adj                                  */
+    int64_t n_und;                  /* rows of und_adj                                           */
+    int64_t n_states;               /* rows of st_*                                              */
+    int64_t n_typed_out, n_typed_in;/* rows of typed_out / typed_in                              */
+    const int32_t *kind_start;      /* [n_kinds+1]                                               */
+    const int32_t *et_src, *et_dst; /* [n_etypes] kind of the start / end node of each edge type */
+    const int32_t *et_cls;          /* [n_etypes] 0 entity-entity, 1 touches a STATE kind        */
+    const int32_t *out_rng;         /* [n_nodes+1][2] (begin, entity_end)                        */
+    const int32_t *out_dst;         /* [n_rels]; slot == relationship id                         */
+    const int32_t *in_rng;          /* [n_nodes+1][2]                                            */
+    const int32_t *in_adj;          /* [n_rels][2] (src, rel)                                    */
+    const int32_t *und_rng;         /* [n_nodes+1][2]                                            */
+    const int32_t *und_adj;         /* [n_und][2] (neighbour, rel)                               */
+    const int32_t *typed_out;       /* [n_typed_out][2] (begin, end) into out_dst                */
+    const int64_t *typed_out_base;  /* [n_etypes+1]                                              */
+    const int32_t *typed_in;        /* [n_typed_in][2] (begin, end) into in_adj                  */
+    const int64_t *typed_in_base;   /* [n_etypes+1]                                              */
+    const int32_t *st_off;          /* [n_nodes+1] HasState interval lists                       */
+    const int64_t *st_tmin, *st_tmax;/* [n_states] milliseconds; interval is [tmin, tmax)        */
+    const int32_t *st_node;         /* [n_states] STATE node id                                  */
+} rca_snapshot_t;
+
+/* One query plan.  A VARLEN plan is the reference's variable-length metapath query
+ * (find_srckind_metapath_neo4j.py:95-116, and :119-129 through pos_kind / node_simple);
+ * a CHAIN plan is the per-metapath instance query (generate_query.py:241-260). */
+typedef struct {
+    int32_t kind;                   /* RCA_PLAN_VARLEN | RCA_PLAN_CHAIN                          */
+    /* --- CHAIN --- */
+    int32_t n_steps;                /* L, 1..RCA_MAX_HOPS                                        */
+    int32_t step_etype[RCA_MAX_HOPS];
+    int32_t step_dir[RCA_MAX_HOPS]; /* RCA_DIR_OUT | RCA_DIR_IN                                  */
+    /* --- VARLEN --- */
+    int32_t direction;              /* RCA_DIR_*                                                 */
+    int32_t min_hops, max_hops;     /* '*1..3' -> 1, 3                                           */
+    int32_t entity_only;            /* walk only entity-entity relationships                     */
+    int32_t node_simple;            /* all(node ... single(...)) : no node repeats (:98)         */
+    int32_t dest_kind;              /* n2.kind = $destKind (:97); -1 = any                       */
+    int32_t has_inter;              /* size($intermediateKinds) > 0 (:100-102)                   */
+    int32_t prune;                  /* drop partial paths whose tail kind cannot reach dest_kind
+                                       in the hops that remain (schema-level, result-neutral)   */
+    int32_t pos_kind[RCA_MAX_HOPS + 1]; /* kind required at path position p, -1 = any (:127)     */
+    uint8_t kind_excl[RCA_MAX_KINDS];   /* 1: kind may appear nowhere on a path (:99)            */
+    uint8_t kind_inter[RCA_MAX_KINDS];  /* 1: kind is in $intermediateKinds                      */
+    /* --- both --- */
+    int32_t with_states;            /* fuse the HasState predicate (analyze_root_cause.py:70-79)
+                                       into emission: rows grow by (len+1) state ids + 1 mask    */
+} rca_plan_t;
+
+/* Counters of the last rca_expand, all exact (they come from the kernels' own count pass). */
+typedef struct {
+    int64_t frontier[RCA_MAX_HOPS + 1];  /* F_s: partial paths alive after step s (F_0 = seeds)  */
+    int64_t scanned[RCA_MAX_HOPS + 1];   /* E_s: adjacency entries scanned at step s             */
+    int64_t emitted[RCA_MAX_HOPS + 1];   /* N_s: path instances of length s                      */
+    int32_t row_len[RCA_MAX_HOPS + 1];   /* int32 words per row at level s                       */
+    int64_t total;                       /* sum of emitted                                       */
+    double kernel_ms;                    /* device time of the expansion kernels (CUDA events)   */
+    int32_t launches;                    /* kernels launched                                     */
+    int32_t retries;                     /* re-runs after growing the scratch arenas             */
+} rca_stats_t;
+
+/* replaces GraphDatabase.driver(uri, auth) + verify_connectivity, neo4j_query_executor.py:7-9 */
+int rca_open(const rca_snapshot_t *snap, int device, rca_engine_t **out);
+/* replaces driver.close(), neo4j_query_executor.py:11-13 */
+int rca_close(rca_engine_t *e);
+/* text of the last error on this engine (or of the last failed rca_open when e == NULL) */
+const char *rca_last_error(const rca_engine_t *e);
+/* run the engine's work on this CUDA stream (cudaStream_t as an integer); 0 = its own stream */
+int rca_set_stream(rca_engine_t *e, uint64_t cuda_stream);
+/* pre-size the scratch arenas: frontier entries (16 B each) and output words (4 B each) */
+int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words);
+
+/* replaces session.run(query, parameters) for the path-producing statements,
+ * neo4j_query_executor.py:16-21.  seeds: node ids (host or device memory, seeds_on_device says
+ * which); seed_ts: one timestamp (ms) per seed, needed only with plan->with_states.
+ * Results stay in the engine until the next rca_expand / rca_close on it. */
+int rca_expand(rca_engine_t *e, const rca_plan_t *plan, const int32_t *seeds, int64_t n_seeds,
+               const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats);
+/* device pointer / shape of the rows of paths with `level` relationships.
+ * Row = (level+1) node ids, level relationship ids [, (level+1) state ids, 1 missing-state mask] */
+int rca_result_level(const rca_engine_t *e, int level, const int32_t **dev_rows, int64_t *n_rows,
+                     int32_t *row_len);
+/* replaces records = list(result), neo4j_query_executor.py:21: copy one level's rows to the host */
+int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows);
+
+/* replaces the per-node state query of check_states_of_entity, analyze_root_cause.py:173-176:
+ * for i < n: STATE nodes of entity nodes[i] whose interval holds ts[i].  out_first[i] = lowest
+ * matching STATE node id or -1; out_cnt[i] = number of matches; out_ids (nullable)
+ * [n][RCA_STATE_LIMIT], -1 padded.  Buffers are host or device memory per on_device. */
+int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, int64_t n, int on_device,
+                     int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
+
+/* library / build information, e.g. "rca_b200 0.1 sm_100a" */
+const char *rca_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RCA_B200_H */

@@ -1,0 +1,486 @@
+// rca_b200.cu - C ABI (include/rca_b200.h) over the kernels in rca_kernels.cuh.
+//
+// Host side of the engine: uploads a snapshot to HBM, turns a plan into one launch per hop, keeps
+// the scratch arenas (frontier entries, output rows, tile states) and hands results back.  There
+// is no CPU path: every entry point that computes runs kernels on the device it was opened on.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "rca_b200.h"
+#include "rca_kernels.cuh"
+
+using namespace rca;
+
+static thread_local std::string g_open_error;
+
+struct rca_engine {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    // graph
+    int n_nodes = 0, n_kinds = 0, n_etypes = 0;
+    long long n_rels = 0, n_und = 0, n_states = 0;
+    std::vector<int> kind_start, et_src, et_dst, et_cls;
+    std::vector<long long> typed_out_base, typed_in_base;
+    int2 *out_rng = nullptr, *in_rng = nullptr, *und_rng = nullptr, *in_adj = nullptr, *und_adj = nullptr;
+    int2 *typed_out = nullptr, *typed_in = nullptr;
+    int *out_dst = nullptr, *st_off = nullptr, *st_node = nullptr;
+    long long *st_tmin = nullptr, *st_tmax = nullptr;
+    // scratch
+    int4 *frontier = nullptr;
+    unsigned long long fcap = 0;
+    int *out = nullptr;
+    unsigned long long ocap = 0;
+    unsigned long long *tstate = nullptr;
+    unsigned long long tcap = 0;
+    Ctl *ctl = nullptr;
+    Ctl *h_ctl = nullptr;                 // pinned
+    int *ktab = nullptr, *h_ktab = nullptr;
+    int *seeds_buf = nullptr;
+    long long seeds_cap = 0;
+    long long *ts_buf = nullptr;
+    long long ts_cap = 0;
+    void *io_buf = nullptr;               // staging for rca_state_lookup with host buffers
+    size_t io_cap = 0;
+    // last result
+    bool have_result = false;
+    int res_levels = 0;
+    int res_row_len[RCA_MAX_HOPS + 1] = {0};
+    long long res_rows[RCA_MAX_HOPS + 1] = {0};
+    unsigned long long res_base[RCA_MAX_HOPS + 1] = {0};
+};
+
+static int fail(rca_engine *e, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (e) e->err = buf; else g_open_error = buf;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            return fail(e, _e == cudaErrorMemoryAllocation ? RCA_ERR_NOMEM : RCA_ERR_CUDA,          \
+                        "%s failed: %s", #call, cudaGetErrorString(_e));                            \
+    } while (0)
+
+template <typename T>
+static cudaError_t upload(T **dst, const void *src, size_t count) {
+    *dst = nullptr;
+    size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+    cudaError_t r = cudaMalloc((void **)dst, bytes);
+    if (r != cudaSuccess) return r;
+    if (count) r = cudaMemcpy(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice);
+    return r;
+}
+
+extern "C" const char *rca_version(void) { return "rca_b200 0.1 sm_100a"; }
+
+extern "C" const char *rca_last_error(const rca_engine_t *e) { return e ? e->err.c_str() : g_open_error.c_str(); }
+
+extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out) {
+    rca_engine *e = nullptr;
+    if (!s || !out) return fail(e, RCA_ERR_ARG, "rca_open: null argument");
+    *out = nullptr;
+    if (s->n_kinds < 1 || s->n_kinds > RCA_MAX_KINDS) return fail(e, RCA_ERR_ARG, "rca_open: n_kinds %d not in 1..%d", s->n_kinds, RCA_MAX_KINDS);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(e, RCA_ERR_NODEVICE, "rca_open: no CUDA device is visible; this library has no CPU path");
+    if (device < 0 || device >= ndev) return fail(e, RCA_ERR_ARG, "rca_open: device %d not in 0..%d", device, ndev - 1);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail(e, RCA_ERR_CUDA, "rca_open: cannot query device");
+    if (prop.major != 10)
+        return fail(e, RCA_ERR_NODEVICE, "rca_open: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    std::unique_ptr<rca_engine> up(new rca_engine);
+    rca_engine *g = up.get();
+#define OCK(call)                                                                                  \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            int rc = fail(nullptr, _e == cudaErrorMemoryAllocation ? RCA_ERR_NOMEM : RCA_ERR_CUDA,  \
+                          "rca_open: %s failed: %s", #call, cudaGetErrorString(_e));                \
+            rca_close(up.release());                                                               \
+            return rc;                                                                             \
+        }                                                                                          \
+    } while (0)
+    g->device = device;
+    g->sm_count = prop.multiProcessorCount;
+    OCK(cudaSetDevice(device));
+    OCK(cudaStreamCreateWithFlags(&g->own_stream, cudaStreamNonBlocking));
+    g->stream = g->own_stream;
+    OCK(cudaEventCreate(&g->ev0));
+    OCK(cudaEventCreate(&g->ev1));
+    g->n_nodes = s->n_nodes; g->n_kinds = s->n_kinds; g->n_etypes = s->n_etypes;
+    g->n_rels = s->n_rels; g->n_und = s->n_und; g->n_states = s->n_states;
+    g->kind_start.assign(s->kind_start, s->kind_start + s->n_kinds + 1);
+    g->et_src.assign(s->et_src, s->et_src + s->n_etypes);
+    g->et_dst.assign(s->et_dst, s->et_dst + s->n_etypes);
+    g->et_cls.assign(s->et_cls, s->et_cls + s->n_etypes);
+    g->typed_out_base.assign(s->typed_out_base, s->typed_out_base + s->n_etypes + 1);
+    g->typed_in_base.assign(s->typed_in_base, s->typed_in_base + s->n_etypes + 1);
+    const size_t V1 = (size_t)s->n_nodes + 1;
+    OCK(upload(&g->out_rng, s->out_rng, V1));
+    OCK(upload(&g->in_rng, s->in_rng, V1));
+    OCK(upload(&g->und_rng, s->und_rng, V1));
+    OCK(upload(&g->out_dst, s->out_dst, (size_t)s->n_rels));
+    OCK(upload(&g->in_adj, s->in_adj, (size_t)s->n_rels));
+    OCK(upload(&g->und_adj, s->und_adj, (size_t)s->n_und));
+    OCK(upload(&g->typed_out, s->typed_out, (size_t)s->n_typed_out));
+    OCK(upload(&g->typed_in, s->typed_in, (size_t)s->n_typed_in));
+    OCK(upload(&g->st_off, s->st_off, V1));
+    OCK(upload(&g->st_tmin, s->st_tmin, (size_t)s->n_states));
+    OCK(upload(&g->st_tmax, s->st_tmax, (size_t)s->n_states));
+    OCK(upload(&g->st_node, s->st_node, (size_t)s->n_states));
+    OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
+    OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
+    OCK(cudaMalloc((void **)&g->ktab, (2 * RCA_MAX_KINDS + 8) * sizeof(int)));
+    OCK(cudaMallocHost((void **)&g->h_ktab, (2 * RCA_MAX_KINDS + 8) * sizeof(int)));
+#undef OCK
+    *out = up.release();
+    return RCA_OK;
+}
+
+extern "C" int rca_close(rca_engine_t *e) {
+    if (!e) return RCA_OK;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
+                   e->st_off, e->st_node, e->st_tmin, e->st_tmax, e->frontier, e->out, e->tstate, e->ctl, e->ktab,
+                   e->seeds_buf, e->ts_buf, e->io_buf};
+    for (void *p : dev) if (p) cudaFree(p);
+    if (e->h_ctl) cudaFreeHost(e->h_ctl);
+    if (e->h_ktab) cudaFreeHost(e->h_ktab);
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->own_stream) cudaStreamDestroy(e->own_stream);
+    delete e;
+    return RCA_OK;
+}
+
+extern "C" int rca_set_stream(rca_engine_t *e, uint64_t cuda_stream) {
+    if (!e) return RCA_ERR_ARG;
+    e->stream = cuda_stream ? (cudaStream_t)(uintptr_t)cuda_stream : e->own_stream;
+    return RCA_OK;
+}
+
+template <typename T>
+static int grow(rca_engine *e, T **buf, unsigned long long *cap, unsigned long long want) {
+    if (want <= *cap && *buf) return RCA_OK;
+    CK(cudaStreamSynchronize(e->stream));
+    if (*buf) CK(cudaFree(*buf));
+    *buf = nullptr;
+    *cap = 0;
+    CK(cudaMalloc((void **)buf, std::max<unsigned long long>(want, 1) * sizeof(T)));
+    *cap = want;
+    return RCA_OK;
+}
+
+extern "C" int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words) {
+    if (!e || frontier_entries < 0 || output_words < 0) return RCA_ERR_ARG;
+    CK(cudaSetDevice(e->device));
+    int rc = grow(e, &e->frontier, &e->fcap, (unsigned long long)frontier_entries);
+    if (rc) return rc;
+    e->have_result = false;
+    return grow(e, &e->out, &e->ocap, (unsigned long long)output_words);
+}
+
+// schema-level reachability: bit (r-1) of reach[k] says a walk of 1..r hops in the plan's
+// direction, through kinds the plan does not exclude, leads from kind k to dest_kind
+static void reach_bits(const rca_engine *e, const rca_plan_t *pl, unsigned *reach) {
+    const int nk = e->n_kinds;
+    bool constrained = false;
+    for (int i = 0; i <= pl->max_hops; i++) constrained |= pl->pos_kind[i] >= 0;
+    if (!pl->prune || pl->dest_kind < 0 || constrained) {
+        for (int k = 0; k < nk; k++) reach[k] = 0xffu;
+        return;
+    }
+    std::vector<unsigned char> in_d(nk, 0), nxt(nk, 0);
+    for (int k = 0; k < nk; k++) reach[k] = 0;
+    if (pl->kind_excl[pl->dest_kind]) return;
+    auto edge = [&](int t, int &a, int &b, int flip) {   // a -> b in walk direction
+        a = flip ? e->et_dst[t] : e->et_src[t];
+        b = flip ? e->et_src[t] : e->et_dst[t];
+    };
+    for (int r = 1; r <= pl->max_hops; r++) {
+        std::fill(nxt.begin(), nxt.end(), 0);
+        for (int t = 0; t < e->n_etypes; t++) {
+            if (pl->entity_only && e->et_cls[t]) continue;
+            for (int flip = 0; flip < 2; flip++) {
+                if (pl->direction == RCA_DIR_OUT && flip) continue;
+                if (pl->direction == RCA_DIR_IN && !flip) continue;
+                int a, b;
+                edge(t, a, b, flip);
+                bool hit = (b == pl->dest_kind) || (r > 1 && in_d[b] && !pl->kind_excl[b]);
+                if (hit) nxt[a] = 1;
+            }
+        }
+        for (int k = 0; k < nk; k++) {
+            in_d[k] = in_d[k] | nxt[k];
+            if (in_d[k]) reach[k] |= 1u << (r - 1);
+        }
+    }
+}
+
+static int validate_plan(rca_engine *e, const rca_plan_t *pl) {
+    if (pl->kind == RCA_PLAN_CHAIN) {
+        if (pl->n_steps < 1 || pl->n_steps > RCA_MAX_HOPS) return fail(e, RCA_ERR_ARG, "chain plan: n_steps %d not in 1..%d", pl->n_steps, RCA_MAX_HOPS);
+        int cur = -1;
+        for (int i = 0; i < pl->n_steps; i++) {
+            int t = pl->step_etype[i], d = pl->step_dir[i];
+            if (t < 0 || t >= e->n_etypes) return fail(e, RCA_ERR_ARG, "chain plan: step %d edge type %d unknown", i, t);
+            if (d != RCA_DIR_OUT && d != RCA_DIR_IN) return fail(e, RCA_ERR_ARG, "chain plan: step %d direction %d", i, d);
+            int from = d == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t], to = d == RCA_DIR_OUT ? e->et_dst[t] : e->et_src[t];
+            if (i > 0 && from != cur) return fail(e, RCA_ERR_ARG, "chain plan: step %d starts at kind %d but step %d ended at kind %d", i, from, i - 1, cur);
+            cur = to;
+        }
+        return RCA_OK;
+    }
+    if (pl->kind != RCA_PLAN_VARLEN) return fail(e, RCA_ERR_ARG, "plan kind %d unknown", pl->kind);
+    if (pl->max_hops < 1 || pl->max_hops > RCA_MAX_HOPS || pl->min_hops < 1 || pl->min_hops > pl->max_hops)
+        return fail(e, RCA_ERR_ARG, "varlen plan: hops %d..%d not within 1..%d", pl->min_hops, pl->max_hops, RCA_MAX_HOPS);
+    if (pl->direction < RCA_DIR_OUT || pl->direction > RCA_DIR_UND) return fail(e, RCA_ERR_ARG, "varlen plan: direction %d", pl->direction);
+    if (pl->dest_kind >= e->n_kinds) return fail(e, RCA_ERR_ARG, "varlen plan: dest_kind %d unknown", pl->dest_kind);
+    for (int i = 0; i <= pl->max_hops; i++)
+        if (pl->pos_kind[i] >= e->n_kinds) return fail(e, RCA_ERR_ARG, "varlen plan: pos_kind[%d] = %d unknown", i, pl->pos_kind[i]);
+    return RCA_OK;
+}
+
+static int row_len_of(const rca_plan_t *pl, int s) { return pl->with_states ? 3 * s + 3 : 2 * s + 1; }
+
+template <typename K>
+static int max_grid(rca_engine *e, K kernel) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    return e->sm_count * per_sm;
+}
+
+extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *seeds, int64_t n_seeds,
+                          const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats) {
+    if (!e) return RCA_ERR_ARG;
+    if (!pl || n_seeds < 0 || (n_seeds > 0 && !seeds)) return fail(e, RCA_ERR_ARG, "rca_expand: null plan or seeds");
+    if (n_seeds > (int64_t)kHalf) return fail(e, RCA_ERR_ARG, "rca_expand: more than 2^31-1 seeds in one call");
+    if (pl->with_states && n_seeds > 0 && !seed_ts) return fail(e, RCA_ERR_ARG, "rca_expand: with_states needs seed_ts");
+    int rc = validate_plan(e, pl);
+    if (rc) return rc;
+    CK(cudaSetDevice(e->device));
+    e->have_result = false;
+    const bool varlen = pl->kind == RCA_PLAN_VARLEN;
+    const int L = varlen ? pl->max_hops : pl->n_steps;
+
+    // ---- seeds (and their timestamps) on the device
+    const int *d_seeds = seeds;
+    const long long *d_ts = (const long long *)seed_ts;
+    if (!seeds_on_device && n_seeds) {
+        unsigned long long cap = (unsigned long long)e->seeds_cap;
+        rc = grow(e, &e->seeds_buf, &cap, (unsigned long long)n_seeds);
+        e->seeds_cap = (long long)cap;
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(e->seeds_buf, seeds, (size_t)n_seeds * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+        d_seeds = e->seeds_buf;
+        if (pl->with_states) {
+            cap = (unsigned long long)e->ts_cap;
+            rc = grow(e, &e->ts_buf, &cap, (unsigned long long)n_seeds);
+            e->ts_cap = (long long)cap;
+            if (rc) return rc;
+            CK(cudaMemcpyAsync(e->ts_buf, seed_ts, (size_t)n_seeds * sizeof(long long), cudaMemcpyHostToDevice, e->stream));
+            d_ts = e->ts_buf;
+        }
+    }
+
+    // ---- kind tables of this plan: kind_start (padded to 4) then attribute words
+    const int nkp = (e->n_kinds + 1 + 3) & ~3, nka = (e->n_kinds + 3) & ~3;
+    std::memset(e->h_ktab, 0, (size_t)(nkp + nka) * sizeof(int));
+    for (int k = 0; k <= e->n_kinds; k++) e->h_ktab[k] = e->kind_start[k];
+    for (int k = e->n_kinds + 1; k < nkp; k++) e->h_ktab[k] = 0x7fffffff;
+    if (varlen) {
+        unsigned reach[RCA_MAX_KINDS];
+        reach_bits(e, pl, reach);
+        for (int k = 0; k < e->n_kinds; k++)
+            e->h_ktab[nkp + k] = (int)((pl->kind_excl[k] ? kAttrExcl : 0u) | (pl->kind_inter[k] ? kAttrInter : 0u) |
+                                       (reach[k] << kAttrReachShift));
+    }
+    CK(cudaMemcpyAsync(e->ktab, e->h_ktab, (size_t)(nkp + nka) * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+
+    // ---- scratch arenas: keep what earlier calls grew to, else a guess from the seed count
+    if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * n_seeds, 1ull << 20)); if (rc) return rc; }
+    if (!e->out) { rc = grow(e, &e->out, &e->ocap, std::max<unsigned long long>(64ull * n_seeds, 1ull << 22)); if (rc) return rc; }
+
+    int retries = 0, launches = 0;
+    float ms = 0.f;
+    while (true) {
+        const unsigned long long tneed = ((unsigned long long)n_seeds + e->fcap) / kTile + kLv + 2;
+        rc = grow(e, &e->tstate, &e->tcap, tneed);
+        if (rc) return rc;
+        launches = 0;
+        std::memset(e->h_ctl, 0, sizeof(Ctl));
+        e->h_ctl->F[0] = (unsigned long long)n_seeds;
+        CK(cudaEventRecord(e->ev0, e->stream));
+        CK(cudaMemcpyAsync(e->ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemsetAsync(e->tstate, 0, tneed * sizeof(unsigned long long), e->stream));
+        for (int s = 1; s <= L; s++) {
+            LevelParams p;
+            std::memset(&p, 0, sizeof p);
+            int dir;
+            if (varlen) {
+                dir = pl->direction;
+                p.typed = 0;
+                p.rng = dir == RCA_DIR_OUT ? e->out_rng : dir == RCA_DIR_IN ? e->in_rng : e->und_rng;
+                p.entity_only = pl->entity_only;
+            } else {
+                const int t = pl->step_etype[s - 1];
+                dir = pl->step_dir[s - 1];
+                const int rowk = dir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
+                p.typed = 1;
+                p.rng = (dir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
+                p.row_lo = e->kind_start[rowk];
+                p.row_hi = e->kind_start[rowk + 1];
+            }
+            p.adj1 = e->out_dst;
+            p.adj2 = dir == RCA_DIR_IN ? e->in_adj : e->und_adj;
+            p.n_nodes = e->n_nodes;
+            p.s = s;
+            p.varlen = varlen;
+            p.min_hops = varlen ? pl->min_hops : L;
+            p.max_hops = L;
+            p.node_simple = pl->node_simple; p.dest_kind = pl->dest_kind; p.has_inter = pl->has_inter;
+            p.pos_kind_prev = varlen ? pl->pos_kind[s - 1] : -1;
+            p.pos_kind_cur = varlen ? pl->pos_kind[s] : -1;
+            p.with_states = pl->with_states;
+            p.row_len = row_len_of(pl, s);
+            p.seeds = d_seeds; p.seed_ts = d_ts;
+            p.frontier = e->frontier; p.fcap = e->fcap;
+            p.out = e->out; p.ocap = e->ocap;
+            p.ctl = e->ctl; p.tstate = e->tstate;
+            p.ktab = e->ktab; p.n_kinds = e->n_kinds; p.nkp = nkp; p.nka = nka;
+            p.st_off = e->st_off; p.st_tmin = e->st_tmin; p.st_tmax = e->st_tmax; p.st_node = e->st_node;
+            int grid;
+            if (dir == RCA_DIR_OUT) {
+                if (varlen) { grid = max_grid(e, expand_level<false, true>); } else { grid = max_grid(e, expand_level<false, false>); }
+            } else {
+                if (varlen) { grid = max_grid(e, expand_level<true, true>); } else { grid = max_grid(e, expand_level<true, false>); }
+            }
+            if (s == 1) grid = (int)std::min<long long>(grid, std::max<long long>(1, (n_seeds + kTile - 1) / kTile));
+            if (dir == RCA_DIR_OUT) {
+                if (varlen) expand_level<false, true><<<grid, kThreads, 0, e->stream>>>(p);
+                else expand_level<false, false><<<grid, kThreads, 0, e->stream>>>(p);
+            } else {
+                if (varlen) expand_level<true, true><<<grid, kThreads, 0, e->stream>>>(p);
+                else expand_level<true, false><<<grid, kThreads, 0, e->stream>>>(p);
+            }
+            launches++;
+            CK(cudaGetLastError());
+        }
+        CK(cudaEventRecord(e->ev1, e->stream));
+        CK(cudaMemcpyAsync(e->h_ctl, e->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        CK(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+        const unsigned ov = e->h_ctl->overflow;
+        if (!ov) break;
+        if (ov & 4u) return fail(e, RCA_ERR_ARG, "rca_expand: a level holds more than 2^31-1 partial paths or rows; split the seeds");
+        if (++retries > 12) return fail(e, RCA_ERR_NOMEM, "rca_expand: scratch arenas still too small after %d retries", retries);
+        // counters are exact up to and including the first level that overflowed: grow to at least that
+        unsigned long long fneed = 0, oneed = 0;
+        for (int s = 1; s <= L; s++) { fneed += e->h_ctl->F[s]; oneed += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s); }
+        if (ov & 1u) { rc = grow(e, &e->frontier, &e->fcap, std::max(e->fcap * 2, fneed + fneed / 4)); if (rc) return rc; }
+        if (ov & 2u) { rc = grow(e, &e->out, &e->ocap, std::max(e->ocap * 2, oneed + oneed / 4)); if (rc) return rc; }
+    }
+
+    // ---- publish the result and the counters
+    e->res_levels = L;
+    long long total = 0;
+    for (int s = 0; s <= RCA_MAX_HOPS; s++) { e->res_rows[s] = 0; e->res_row_len[s] = row_len_of(pl, s); e->res_base[s] = 0; }
+    for (int s = 1; s <= L; s++) {
+        e->res_rows[s] = (long long)e->h_ctl->N[s];
+        e->res_base[s] = e->h_ctl->obase[s];
+        total += e->res_rows[s];
+    }
+    e->have_result = true;
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->frontier[0] = n_seeds;
+        for (int s = 1; s <= L; s++) {
+            stats->frontier[s] = (int64_t)e->h_ctl->F[s];
+            stats->scanned[s] = (int64_t)e->h_ctl->E[s];
+        }
+        for (int s = 0; s <= L; s++) { stats->emitted[s] = e->res_rows[s]; stats->row_len[s] = e->res_row_len[s]; }
+        stats->total = total;
+        stats->kernel_ms = ms;
+        stats->launches = launches;
+        stats->retries = retries;
+    }
+    return RCA_OK;
+}
+
+extern "C" int rca_result_level(const rca_engine_t *e, int level, const int32_t **dev_rows, int64_t *n_rows, int32_t *row_len) {
+    if (!e || level < 0 || level > RCA_MAX_HOPS) return RCA_ERR_ARG;
+    if (!e->have_result) return fail(const_cast<rca_engine *>(e), RCA_ERR_ARG, "rca_result_level: no result held (call rca_expand first)");
+    if (dev_rows) *dev_rows = e->res_rows[level] ? e->out + e->res_base[level] : nullptr;
+    if (n_rows) *n_rows = e->res_rows[level];
+    if (row_len) *row_len = e->res_row_len[level];
+    return RCA_OK;
+}
+
+extern "C" int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows) {
+    if (!e || level < 0 || level > RCA_MAX_HOPS) return RCA_ERR_ARG;
+    if (!e->have_result) return fail(e, RCA_ERR_ARG, "rca_result_copy: no result held (call rca_expand first)");
+    const size_t words = (size_t)e->res_rows[level] * (size_t)e->res_row_len[level];
+    if (!words) return RCA_OK;
+    if (!host_rows) return fail(e, RCA_ERR_ARG, "rca_result_copy: null buffer");
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemcpyAsync(host_rows, e->out + e->res_base[level], words * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return RCA_OK;
+}
+
+extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, int64_t n, int on_device,
+                                int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
+    if (!e) return RCA_ERR_ARG;
+    if (n < 0 || (n > 0 && (!nodes || !ts || !out_first || !out_cnt))) return fail(e, RCA_ERR_ARG, "rca_state_lookup: null argument");
+    if (n == 0) return RCA_OK;
+    CK(cudaSetDevice(e->device));
+    const int *d_nodes = nodes;
+    const long long *d_ts = (const long long *)ts;
+    int *d_first = out_first, *d_cnt = out_cnt, *d_ids = out_ids;
+    if (!on_device) {
+        // staging layout: ts[n] (8 B) | nodes[n] | first[n] | cnt[n] | ids[n][LIMIT]
+        const size_t need = (size_t)n * (8 + 4 + 4 + 4 + 4 * RCA_STATE_LIMIT);
+        if (need > e->io_cap) {
+            CK(cudaStreamSynchronize(e->stream));
+            if (e->io_buf) CK(cudaFree(e->io_buf));
+            e->io_buf = nullptr; e->io_cap = 0;
+            CK(cudaMalloc(&e->io_buf, need));
+            e->io_cap = need;
+        }
+        char *b = (char *)e->io_buf;
+        d_ts = (long long *)b;
+        d_nodes = (int *)(b + 8 * (size_t)n);
+        d_first = (int *)(b + 12 * (size_t)n);
+        d_cnt = (int *)(b + 16 * (size_t)n);
+        d_ids = out_ids ? (int *)(b + 20 * (size_t)n) : nullptr;
+        CK(cudaMemcpyAsync((void *)d_ts, ts, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemcpyAsync((void *)d_nodes, nodes, 4 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+    }
+    state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_tmin, e->st_tmax, e->st_node, e->n_nodes,
+                                                                    d_nodes, d_ts, n, d_first, d_cnt, d_ids);
+    CK(cudaGetLastError());
+    if (!on_device) {
+        CK(cudaMemcpyAsync(out_first, d_first, 4 * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaMemcpyAsync(out_cnt, d_cnt, 4 * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
+        if (out_ids) CK(cudaMemcpyAsync(out_ids, d_ids, 4 * (size_t)n * RCA_STATE_LIMIT, cudaMemcpyDeviceToHost, e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    return RCA_OK;
+}

@@ -1,0 +1,269 @@
+"""ctypes binding of the C-ABI library (include/rca_b200.h, csrc/rca_b200.cu).
+
+This is the only door from Python to the kernels.  There is no CPU implementation behind it:
+if the shared library is missing, or no B200 is visible, the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+MAX_HOPS = 8
+MAX_KINDS = 256
+STATE_LIMIT = 10
+DIR_OUT, DIR_IN, DIR_UND = 0, 1, 2
+PLAN_VARLEN, PLAN_CHAIN = 0, 1
+_DIRS = {"out": DIR_OUT, "in": DIR_IN, "und": DIR_UND}
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
+
+EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_reserve", "rca_expand",
+           "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_version")
+
+
+class RcaError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"rca_b200 error {code}: {text}")
+        self.code = code
+
+
+class SnapshotDesc(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("n_kinds", C.c_int32), ("n_etypes", C.c_int32), ("reserved", C.c_int32),
+                ("n_rels", C.c_int64), ("n_und", C.c_int64), ("n_states", C.c_int64),
+                ("n_typed_out", C.c_int64), ("n_typed_in", C.c_int64),
+                ("kind_start", C.c_void_p), ("et_src", C.c_void_p), ("et_dst", C.c_void_p), ("et_cls", C.c_void_p),
+                ("out_rng", C.c_void_p), ("out_dst", C.c_void_p), ("in_rng", C.c_void_p), ("in_adj", C.c_void_p),
+                ("und_rng", C.c_void_p), ("und_adj", C.c_void_p),
+                ("typed_out", C.c_void_p), ("typed_out_base", C.c_void_p),
+                ("typed_in", C.c_void_p), ("typed_in_base", C.c_void_p),
+                ("st_off", C.c_void_p), ("st_tmin", C.c_void_p), ("st_tmax", C.c_void_p), ("st_node", C.c_void_p)]
+
+
+class PlanDesc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n_steps", C.c_int32),
+                ("step_etype", C.c_int32 * MAX_HOPS), ("step_dir", C.c_int32 * MAX_HOPS),
+                ("direction", C.c_int32), ("min_hops", C.c_int32), ("max_hops", C.c_int32),
+                ("entity_only", C.c_int32), ("node_simple", C.c_int32), ("dest_kind", C.c_int32),
+                ("has_inter", C.c_int32), ("prune", C.c_int32),
+                ("pos_kind", C.c_int32 * (MAX_HOPS + 1)),
+                ("kind_excl", C.c_uint8 * MAX_KINDS), ("kind_inter", C.c_uint8 * MAX_KINDS),
+                ("with_states", C.c_int32)]
+
+
+class StatsDesc(C.Structure):
+    _fields_ = [("frontier", C.c_int64 * (MAX_HOPS + 1)), ("scanned", C.c_int64 * (MAX_HOPS + 1)),
+                ("emitted", C.c_int64 * (MAX_HOPS + 1)), ("row_len", C.c_int32 * (MAX_HOPS + 1)),
+                ("total", C.c_int64), ("kernel_ms", C.c_double), ("launches", C.c_int32), ("retries", C.c_int32)]
+
+
+_lib = None
+
+
+def load_library(path: str | None = None):
+    """Load librca_b200.so.  Raises if it has not been built (python -c 'import __graft_entry__ as
+    g; g.build()') - there is deliberately nothing to fall back to."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise RuntimeError(f"{p} is missing: build the CUDA library first (__graft_entry__.build()); "
+                           "this package has no CPU path")
+    lib = C.CDLL(p)
+    lib.rca_last_error.restype = C.c_char_p
+    lib.rca_last_error.argtypes = [C.c_void_p]
+    lib.rca_version.restype = C.c_char_p
+    lib.rca_open.argtypes = [C.POINTER(SnapshotDesc), C.c_int, C.POINTER(C.c_void_p)]
+    lib.rca_close.argtypes = [C.c_void_p]
+    lib.rca_set_stream.argtypes = [C.c_void_p, C.c_uint64]
+    lib.rca_reserve.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+    lib.rca_expand.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
+                               C.POINTER(StatsDesc)]
+    lib.rca_result_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
+                                     C.POINTER(C.c_int32)]
+    lib.rca_result_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    lib.rca_state_lookup.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def varlen_plan(direction, max_hops, min_hops=1, dest_kind=-1, excl_kinds=(), inter_kinds=(), entity_only=False,
+                node_simple=True, pos_kind=None, prune=True, with_states=False) -> PlanDesc:
+    """Variable-length path plan - the reference's metapath statements,
+    find_metapath/find_srckind_metapath_neo4j.py:95-129."""
+    p = PlanDesc()
+    p.kind = PLAN_VARLEN
+    p.direction = _DIRS[direction] if isinstance(direction, str) else int(direction)
+    p.min_hops, p.max_hops = int(min_hops), int(max_hops)
+    p.entity_only, p.node_simple = int(bool(entity_only)), int(bool(node_simple))
+    p.dest_kind = int(dest_kind)
+    p.has_inter = int(len(inter_kinds) > 0)
+    p.prune = int(bool(prune))
+    for i in range(MAX_HOPS + 1):
+        p.pos_kind[i] = -1
+    if pos_kind is not None:
+        for i, k in enumerate(pos_kind):
+            p.pos_kind[i] = int(k)
+    for k in excl_kinds:
+        p.kind_excl[int(k)] = 1
+    for k in inter_kinds:
+        p.kind_inter[int(k)] = 1
+    p.with_states = int(bool(with_states))
+    return p
+
+
+def chain_plan(etypes, dirs, with_states=False) -> PlanDesc:
+    """Typed chain plan - one step per MATCH clause of the instance query,
+    generate_query/generate_query.py:241-248."""
+    assert len(etypes) == len(dirs) and 1 <= len(etypes) <= MAX_HOPS
+    p = PlanDesc()
+    p.kind = PLAN_CHAIN
+    p.n_steps = len(etypes)
+    for i, (t, d) in enumerate(zip(etypes, dirs)):
+        p.step_etype[i] = int(t)
+        p.step_dir[i] = _DIRS[d] if isinstance(d, str) else int(d)
+    for i in range(MAX_HOPS + 1):
+        p.pos_kind[i] = -1
+    p.dest_kind = -1
+    p.with_states = int(bool(with_states))
+    return p
+
+
+def _dev_ptr(x):
+    """(pointer, on_device, keepalive) for a numpy array, a torch tensor or a raw device pointer."""
+    if x is None:
+        return None, 0, None
+    if isinstance(x, np.ndarray):
+        a = np.ascontiguousarray(x)
+        return a.ctypes.data, 0, a
+    if hasattr(x, "data_ptr"):                       # torch tensor
+        t = x.contiguous()
+        return t.data_ptr(), int(t.is_cuda), t
+    raise TypeError(f"unsupported buffer type {type(x)}")
+
+
+class ExpandResult:
+    """Counters of one expansion plus access to its rows.  Rows live in the engine's output arena
+    until the next expand() on the same engine; rows() copies them out."""
+
+    def __init__(self, engine, st: StatsDesc, levels: int):
+        self.engine = engine
+        self.levels = levels
+        self.frontier = list(st.frontier)[:levels + 1]
+        self.scanned = list(st.scanned)[:levels + 1]
+        self.emitted = list(st.emitted)[:levels + 1]
+        self.row_len = list(st.row_len)[:levels + 1]
+        self.total = int(st.total)
+        self.kernel_ms = float(st.kernel_ms)
+        self.launches = int(st.launches)
+        self.retries = int(st.retries)
+        self._gen = engine._gen
+
+    def rows(self, level: int) -> np.ndarray:
+        assert self._gen == self.engine._gen, "result was overwritten by a later expand()"
+        n, w = self.emitted[level], self.row_len[level]
+        out = np.empty((n, w), dtype=np.int32)
+        if n:
+            self.engine._ck(self.engine.lib.rca_result_copy(self.engine.h, level, out.ctypes.data))
+        return out
+
+    def all_rows(self) -> dict:
+        return {s: self.rows(s) for s in range(self.levels + 1) if self.emitted[s]}
+
+    def device_rows(self, level: int):
+        """(device pointer, n_rows, row_len) - for consumers that stay on the GPU (NCCL gather)."""
+        assert self._gen == self.engine._gen, "result was overwritten by a later expand()"
+        p, n, w = C.c_void_p(), C.c_int64(), C.c_int32()
+        self.engine._ck(self.engine.lib.rca_result_level(self.engine.h, level, C.byref(p), C.byref(n), C.byref(w)))
+        return (p.value or 0), int(n.value), int(w.value)
+
+    def algorithmic_bytes(self) -> int:
+        """sum_s (12 F_{s-1} + 4 E_s) + 4 (2s+1) N_s, plus, with the fused
+        state filter, (s+1) N_s (8 + 16 I + 5) with I = 1 interval inspected per node."""
+        b = 0
+        for s in range(1, self.levels + 1):
+            b += 12 * self.frontier[s - 1] + 4 * self.scanned[s] + 4 * (2 * s + 1) * self.emitted[s]
+            if self.row_len[s] > 2 * s + 1:
+                b += (s + 1) * self.emitted[s] * (8 + 16 + 5)
+        return b
+
+
+class Engine:
+    """One snapshot resident on one GPU."""
+
+    def __init__(self, snap, device: int = 0):
+        self.lib = load_library()
+        self.snap = snap
+        self.device = device
+        self._gen = 0
+        names = ("kind_start", "et_src", "et_dst", "et_cls", "out_rng", "out_dst", "in_rng", "in_adj", "und_rng",
+                 "und_adj", "typed_out", "typed_out_base", "typed_in", "typed_in_base", "st_off", "st_tmin",
+                 "st_tmax", "st_node")
+        dt = {"typed_out_base": np.int64, "typed_in_base": np.int64, "st_tmin": np.int64, "st_tmax": np.int64}
+        keep = {n: np.ascontiguousarray(getattr(snap, n), dtype=dt.get(n, np.int32)) for n in names}
+        d = SnapshotDesc()
+        d.n_nodes, d.n_kinds, d.n_etypes = snap.n_nodes, snap.n_kinds, snap.n_etypes
+        d.n_rels, d.n_und, d.n_states = snap.n_rels, len(keep["und_adj"]), len(keep["st_node"])
+        d.n_typed_out, d.n_typed_in = len(keep["typed_out"]), len(keep["typed_in"])
+        for n in names:
+            setattr(d, n, keep[n].ctypes.data)
+        h = C.c_void_p()
+        rc = self.lib.rca_open(C.byref(d), device, C.byref(h))
+        if rc != 0:
+            raise RcaError(rc, self.lib.rca_last_error(None).decode())
+        self.h = h
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RcaError(rc, self.lib.rca_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.rca_close(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream: int):
+        self._ck(self.lib.rca_set_stream(self.h, int(cuda_stream)))
+
+    def reserve(self, frontier_entries: int, output_words: int):
+        self._ck(self.lib.rca_reserve(self.h, int(frontier_entries), int(output_words)))
+        self._gen += 1
+
+    def expand(self, plan: PlanDesc, seeds, seed_ts=None) -> ExpandResult:
+        sp, on_dev, k1 = _dev_ptr(seeds if not isinstance(seeds, (list, tuple)) else np.asarray(seeds, np.int32))
+        if isinstance(k1, np.ndarray) and k1.dtype != np.int32:
+            k1 = np.ascontiguousarray(k1, dtype=np.int32)
+            sp = k1.ctypes.data
+        n = int(k1.shape[0]) if k1 is not None else 0
+        tp, ts_dev, k2 = _dev_ptr(seed_ts if seed_ts is None or hasattr(seed_ts, "data_ptr")
+                                  else np.ascontiguousarray(seed_ts, dtype=np.int64))
+        if seed_ts is not None and ts_dev != on_dev:
+            raise ValueError("seeds and seed_ts must both be host or both be device buffers")
+        st = StatsDesc()
+        self._gen += 1
+        self._ck(self.lib.rca_expand(self.h, C.byref(plan), sp, n, tp, on_dev, C.byref(st)))
+        levels = plan.max_hops if plan.kind == PLAN_VARLEN else plan.n_steps
+        return ExpandResult(self, st, levels)
+
+    def state_lookup(self, nodes, ts, with_ids=True):
+        """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids)."""
+        nodes = np.ascontiguousarray(nodes, dtype=np.int32)
+        ts = np.ascontiguousarray(ts, dtype=np.int64)
+        n = len(nodes)
+        first = np.empty(n, np.int32)
+        cnt = np.empty(n, np.int32)
+        ids = np.empty((n, STATE_LIMIT), np.int32) if with_ids else None
+        self._ck(self.lib.rca_state_lookup(self.h, nodes.ctypes.data, ts.ctypes.data, n, 0, first.ctypes.data,
+                                           cnt.ctypes.data, ids.ctypes.data if with_ids else None))
+        return first, cnt, ids

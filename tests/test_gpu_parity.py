@@ -1,0 +1,251 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle on seeded graphs."""
+import numpy as np
+import pytest
+
+from conftest import rows_to_set, sort_rows
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng_small(snap_small):
+    from k8s_llm_rca_b200 import engine
+    e = engine.Engine(snap_small)
+    yield e
+    e.close()
+
+
+@pytest.fixture(scope="module")
+def eng_10k(snap_10k):
+    from k8s_llm_rca_b200 import engine
+    e = engine.Engine(snap_10k)
+    yield e
+    e.close()
+
+
+def _kinds(snap, *names):
+    return [snap.kind_index(n) for n in names]
+
+
+def check_varlen(eng, orc, seeds, direction, max_hops, **kw):
+    from k8s_llm_rca_b200 import engine
+    prune = kw.pop("prune", True)
+    plan = engine.varlen_plan(direction, max_hops, prune=prune, **kw)
+    res = eng.expand(plan, seeds)
+    ref, scanned = orc.varlen(seeds, direction, max_hops, **kw)
+    got = rows_to_set(res.all_rows())
+    want = rows_to_set(ref)
+    assert len(got) == len(want)
+    assert got == want                       # bit-exact as sorted sets of (nodes, rels)
+    assert res.total == len(want)
+    if not prune:
+        assert sum(res.scanned) == scanned   # same number of adjacency entries inspected
+    return res
+
+
+@pytest.mark.parametrize("direction", ["out", "in", "und"])
+@pytest.mark.parametrize("max_hops", [1, 2, 3, 4])
+def test_varlen_entity_projection(eng_small, snap_small, csr_oracle_lib, direction, max_hops):
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    pod, node, ev, ns = _kinds(snap_small, "Pod", "Node", "Event", "Namespace")
+    seeds = snap_small.nodes_of_kind(pod)
+    dest = node if direction != "in" else _kinds(snap_small, "Service")[0]
+    for prune in (True, False):
+        check_varlen(eng_small, orc, seeds, direction, max_hops, dest_kind=dest, excl_kinds=[ev, ns],
+                     entity_only=True, prune=prune)
+
+
+def test_varlen_with_intermediate_kinds(eng_small, snap_small, csr_oracle_lib):
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    pod, node, ev, ns, cm, rs = _kinds(snap_small, "Pod", "Node", "Event", "Namespace", "ConfigMap", "ReplicaSet")
+    seeds = snap_small.nodes_of_kind(pod)
+    res = check_varlen(eng_small, orc, seeds, "und", 4, dest_kind=node, excl_kinds=[ev, ns], inter_kinds=[cm, rs],
+                       entity_only=True)
+    assert res.emitted[1] == 0               # a 1-hop path has no interior node
+
+
+def test_varlen_full_graph_any_dest(eng_small, snap_small, csr_oracle_lib):
+    """entity_only off: STATE nodes are reachable; dest any; nothing excluded."""
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    seeds = np.arange(0, snap_small.n_nodes, 7, dtype=np.int32)
+    check_varlen(eng_small, orc, seeds, "und", 2, dest_kind=-1)
+    check_varlen(eng_small, orc, seeds, "out", 3, dest_kind=-1)
+
+
+def test_varlen_via_namespace_shape(eng_small, snap_small, csr_oracle_lib):
+    """src-Namespace-dest with r1 != r2 and nodes allowed to coincide (reference :125-129)."""
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    pod, ns, cm = _kinds(snap_small, "Pod", "Namespace", "ConfigMap")
+    seeds = snap_small.nodes_of_kind(pod)
+    check_varlen(eng_small, orc, seeds, "und", 2, min_hops=2, dest_kind=cm, node_simple=False,
+                 pos_kind=[pod, ns, cm], entity_only=True)
+    check_varlen(eng_small, orc, seeds, "und", 2, min_hops=2, dest_kind=pod, node_simple=False,
+                 pos_kind=[pod, ns, pod], entity_only=True)
+
+
+def test_varlen_edge_cases(eng_small, snap_small, csr_oracle_lib):
+    from k8s_llm_rca_b200 import engine
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    pod, node, ev, ns = _kinds(snap_small, "Pod", "Node", "Event", "Namespace")
+    # empty seed list
+    res = eng_small.expand(engine.varlen_plan("und", 3, dest_kind=node), np.zeros(0, np.int32))
+    assert res.total == 0
+    # seeds of an excluded kind, out-of-range seeds, duplicate seeds
+    seeds = np.concatenate([snap_small.nodes_of_kind(ns), [-5, snap_small.n_nodes + 3],
+                            snap_small.nodes_of_kind(pod)[:5], snap_small.nodes_of_kind(pod)[:5]]).astype(np.int32)
+    plan = engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    res = eng_small.expand(plan, seeds)
+    ok = seeds[(seeds >= 0) & (seeds < snap_small.n_nodes)]
+    ref, _ = orc.varlen(ok, "und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    assert rows_to_set(res.all_rows()) == rows_to_set(ref)
+    # one seed
+    check_varlen(eng_small, orc, snap_small.nodes_of_kind(pod)[:1], "und", 4, dest_kind=node, excl_kinds=[ev, ns],
+                 entity_only=True)
+
+
+def test_scratch_arena_growth(snap_small, csr_oracle_lib):
+    """A tiny reservation forces the overflow -> grow -> re-run path; results must not change."""
+    from k8s_llm_rca_b200 import engine
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    eng = engine.Engine(snap_small)
+    eng.reserve(64, 256)
+    pod, node, ev, ns = _kinds(snap_small, "Pod", "Node", "Event", "Namespace")
+    res = check_varlen(eng, orc, snap_small.nodes_of_kind(pod), "und", 3, dest_kind=node, excl_kinds=[ev, ns],
+                       entity_only=True)
+    assert res.retries >= 1
+    eng.close()
+
+
+def _chain_for(snap, *steps):
+    """steps: (relType, srcKind, dstKind, key, dir)"""
+    ets, dirs = [], []
+    for (rt, sk, dk, key, d) in steps:
+        t = snap.find_etypes(rt, snap.label_index(sk), snap.label_index(dk), key)
+        assert len(t) == 1
+        ets.append(t[0])
+        dirs.append(d)
+    return ets, dirs
+
+
+def test_chain_event_to_configmap(eng_10k, snap_10k, csr_oracle_lib):
+    """The instance query of the reference's worked example (generate_query.py:188-207):
+    EVENT <-HasEvent- Event -involvedObject-> Pod -configMap-> ConfigMap."""
+    from k8s_llm_rca_b200 import engine
+    orc = csr_oracle_lib.CsrOracle(snap_10k)
+    ets, dirs = _chain_for(snap_10k,
+                           ("HasEvent", "Event", "EVENT", "metadata_uid", "in"),
+                           ("ReferInternal", "Event", "Pod", "involvedObject_uid", "out"),
+                           ("ReferInternal", "Pod", "ConfigMap", "spec_volumes_configMap_name", "out"))
+    seeds = snap_10k.nodes_of_kind(snap_10k.label_index("EVENT"))
+    res = eng_10k.expand(engine.chain_plan(ets, dirs), seeds)
+    ref, _ = orc.chain(seeds, ets, [{"out": 0, "in": 1}[d] for d in dirs])
+    assert np.array_equal(sort_rows(res.rows(3)), sort_rows(ref))
+    assert res.total == len(ref) > 0
+
+
+def test_chain_with_reversed_step(eng_10k, snap_10k, csr_oracle_lib):
+    """Pod -> PVC <- PV -> nfs: the reversed step of reference test_generate_query.py:34-40."""
+    from k8s_llm_rca_b200 import engine
+    orc = csr_oracle_lib.CsrOracle(snap_10k)
+    ets, dirs = _chain_for(snap_10k,
+                           ("ReferInternal", "Pod", "PersistentVolumeClaim",
+                            "spec_volumes_persistentVolumeClaim_claimName", "out"),
+                           ("ReferInternal", "PersistentVolume", "PersistentVolumeClaim", "spec_claimRef_uid", "in"),
+                           ("UseExternal", "PersistentVolume", "nfs", "spec_nfs_path", "out"))
+    seeds = snap_10k.nodes_of_kind(snap_10k.kind_index("Pod"))
+    res = eng_10k.expand(engine.chain_plan(ets, dirs), seeds)
+    ref, _ = orc.chain(seeds, ets, [{"out": 0, "in": 1}[d] for d in dirs])
+    assert np.array_equal(sort_rows(res.rows(3)), sort_rows(ref))
+    assert len(ref) > 0
+    # seeds of the wrong kind produce nothing
+    res = eng_10k.expand(engine.chain_plan(ets, dirs), snap_10k.nodes_of_kind(snap_10k.kind_index("Node")))
+    assert res.total == 0
+
+
+def test_state_lookup(eng_10k, snap_10k, csr_oracle_lib):
+    orc = csr_oracle_lib.CsrOracle(snap_10k)
+    rng = np.random.default_rng(3)
+    n_ent = int(snap_10k.kind_start[snap_10k.kind_index("Event")])
+    nodes = rng.integers(0, n_ent, size=5000).astype(np.int32)
+    from k8s_llm_rca_b200.synth import T_BASE, DAY
+    ts = (T_BASE + rng.integers(-5 * DAY, 35 * DAY, size=5000)).astype(np.int64)
+    # hit interval boundaries exactly: tmin is inside, tmax is outside (half-open)
+    some = snap_10k.st_off[nodes[:200]]
+    has = snap_10k.st_off[nodes[:200] + 1] > some
+    ts[:200][has] = snap_10k.st_tmin[some[has]]
+    ts[200:400] = ts[:200]
+    ts[200:400][has] = snap_10k.st_tmax[some[has]]
+    nodes[200:400] = nodes[:200]
+    f, c, ids = eng_10k.state_lookup(nodes, ts)
+    rf, rc, rids = orc.states(nodes, ts)
+    assert np.array_equal(f, rf) and np.array_equal(c, rc) and np.array_equal(ids, rids)
+    assert (c == 0).any() and (c > 0).any()
+
+
+def test_fused_state_filter(eng_10k, snap_10k, csr_oracle_lib):
+    """with_states: every emitted row also carries, per node, the STATE valid at the seed's time."""
+    from k8s_llm_rca_b200 import engine
+    orc = csr_oracle_lib.CsrOracle(snap_10k)
+    pod, node, ev, ns = _kinds(snap_10k, "Pod", "Node", "Event", "Namespace")
+    seeds = snap_10k.nodes_of_kind(pod)[::5]
+    from k8s_llm_rca_b200.synth import T_BASE, DAY
+    ts = (T_BASE + np.random.default_rng(5).integers(0, 30 * DAY, size=len(seeds))).astype(np.int64)
+    plan = engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True, with_states=True)
+    res = eng_10k.expand(plan, seeds, ts)
+    ref, _ = orc.varlen(seeds, "und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    ts_of_seed = dict(zip(seeds.tolist(), ts.tolist()))
+    for s in (1, 2, 3):
+        got = sort_rows(res.rows(s))
+        want = sort_rows(ref.get(s, np.zeros((0, 2 * s + 1), np.int32)))
+        assert got.shape == (len(want), 3 * s + 3)
+        assert np.array_equal(got[:, :2 * s + 1], want)
+        if len(got) == 0:
+            continue
+        t = np.array([ts_of_seed[v] for v in got[:, 0].tolist()], dtype=np.int64)
+        miss = np.zeros(len(got), np.int64)
+        for d in range(s + 1):
+            f, c, _ = orc.states(got[:, d], t)
+            assert np.array_equal(got[:, 2 * s + 1 + d], f)
+            miss |= (c == 0).astype(np.int64) << d
+        assert np.array_equal(got[:, 3 * s + 2].astype(np.int64), miss)
+
+
+def test_10k_all_source_kinds_to_node(eng_10k, snap_10k, csr_oracle_lib):
+    """BASELINE config 2 shape: every source kind -> Node, <= 4 hops, directed then undirected."""
+    orc = csr_oracle_lib.CsrOracle(snap_10k)
+    node, ev, ns = _kinds(snap_10k, "Node", "Event", "Namespace")
+    for k, kind in enumerate(snap_10k.kinds):
+        if kind.is_state or kind.name in ("Event", "Namespace"):
+            continue
+        seeds = snap_10k.nodes_of_kind(k)[::4]
+        check_varlen(eng_10k, orc, seeds, "out", 4, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+        check_varlen(eng_10k, orc, seeds, "und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+
+
+def test_determinism(eng_10k, snap_10k):
+    """Same input -> byte-identical output buffers (slot = f(seed order, CSR order))."""
+    from k8s_llm_rca_b200 import engine
+    pod, node, ev, ns = _kinds(snap_10k, "Pod", "Node", "Event", "Namespace")
+    plan = engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    seeds = snap_10k.nodes_of_kind(pod)
+    a = eng_10k.expand(plan, seeds).all_rows()
+    b = eng_10k.expand(plan, seeds).all_rows()
+    assert a.keys() == b.keys()
+    for s in a:
+        assert np.array_equal(a[s], b[s])
+
+
+def test_metagraph_on_gpu(snap_10k, csr_oracle_lib):
+    """The reference's own use: metapaths Pod -> nfs on the (tiny) metagraph."""
+    from k8s_llm_rca_b200 import engine
+    meta = snap_10k.derive_metagraph()
+    orc = csr_oracle_lib.CsrOracle(meta)
+    eng = engine.Engine(meta)
+    pod, nfs, ev, ns, pv, pvc = _kinds(meta, "Pod", "nfs", "Event", "Namespace", "PersistentVolume",
+                                       "PersistentVolumeClaim")
+    seeds = meta.nodes_of_kind(pod)
+    res = check_varlen(eng, orc, seeds, "out", 3, dest_kind=nfs, excl_kinds=[ev, ns], inter_kinds=[pvc, pv])
+    assert res.total == 0                     # PV -> PVC points the other way: no directed path
+    res = check_varlen(eng, orc, seeds, "und", 3, dest_kind=nfs, excl_kinds=[ev, ns], inter_kinds=[pvc, pv])
+    assert res.total >= 1
+    eng.close()
