@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""bench.py - path-instances/s of the hot path on BASELINE.json's headline configuration.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One step = one pass of the hot path over one incident batch (workloads.Config3): the undirected
+<=4-hop Pod->Node enumeration from 100k seed Pods plus the five per-incident instance queries,
+with the state predicate fused into emission.  Multi-GPU: graph replicated, one incident batch
+per rank (weak scaling), NCCL all-gather of the per-rank instance counts; no data-path collective.
+
+Printed line (rank 0): see the contract in the project brief.  `value` = instances of all ranks /
+max-over-ranks device time with inputs resident in HBM; `e2e` = the same through host buffers
+(pinned H2D of seeds and timestamps, D2H of every result row inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "path-instances/s"
+FALLBACK_HBM_GBS = 6650.0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement of the reference's path (oracle/csr_oracle.c, kind
+    "port" - Neo4j itself is unavailable on this box), all host threads, bounded sample."""
+    if rank != 0:
+        return
+    from k8s_llm_rca_b200 import workloads
+    from oracle.csr import CsrOracle, build
+    build()
+    w = workloads.Config3(n_objects=args.objects, n_events=args.events)
+    orc = CsrOracle(w.snap)
+    pods, ev, ts = w.batch(0)
+    n = min(len(pods), args.cpu_sample)
+    pods, ev, ts = pods[:n], ev[:n], ts[:n]
+    threads = orc.max_threads()
+    for _ in range(args.warmup):
+        w.oracle_run(orc, pods[:max(1, n // 10)], ev[:max(1, n // 10)], ts[:max(1, n // 10)])
+    t0 = time.perf_counter()
+    inst = 0
+    for _ in range(args.steps):
+        tot, _ = w.oracle_run(orc, pods, ev, ts)
+        inst += tot
+    dt = time.perf_counter() - t0
+    v = inst / dt
+    sample = f"first {n} of {w.n_inc} incidents of the config-3 batch per step"
+    print(json.dumps({
+        "metric": METRIC, "value": v, "unit": "instances/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic", "impl": "reference",
+        "config": {"workload": w.name, "objects": args.objects, "incidents_per_step": n},
+        "cpu_baseline": {"value": v, "unit": "instances/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--objects", type=int, default=1_000_000)
+    ap.add_argument("--events", type=int, default=108_696)
+    ap.add_argument("--cpu-sample", type=int, default=50_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU path (use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from k8s_llm_rca_b200 import engine as E
+    from k8s_llm_rca_b200 import workloads
+    w = workloads.Config3(n_objects=args.objects, n_events=args.events)
+    eng = E.Engine(w.snap, device=local_rank)
+    stream = torch.cuda.Stream()
+    eng.set_stream(stream.cuda_stream)
+    pods, ev, ts = w.batch(rank)
+    dev = torch.device("cuda", local_rank)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        d_pods, d_ev, d_ts = (torch.from_numpy(x).to(dev) for x in (pods, ev, ts))
+        h_pods, h_ev, h_ts = (torch.from_numpy(x).pin_memory() for x in (pods, ev, ts))
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+        counts = torch.zeros(world, dtype=torch.int64, device=dev)
+
+        # size the pinned result buffer from one untimed run
+        tot0, res0 = w.run(eng, d_pods, d_ev, d_ts)
+        max_words = max(max(r.emitted[s] * r.row_len[s] for s in range(r.levels + 1)) for _, r in res0)
+        h_rows = torch.empty(max_words + 16, dtype=torch.int32).pin_memory().numpy()
+        d2h = [0]
+
+        def fetch(r):
+            for s in range(1, r.levels + 1):
+                if r.emitted[s]:
+                    r.rows(s, out=h_rows)
+                    d2h[0] += r.emitted[s] * r.row_len[s] * 4
+
+        def step(resident):
+            if resident:
+                tot, res = w.run(eng, d_pods, d_ev, d_ts)
+            else:
+                tot, res = w.run(eng, h_pods.numpy(), h_ev.numpy(), h_ts.numpy(), fetch=fetch)
+            if world > 1:       # the only collective of the path: every rank learns every rank's count
+                mine = torch.tensor([tot], dtype=torch.int64, device=dev)
+                dist.all_gather_into_tensor(counts, mine)
+            return tot, res
+
+        def timed(resident, steps):
+            evs = []
+            inst, launches, per_level = 0, 0, {}
+            for _ in range(steps):
+                flush.zero_()                                                # evict the graph from L2
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                tot, res = step(resident)
+                e1.record(stream)
+                evs.append((e0, e1))
+                inst += tot
+                for name, r in res:
+                    launches += r.launches
+                    for s in range(1, r.levels + 1):
+                        a = per_level.setdefault((name, s), [0.0, 0, 0])
+                        a[0] += r.level_ms[s]
+                        a[1] += r.level_bytes(s)
+                        a[2] += 1
+            torch.cuda.synchronize()
+            ms = sum(a.elapsed_time(b) for a, b in evs)
+            return ms, inst, launches, per_level
+
+        for _ in range(args.warmup):
+            step(True)
+        for _ in range(args.warmup):
+            step(False)
+
+        sampler = ClockSampler(local_rank)
+        barrier()
+        if rank == 0:
+            sampler.start()
+        ms_res, inst_res, launches, per_level = timed(True, args.steps)
+        barrier()
+        d2h[0] = 0
+        t0 = time.perf_counter()
+        ms_e2e, inst_e2e, _, _ = timed(False, args.steps)
+        wall_e2e = time.perf_counter() - t0
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+
+    # max over ranks of the device time, sum over ranks of the instances
+    red = torch.tensor([ms_res, ms_e2e], dtype=torch.float64, device=dev)
+    tot = torch.tensor([inst_res, inst_e2e], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_res, ms_e2e = red.tolist()
+    inst_res, inst_e2e = tot.tolist()
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        # dominant kernel = the level launch with the largest share of the step
+        (kname, ks), (kms, kbytes, kcalls) = max(per_level.items(), key=lambda kv: kv[1][0])
+        achieved = (kbytes / kcalls) / (kms / kcalls * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get(f"{kname}/level{ks}")
+            except Exception:
+                traffic = None
+        step_ms_sum = sum(v[0] for v in per_level.values())
+        out = {
+            "metric": METRIC, "value": inst_res / (ms_res * 1e-3), "unit": "instances/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_res / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": w.name, "objects": args.objects, "incidents_per_step_per_gpu": int(len(pods)),
+                       "instances_per_step": inst_res // args.steps, "max_hops": w.max_hops,
+                       "graph_bytes_in_hbm": int(w.snap.device_bytes()),
+                       "l2": "flushed between timed steps (256 MiB write); graph (338 MB) also exceeds the 126 MB L2",
+                       "parallelism": f"graph replicated x{world}, one incident batch per GPU, all-gather of counts"},
+            "e2e": {"value": inst_e2e / (ms_e2e * 1e-3), "unit": "instances/s",
+                    "h2d_bytes_per_step": int(6 * (pods.nbytes + ts.nbytes)),
+                    "d2h_bytes_per_step": int(d2h[0] // args.steps), "ms_per_step": ms_e2e / args.steps,
+                    "wall_ms_per_step": 1e3 * wall_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "kernel": f"expand_level ({kname}, level {ks})",
+                         "peak_source": peak_src, "bytes_per_launch": kbytes // kcalls,
+                         "ms_per_launch": kms / kcalls, "share_of_step": kms / step_ms_sum if step_ms_sum else None},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle.csr import CsrOracle, build
+            build()
+            orc = CsrOracle(w.snap)
+            n = min(len(pods), args.cpu_sample)
+            w.oracle_run(orc, pods[:n // 10], ev[:n // 10], ts[:n // 10])
+            t0 = time.perf_counter()
+            ctot, _ = w.oracle_run(orc, pods[:n], ev[:n], ts[:n])
+            dt = time.perf_counter() - t0
+            out["cpu_baseline"] = {"value": ctot / dt, "unit": "instances/s", "cores": orc.max_threads(), "kind": "port",
+                                   "sample": f"first {n} of {len(pods)} incidents of the same batch, one pass, {dt:.1f} s"}
+        print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

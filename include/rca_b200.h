@@ -99,7 +99,8 @@ typedef struct {
     int64_t emitted[RCA_MAX_HOPS + 1];   /* N_s: path instances of length s                      */
     int32_t row_len[RCA_MAX_HOPS + 1];   /* int32 words per row at level s                       */
     int64_t total;                       /* sum of emitted                                       */
-    double kernel_ms;                    /* device time of the expansion kernels (CUDA events)   */
+    double kernel_ms;                    /* device time of the whole expansion (CUDA events)     */
+    double level_ms[RCA_MAX_HOPS + 1];   /* device time of the launch that produced level s      */
     int32_t launches;                    /* kernels launched                                     */
     int32_t retries;                     /* re-runs after growing the scratch arenas             */
 } rca_stats_t;

@@ -25,6 +25,7 @@ struct rca_engine {
     int sm_count = 148;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_lv[RCA_MAX_HOPS + 2] = {nullptr};
     std::string err;
     // graph
     int n_nodes = 0, n_kinds = 0, n_etypes = 0;
@@ -123,6 +124,7 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
     g->stream = g->own_stream;
     OCK(cudaEventCreate(&g->ev0));
     OCK(cudaEventCreate(&g->ev1));
+    for (auto &ev : g->ev_lv) OCK(cudaEventCreate(&ev));
     g->n_nodes = s->n_nodes; g->n_kinds = s->n_kinds; g->n_etypes = s->n_etypes;
     g->n_rels = s->n_rels; g->n_und = s->n_und; g->n_states = s->n_states;
     g->kind_start.assign(s->kind_start, s->kind_start + s->n_kinds + 1);
@@ -165,6 +167,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->h_ktab) cudaFreeHost(e->h_ktab);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
+    for (auto ev : e->ev_lv) if (ev) cudaEventDestroy(ev);
     if (e->own_stream) cudaStreamDestroy(e->own_stream);
     delete e;
     return RCA_OK;
@@ -330,6 +333,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         CK(cudaEventRecord(e->ev0, e->stream));
         CK(cudaMemcpyAsync(e->ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
         CK(cudaMemsetAsync(e->tstate, 0, tneed * sizeof(unsigned long long), e->stream));
+        CK(cudaEventRecord(e->ev_lv[0], e->stream));
         for (int s = 1; s <= L; s++) {
             LevelParams p;
             std::memset(&p, 0, sizeof p);
@@ -382,6 +386,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             }
             launches++;
             CK(cudaGetLastError());
+            CK(cudaEventRecord(e->ev_lv[s], e->stream));
         }
         CK(cudaEventRecord(e->ev1, e->stream));
         CK(cudaMemcpyAsync(e->h_ctl, e->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
@@ -418,6 +423,10 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         for (int s = 0; s <= L; s++) { stats->emitted[s] = e->res_rows[s]; stats->row_len[s] = e->res_row_len[s]; }
         stats->total = total;
         stats->kernel_ms = ms;
+        for (int s = 1; s <= L; s++) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, e->ev_lv[s - 1], e->ev_lv[s]) == cudaSuccess) stats->level_ms[s] = t;
+        }
         stats->launches = launches;
         stats->retries = retries;
     }

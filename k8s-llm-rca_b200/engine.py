@@ -56,7 +56,7 @@ class PlanDesc(C.Structure):
 class StatsDesc(C.Structure):
     _fields_ = [("frontier", C.c_int64 * (MAX_HOPS + 1)), ("scanned", C.c_int64 * (MAX_HOPS + 1)),
                 ("emitted", C.c_int64 * (MAX_HOPS + 1)), ("row_len", C.c_int32 * (MAX_HOPS + 1)),
-                ("total", C.c_int64), ("kernel_ms", C.c_double), ("launches", C.c_int32), ("retries", C.c_int32)]
+                ("total", C.c_int64), ("kernel_ms", C.c_double), ("level_ms", C.c_double * (MAX_HOPS + 1)), ("launches", C.c_int32), ("retries", C.c_int32)]
 
 
 _lib = None
@@ -160,14 +160,22 @@ class ExpandResult:
         self.row_len = list(st.row_len)[:levels + 1]
         self.total = int(st.total)
         self.kernel_ms = float(st.kernel_ms)
+        self.level_ms = list(st.level_ms)[:levels + 1]
         self.launches = int(st.launches)
         self.retries = int(st.retries)
         self._gen = engine._gen
 
-    def rows(self, level: int) -> np.ndarray:
+    def rows(self, level: int, out: np.ndarray | None = None) -> np.ndarray:
+        """Copy the rows of one level to the host.  `out`: optional pre-allocated (ideally pinned)
+        int32 buffer with room for n*row_len words; a view of it is returned."""
         assert self._gen == self.engine._gen, "result was overwritten by a later expand()"
         n, w = self.emitted[level], self.row_len[level]
-        out = np.empty((n, w), dtype=np.int32)
+        if out is not None:
+            flat = out.reshape(-1)
+            assert flat.dtype == np.int32 and flat.size >= n * w and flat.flags.c_contiguous
+            out = flat[:n * w].reshape(n, w)
+        else:
+            out = np.empty((n, w), dtype=np.int32)
         if n:
             self.engine._ck(self.engine.lib.rca_result_copy(self.engine.h, level, out.ctypes.data))
         return out
@@ -182,15 +190,17 @@ class ExpandResult:
         self.engine._ck(self.engine.lib.rca_result_level(self.engine.h, level, C.byref(p), C.byref(n), C.byref(w)))
         return (p.value or 0), int(n.value), int(w.value)
 
-    def algorithmic_bytes(self) -> int:
-        """sum_s (12 F_{s-1} + 4 E_s) + 4 (2s+1) N_s, plus, with the fused
-        state filter, (s+1) N_s (8 + 16 I + 5) with I = 1 interval inspected per node."""
-        b = 0
-        for s in range(1, self.levels + 1):
-            b += 12 * self.frontier[s - 1] + 4 * self.scanned[s] + 4 * (2 * s + 1) * self.emitted[s]
-            if self.row_len[s] > 2 * s + 1:
-                b += (s + 1) * self.emitted[s] * (8 + 16 + 5)
+    def level_bytes(self, s: int) -> int:
+        """Algorithmic bytes of the launch that produced level s:
+        12 F_{s-1} + 4 E_s + 4 (2s+1) N_s, plus, with the fused state filter,
+        (s+1) N_s (8 + 16 I + 5) with I = 1 interval inspected per node."""
+        b = 12 * self.frontier[s - 1] + 4 * self.scanned[s] + 4 * (2 * s + 1) * self.emitted[s]
+        if self.row_len[s] > 2 * s + 1:
+            b += (s + 1) * self.emitted[s] * (8 + 16 + 5)
         return b
+
+    def algorithmic_bytes(self) -> int:
+        return sum(self.level_bytes(s) for s in range(1, self.levels + 1))
 
 
 class Engine:

@@ -1,0 +1,127 @@
+"""The benchmark workloads of BASELINE.json, expressed as plans + seeds over a generated graph.
+
+`Config3` is the configuration the headline metric is quoted on: a 1M-object multi-tenant
+cluster, 100k seed Pods (every 5th Pod, each with one incident timestamp), per step
+  (a) the undirected <=4-hop Pod -> Node enumeration from every seed Pod (the variable-length
+      statement of reference find_metapath/find_srckind_metapath_neo4j.py:107-116 applied to the
+      instance graph's entity projection), and
+  (b) the per-incident instance queries (reference generate_query/generate_query.py:214-260) for
+      the metapaths Pod -> {Node, ConfigMap (two edge types), Secret, nfs via PVC <- PV},
+both with the state predicate of check_state/analyze_root_cause.py:70-79 fused into emission.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import engine as E
+from . import synth
+
+N_OBJECTS = 1_000_000
+N_EVENTS = 108_696            # 92 % of them involve a Pod -> 100,000 seed Pods = every 5th Pod
+
+
+class Config3:
+    name = "config3: 1M-object cluster, 100k seed Pods, undirected <=4-hop Pod->Node + 5 instance queries, fused state filter"
+
+    def __init__(self, snap=None, n_objects=N_OBJECTS, n_events=N_EVENTS, max_hops=4, with_states=True):
+        self.snap = snap if snap is not None else synth.generate(n_objects, n_events, synth.config_seed(2))
+        s = self.snap
+        self.max_hops = max_hops
+        K = s.kind_index
+        self.excl = [K("Event"), K("Namespace")]
+        self.varlen = E.varlen_plan("und", max_hops, dest_kind=K("Node"), excl_kinds=self.excl, entity_only=True,
+                                    with_states=with_states)
+        L = s.label_index
+
+        def et(rel, a, b, key):
+            t = s.find_etypes(rel, L(a), L(b), key)
+            assert len(t) == 1, (rel, a, b, key)
+            return t[0]
+
+        head = [(et("HasEvent", "Event", "EVENT", "metadata_uid"), "in"),
+                (et("ReferInternal", "Event", "Pod", "involvedObject_uid"), "out")]
+        tails = {
+            "Pod->Node": [(et("ReferInternal", "Pod", "Node", "spec_nodeName"), "out")],
+            "Pod->ConfigMap(volume)": [(et("ReferInternal", "Pod", "ConfigMap", "spec_volumes_configMap_name"), "out")],
+            "Pod->ConfigMap(envFrom)": [(et("ReferInternal", "Pod", "ConfigMap",
+                                            "spec_containers_envFrom_configMapRef_name"), "out")],
+            "Pod->Secret": [(et("ReferInternal", "Pod", "Secret", "spec_volumes_secret_secretName"), "out")],
+            "Pod->PVC<-PV->nfs": [
+                (et("ReferInternal", "Pod", "PersistentVolumeClaim", "spec_volumes_persistentVolumeClaim_claimName"), "out"),
+                (et("ReferInternal", "PersistentVolume", "PersistentVolumeClaim", "spec_claimRef_uid"), "in"),
+                (et("UseExternal", "PersistentVolume", "nfs", "spec_nfs_path"), "out")],
+        }
+        self.chains = {}
+        for name, tail in tails.items():
+            steps = head + tail
+            self.chains[name] = ([t for t, _ in steps], [d for _, d in steps],
+                                 E.chain_plan([t for t, _ in steps], [d for _, d in steps], with_states=with_states))
+        self.with_states = with_states
+        syn = s.synth
+        self.n_inc = int(syn["n_pod_events"])
+        self._ev_state_lo = s.kind_range(s.label_index("EVENT"))[0]
+        self._pod_lo, self._pod_hi = s.kind_range(K("Pod"))
+
+    def batch(self, rank: int = 0):
+        """Incident batch of one rank: (seed Pods, EVENT nodes, timestamps ms).  Every rank gets the
+        same number of incidents (weak scaling); rank r's Pods are the (r mod 5)-th residue class
+        of the Pod ids, so ranks 0..4 touch disjoint seed sets."""
+        s = self.snap
+        pods = s.synth["event_pod"][:self.n_inc].astype(np.int64)
+        n_pod = self._pod_hi - self._pod_lo
+        pods = (pods - self._pod_lo + (rank % 5) + 5 * (rank // 5) * 997) % n_pod + self._pod_lo
+        ev = (self._ev_state_lo + np.arange(self.n_inc)).astype(np.int32)
+        ts = np.asarray(s.props.ev_ts[:self.n_inc], dtype=np.int64)
+        if rank:
+            ts = ts + rank * 3_600_000
+        return pods.astype(np.int32), ev, ts
+
+    def run(self, eng: E.Engine, pods, ev, ts, fetch=None):
+        """One step.  `fetch(result)` is called after each expansion while its rows are still
+        resident (e2e runs copy them out there).  Returns (instances, [ExpandResult...])."""
+        results = []
+        total = 0
+        r = eng.expand(self.varlen, pods, ts if self.with_states else None)
+        if fetch:
+            fetch(r)
+        results.append(("varlen", r))
+        total += r.total
+        for name, (_, _, plan) in self.chains.items():
+            r = eng.expand(plan, ev, ts if self.with_states else None)
+            if fetch:
+                fetch(r)
+            results.append((name, r))
+            total += r.total
+        return total, results
+
+    def oracle_run(self, orc, pods, ev, ts, threads=0):
+        """The same step on the CPU oracle (callers: tests and bench.py's cpu_baseline leg only):
+        the enumeration, the five instance queries, and the state predicate for every node of
+        every row.  Returns (instances, {plan name: {length: rows with state columns}})."""
+        s = self.snap
+        total = 0
+        out = {}
+
+        def with_state_cols(rows, length, seeds):
+            if not self.with_states or len(rows) == 0:
+                return rows
+            order = np.argsort(seeds, kind="stable")
+            t = ts[order[np.searchsorted(seeds[order], rows[:, 0])]]
+            cols = [rows]
+            miss = np.zeros(len(rows), np.int64)
+            for d in range(length + 1):
+                first, cnt, _ = orc.states(rows[:, d], t, limit=1)
+                cols.append(first[:, None])
+                miss |= (cnt == 0).astype(np.int64) << d
+            cols.append(miss.astype(np.int32)[:, None])
+            return np.concatenate(cols, axis=1)
+
+        lv, _ = orc.varlen(pods, "und", self.max_hops, dest_kind=s.kind_index("Node"), excl_kinds=self.excl,
+                           entity_only=True, threads=threads)
+        out["varlen"] = {length: with_state_cols(rows, length, pods) for length, rows in lv.items()}
+        total += sum(len(r) for r in lv.values())
+        for name, (ets, dirs, _) in self.chains.items():
+            rows, _ = orc.chain(ev, ets, [{"out": 0, "in": 1}[d] for d in dirs], threads=threads)
+            out[name] = {len(ets): with_state_cols(rows, len(ets), ev)}
+            total += len(rows)
+        return total, out
