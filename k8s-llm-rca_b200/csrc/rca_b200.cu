@@ -31,18 +31,21 @@ struct rca_engine {
     int n_nodes = 0, n_kinds = 0, n_etypes = 0;
     long long n_rels = 0, n_und = 0, n_states = 0;
     std::vector<int> kind_start, et_src, et_dst, et_cls;
+    std::vector<unsigned char> kind_lut;   // node id block -> kind of the block's first id
+    int lut_shift = 0;
     std::vector<long long> typed_out_base, typed_in_base;
     int2 *out_rng = nullptr, *in_rng = nullptr, *und_rng = nullptr, *in_adj = nullptr, *und_adj = nullptr;
     int2 *typed_out = nullptr, *typed_in = nullptr;
-    int *out_dst = nullptr, *st_off = nullptr, *st_node = nullptr;
-    long long *st_tmin = nullptr, *st_tmax = nullptr;
+    int *out_dst = nullptr, *st_off = nullptr;
+    StRec *st_rec = nullptr;              // HasState intervals, one 32 B record each
     // scratch
     int4 *frontier = nullptr;
     unsigned long long fcap = 0;
     int *out = nullptr;
     unsigned long long ocap = 0;
-    unsigned long long *tstate = nullptr;
+    ulonglong2 *tstate = nullptr;         // tile-state words, tagged with `epoch`; zeroed when (re)allocated
     unsigned long long tcap = 0;
+    unsigned epoch = 0;
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
     int *ktab = nullptr, *h_ktab = nullptr;
@@ -128,6 +131,13 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
     g->n_nodes = s->n_nodes; g->n_kinds = s->n_kinds; g->n_etypes = s->n_etypes;
     g->n_rels = s->n_rels; g->n_und = s->n_und; g->n_states = s->n_states;
     g->kind_start.assign(s->kind_start, s->kind_start + s->n_kinds + 1);
+    while (((long long)std::max(s->n_nodes, 1) - 1) >> g->lut_shift >= kLutEntries) g->lut_shift++;
+    g->kind_lut.assign(kLutEntries, 0);
+    for (int b = 0, k = 0; b < kLutEntries; b++) {
+        const long long v = (long long)b << g->lut_shift;
+        while (k + 1 < s->n_kinds && s->kind_start[k + 1] <= v) k++;
+        g->kind_lut[b] = (unsigned char)k;
+    }
     g->et_src.assign(s->et_src, s->et_src + s->n_etypes);
     g->et_dst.assign(s->et_dst, s->et_dst + s->n_etypes);
     g->et_cls.assign(s->et_cls, s->et_cls + s->n_etypes);
@@ -143,13 +153,15 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
     OCK(upload(&g->typed_out, s->typed_out, (size_t)s->n_typed_out));
     OCK(upload(&g->typed_in, s->typed_in, (size_t)s->n_typed_in));
     OCK(upload(&g->st_off, s->st_off, V1));
-    OCK(upload(&g->st_tmin, s->st_tmin, (size_t)s->n_states));
-    OCK(upload(&g->st_tmax, s->st_tmax, (size_t)s->n_states));
-    OCK(upload(&g->st_node, s->st_node, (size_t)s->n_states));
+    {
+        std::vector<StRec> rec((size_t)s->n_states);
+        for (size_t j = 0; j < rec.size(); j++) rec[j] = StRec{s->st_tmin[j], s->st_tmax[j], s->st_node[j], {0, 0, 0}};
+        OCK(upload(&g->st_rec, rec.data(), rec.size()));
+    }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
     OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
-    OCK(cudaMalloc((void **)&g->ktab, (2 * RCA_MAX_KINDS + 8) * sizeof(int)));
-    OCK(cudaMallocHost((void **)&g->h_ktab, (2 * RCA_MAX_KINDS + 8) * sizeof(int)));
+    OCK(cudaMalloc((void **)&g->ktab, kKtabWords * sizeof(int)));
+    OCK(cudaMallocHost((void **)&g->h_ktab, kKtabWords * sizeof(int)));
 #undef OCK
     *out = up.release();
     return RCA_OK;
@@ -160,7 +172,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_node, e->st_tmin, e->st_tmax, e->frontier, e->out, e->tstate, e->ctl, e->ktab,
+                   e->st_off, e->st_rec, e->frontier, e->out, e->tstate, e->ctl, e->ktab,
                    e->seeds_buf, e->ts_buf, e->io_buf};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
@@ -264,9 +276,9 @@ static int validate_plan(rca_engine *e, const rca_plan_t *pl) {
 static int row_len_of(const rca_plan_t *pl, int s) { return pl->with_states ? 3 * s + 3 : 2 * s + 1; }
 
 template <typename K>
-static int max_grid(rca_engine *e, K kernel) {
+static int max_grid(rca_engine *e, K kernel, size_t dyn_smem) {
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem) != cudaSuccess || per_sm < 1) per_sm = 1;
     return e->sm_count * per_sm;
 }
 
@@ -274,7 +286,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
                           const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats) {
     if (!e) return RCA_ERR_ARG;
     if (!pl || n_seeds < 0 || (n_seeds > 0 && !seeds)) return fail(e, RCA_ERR_ARG, "rca_expand: null plan or seeds");
-    if (n_seeds > (int64_t)kHalf) return fail(e, RCA_ERR_ARG, "rca_expand: more than 2^31-1 seeds in one call");
+    if (n_seeds > 0x7fffffffLL) return fail(e, RCA_ERR_ARG, "rca_expand: more than 2^31-1 seeds in one call");
     if (pl->with_states && n_seeds > 0 && !seed_ts) return fail(e, RCA_ERR_ARG, "rca_expand: with_states needs seed_ts");
     int rc = validate_plan(e, pl);
     if (rc) return rc;
@@ -305,7 +317,8 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
 
     // ---- kind tables of this plan: kind_start (padded to 4) then attribute words
     const int nkp = (e->n_kinds + 1 + 3) & ~3, nka = (e->n_kinds + 3) & ~3;
-    std::memset(e->h_ktab, 0, (size_t)(nkp + nka) * sizeof(int));
+    std::memset(e->h_ktab, 0, (size_t)(nkp + nka + kLutWords) * sizeof(int));
+    std::memcpy(e->h_ktab + nkp + nka, e->kind_lut.data(), kLutEntries);
     for (int k = 0; k <= e->n_kinds; k++) e->h_ktab[k] = e->kind_start[k];
     for (int k = e->n_kinds + 1; k < nkp; k++) e->h_ktab[k] = 0x7fffffff;
     if (varlen) {
@@ -315,7 +328,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             e->h_ktab[nkp + k] = (int)((pl->kind_excl[k] ? kAttrExcl : 0u) | (pl->kind_inter[k] ? kAttrInter : 0u) |
                                        (reach[k] << kAttrReachShift));
     }
-    CK(cudaMemcpyAsync(e->ktab, e->h_ktab, (size_t)(nkp + nka) * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->ktab, e->h_ktab, (size_t)(nkp + nka + kLutWords) * sizeof(int), cudaMemcpyHostToDevice, e->stream));
 
     // ---- scratch arenas: keep what earlier calls grew to, else a guess from the seed count
     if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * n_seeds, 1ull << 20)); if (rc) return rc; }
@@ -325,14 +338,17 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     float ms = 0.f;
     while (true) {
         const unsigned long long tneed = ((unsigned long long)n_seeds + e->fcap) / kTile + kLv + 2;
-        rc = grow(e, &e->tstate, &e->tcap, tneed);
-        if (rc) return rc;
+        if (tneed > e->tcap || (++e->epoch & 0x3fffffffu) == 0) {     // new array or epoch wrapped: start from zeros
+            rc = grow(e, &e->tstate, &e->tcap, std::max(tneed, e->tcap));
+            if (rc) return rc;
+            CK(cudaMemsetAsync(e->tstate, 0, e->tcap * sizeof(ulonglong2), e->stream));
+            e->epoch = 1;
+        }
         launches = 0;
         std::memset(e->h_ctl, 0, sizeof(Ctl));
         e->h_ctl->F[0] = (unsigned long long)n_seeds;
         CK(cudaEventRecord(e->ev0, e->stream));
         CK(cudaMemcpyAsync(e->ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
-        CK(cudaMemsetAsync(e->tstate, 0, tneed * sizeof(unsigned long long), e->stream));
         CK(cudaEventRecord(e->ev_lv[0], e->stream));
         for (int s = 1; s <= L; s++) {
             LevelParams p;
@@ -368,21 +384,22 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             p.frontier = e->frontier; p.fcap = e->fcap;
             p.out = e->out; p.ocap = e->ocap;
             p.ctl = e->ctl; p.tstate = e->tstate;
-            p.ktab = e->ktab; p.n_kinds = e->n_kinds; p.nkp = nkp; p.nka = nka;
-            p.st_off = e->st_off; p.st_tmin = e->st_tmin; p.st_tmax = e->st_tmax; p.st_node = e->st_node;
+            p.ktab = e->ktab; p.n_kinds = e->n_kinds; p.nkp = nkp; p.nka = nka; p.lut_shift = e->lut_shift;
+            p.st_off = e->st_off; p.st_rec = e->st_rec; p.epoch = e->epoch;
             int grid;
+            const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
             if (dir == RCA_DIR_OUT) {
-                if (varlen) { grid = max_grid(e, expand_level<false, true>); } else { grid = max_grid(e, expand_level<false, false>); }
+                if (varlen) { grid = max_grid(e, expand_level<false, true>, dyn); } else { grid = max_grid(e, expand_level<false, false>, dyn); }
             } else {
-                if (varlen) { grid = max_grid(e, expand_level<true, true>); } else { grid = max_grid(e, expand_level<true, false>); }
+                if (varlen) { grid = max_grid(e, expand_level<true, true>, dyn); } else { grid = max_grid(e, expand_level<true, false>, dyn); }
             }
-            if (s == 1) grid = (int)std::min<long long>(grid, std::max<long long>(1, (n_seeds + kTile - 1) / kTile));
+            if (s == 1) grid = (int)std::min<long long>(grid, std::max<long long>(1, (n_seeds + kTile * kWarps - 1) / (kTile * kWarps)));
             if (dir == RCA_DIR_OUT) {
-                if (varlen) expand_level<false, true><<<grid, kThreads, 0, e->stream>>>(p);
-                else expand_level<false, false><<<grid, kThreads, 0, e->stream>>>(p);
+                if (varlen) expand_level<false, true><<<grid, kThreads, dyn, e->stream>>>(p);
+                else expand_level<false, false><<<grid, kThreads, dyn, e->stream>>>(p);
             } else {
-                if (varlen) expand_level<true, true><<<grid, kThreads, 0, e->stream>>>(p);
-                else expand_level<true, false><<<grid, kThreads, 0, e->stream>>>(p);
+                if (varlen) expand_level<true, true><<<grid, kThreads, dyn, e->stream>>>(p);
+                else expand_level<true, false><<<grid, kThreads, dyn, e->stream>>>(p);
             }
             launches++;
             CK(cudaGetLastError());
@@ -394,7 +411,6 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         CK(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
         const unsigned ov = e->h_ctl->overflow;
         if (!ov) break;
-        if (ov & 4u) return fail(e, RCA_ERR_ARG, "rca_expand: a level holds more than 2^31-1 partial paths or rows; split the seeds");
         if (++retries > 12) return fail(e, RCA_ERR_NOMEM, "rca_expand: scratch arenas still too small after %d retries", retries);
         // counters are exact up to and including the first level that overflowed: grow to at least that
         unsigned long long fneed = 0, oneed = 0;
@@ -482,7 +498,7 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
         CK(cudaMemcpyAsync((void *)d_ts, ts, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
         CK(cudaMemcpyAsync((void *)d_nodes, nodes, 4 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
     }
-    state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_tmin, e->st_tmax, e->st_node, e->n_nodes,
+    state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_rec, e->n_nodes,
                                                                     d_nodes, d_ts, n, d_first, d_cnt, d_ids);
     CK(cudaGetLastError());
     if (!on_device) {
