@@ -113,6 +113,11 @@ int rca_close(rca_engine_t *e);
 const char *rca_last_error(const rca_engine_t *e);
 /* run the engine's work on this CUDA stream (cudaStream_t as an integer); 0 = its own stream */
 int rca_set_stream(rca_engine_t *e, uint64_t cuda_stream);
+/* Plans with at most `max_seeds` seeds run one fused launch per hop (fewest launches: the
+ * per-incident latency case); larger seed sets run count / scan / fill launches per hop (no
+ * inter-tile waiting: the throughput case).  Results are identical either way.  Default 16384.
+ * No counterpart in the reference: it is a tuning knob of this engine. */
+int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds);
 /* pre-size the scratch arenas: frontier entries (16 B each) and output words (4 B each) */
 int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words);
 

@@ -43,12 +43,17 @@ struct rca_engine {
     unsigned long long fcap = 0;
     int *out = nullptr;
     unsigned long long ocap = 0;
-    ulonglong2 *tstate = nullptr;         // tile-state words, tagged with `epoch`; zeroed when (re)allocated
+    ulonglong2 *tstate = nullptr;         // fused path: tile-state words, tagged with `epoch`; zeroed when (re)allocated
     unsigned long long tcap = 0;
     unsigned epoch = 0;
+    uint2 *tcount = nullptr;              // split path: per-tile counts
+    unsigned long long ccap = 0;
+    ulonglong2 *gsum = nullptr, *gscan = nullptr;   // split path: group sums (zeroed per call) and their scan
+    unsigned long long gcap = 0;
+    long long fused_max_seeds = 16384;    // up to this many seeds a plan runs one fused launch per level
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
-    int *ktab = nullptr, *h_ktab = nullptr;
+    unsigned char *ptab = nullptr, *h_ptab = nullptr;   // plan table (rca_kernels.cuh: kPt*)
     int *seeds_buf = nullptr;
     long long seeds_cap = 0;
     long long *ts_buf = nullptr;
@@ -160,8 +165,8 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
     }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
     OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
-    OCK(cudaMalloc((void **)&g->ktab, kKtabWords * sizeof(int)));
-    OCK(cudaMallocHost((void **)&g->h_ktab, kKtabWords * sizeof(int)));
+    OCK(cudaMalloc((void **)&g->ptab, kPtBytes));
+    OCK(cudaMallocHost((void **)&g->h_ptab, kPtBytes));
 #undef OCK
     *out = up.release();
     return RCA_OK;
@@ -172,11 +177,11 @@ extern "C" int rca_close(rca_engine_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_rec, e->frontier, e->out, e->tstate, e->ctl, e->ktab,
+                   e->st_off, e->st_rec, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
-    if (e->h_ktab) cudaFreeHost(e->h_ktab);
+    if (e->h_ptab) cudaFreeHost(e->h_ptab);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     for (auto ev : e->ev_lv) if (ev) cudaEventDestroy(ev);
@@ -275,11 +280,34 @@ static int validate_plan(rca_engine *e, const rca_plan_t *pl) {
 
 static int row_len_of(const rca_plan_t *pl, int s) { return pl->with_states ? 3 * s + 3 : 2 * s + 1; }
 
-template <typename K>
-static int max_grid(rca_engine *e, K kernel, size_t dyn_smem) {
+// ---- kernel dispatch: one instantiation per (adjacency format, predicate mode, known depth)
+typedef void (*level_kernel_t)(const LevelParams);
+struct KernelSet { level_kernel_t count, fill, fused; };
+template <bool ADJ2, int MODE, int QT>
+static KernelSet kernel_set() { return KernelSet{count_level<ADJ2, MODE, QT>, fill_level<ADJ2, MODE, QT>, fused_level<ADJ2, MODE, QT>}; }
+template <bool ADJ2>
+static KernelSet pick_kernels(int mode, int q) {
+    if (mode == kModeChain) return kernel_set<ADJ2, kModeChain, -1>();
+    if (mode == kModeRelUnique) return kernel_set<ADJ2, kModeRelUnique, -1>();
+    switch (q) {
+        case 0: return kernel_set<ADJ2, kModeSimple, 0>();
+        case 1: return kernel_set<ADJ2, kModeSimple, 1>();
+        case 2: return kernel_set<ADJ2, kModeSimple, 2>();
+        case 3: return kernel_set<ADJ2, kModeSimple, 3>();
+        default: return kernel_set<ADJ2, kModeSimple, -1>();
+    }
+}
+
+static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem) != cudaSuccess || per_sm < 1) per_sm = 1;
     return e->sm_count * per_sm;
+}
+
+extern "C" int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds) {
+    if (!e || max_seeds < 0) return RCA_ERR_ARG;
+    e->fused_max_seeds = max_seeds;
+    return RCA_OK;
 }
 
 extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *seeds, int64_t n_seeds,
@@ -294,6 +322,8 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     e->have_result = false;
     const bool varlen = pl->kind == RCA_PLAN_VARLEN;
     const int L = varlen ? pl->max_hops : pl->n_steps;
+    const int mode = !varlen ? kModeChain : (pl->node_simple ? kModeSimple : kModeRelUnique);
+    const bool fused = n_seeds <= e->fused_max_seeds;
 
     // ---- seeds (and their timestamps) on the device
     const int *d_seeds = seeds;
@@ -315,20 +345,30 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         }
     }
 
-    // ---- kind tables of this plan: kind_start (padded to 4) then attribute words
-    const int nkp = (e->n_kinds + 1 + 3) & ~3, nka = (e->n_kinds + 3) & ~3;
-    std::memset(e->h_ktab, 0, (size_t)(nkp + nka + kLutWords) * sizeof(int));
-    std::memcpy(e->h_ktab + nkp + nka, e->kind_lut.data(), kLutEntries);
-    for (int k = 0; k <= e->n_kinds; k++) e->h_ktab[k] = e->kind_start[k];
-    for (int k = e->n_kinds + 1; k < nkp; k++) e->h_ktab[k] = 0x7fffffff;
-    if (varlen) {
-        unsigned reach[RCA_MAX_KINDS];
-        reach_bits(e, pl, reach);
-        for (int k = 0; k < e->n_kinds; k++)
-            e->h_ktab[nkp + k] = (int)((pl->kind_excl[k] ? kAttrExcl : 0u) | (pl->kind_inter[k] ? kAttrInter : 0u) |
-                                       (reach[k] << kAttrReachShift));
+    // ---- plan table: kind boundaries, one kind-action row per level, node-block -> kind table
+    {
+        unsigned char *t = e->h_ptab;
+        std::memset(t, 0, kPtBytes);
+        int *ks = reinterpret_cast<int *>(t + kPtKs);
+        for (int k = 0; k < kKindPad; k++) ks[k] = k <= e->n_kinds ? e->kind_start[k] : 0x7fffffff;
+        if (varlen) {
+            unsigned reach[RCA_MAX_KINDS];
+            reach_bits(e, pl, reach);
+            for (int s = 0; s <= L; s++) {
+                unsigned char *row = t + kPtAct + s * RCA_MAX_KINDS;
+                for (int k = 0; k < e->n_kinds; k++) {
+                    const bool dead = pl->kind_excl[k] || (pl->pos_kind[s] >= 0 && pl->pos_kind[s] != k);
+                    unsigned a = dead ? kActDead : 0u;
+                    if (!dead && s < L && ((reach[k] >> (L - s - 1)) & 1u)) a |= kActCont;
+                    if (!dead && s >= pl->min_hops && (pl->dest_kind < 0 || pl->dest_kind == k)) a |= kActEmit;
+                    if (pl->kind_inter[k]) a |= kActInter;
+                    row[k] = (unsigned char)a;
+                }
+            }
+        }
+        std::memcpy(t + kPtLut, e->kind_lut.data(), kLutEntries);
+        CK(cudaMemcpyAsync(e->ptab, t, kPtBytes, cudaMemcpyHostToDevice, e->stream));
     }
-    CK(cudaMemcpyAsync(e->ktab, e->h_ktab, (size_t)(nkp + nka + kLutWords) * sizeof(int), cudaMemcpyHostToDevice, e->stream));
 
     // ---- scratch arenas: keep what earlier calls grew to, else a guess from the seed count
     if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * n_seeds, 1ull << 20)); if (rc) return rc; }
@@ -337,18 +377,34 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     int retries = 0, launches = 0;
     float ms = 0.f;
     while (true) {
-        const unsigned long long tneed = ((unsigned long long)n_seeds + e->fcap) / kTile + kLv + 2;
-        if (tneed > e->tcap || (++e->epoch & 0x3fffffffu) == 0) {     // new array or epoch wrapped: start from zeros
-            rc = grow(e, &e->tstate, &e->tcap, std::max(tneed, e->tcap));
+        // tile slots: one per 32 frontier entries, levels group-aligned with a group of slack each
+        const unsigned long long slots = ((unsigned long long)n_seeds + e->fcap) / kTile + (unsigned long long)kGroup * (kLv + 2);
+        const unsigned long long groups = slots / kGroup + kLv + 2;
+        if (fused) {
+            if (slots > e->tcap || (++e->epoch & 0x3fffffffu) == 0) {     // new array or epoch wrapped: start from zeros
+                rc = grow(e, &e->tstate, &e->tcap, std::max(slots, e->tcap));
+                if (rc) return rc;
+                CK(cudaMemsetAsync(e->tstate, 0, e->tcap * sizeof(ulonglong2), e->stream));
+                e->epoch = 1;
+            }
+        } else {
+            rc = grow(e, &e->tcount, &e->ccap, slots);
             if (rc) return rc;
-            CK(cudaMemsetAsync(e->tstate, 0, e->tcap * sizeof(ulonglong2), e->stream));
-            e->epoch = 1;
+            if (groups > e->gcap) {
+                unsigned long long c1 = e->gcap, c2 = e->gcap;
+                rc = grow(e, &e->gsum, &c1, groups);
+                if (rc) return rc;
+                rc = grow(e, &e->gscan, &c2, groups);
+                if (rc) return rc;
+                e->gcap = groups;
+            }
         }
         launches = 0;
         std::memset(e->h_ctl, 0, sizeof(Ctl));
         e->h_ctl->F[0] = (unsigned long long)n_seeds;
         CK(cudaEventRecord(e->ev0, e->stream));
         CK(cudaMemcpyAsync(e->ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+        if (!fused) CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
         CK(cudaEventRecord(e->ev_lv[0], e->stream));
         for (int s = 1; s <= L; s++) {
             LevelParams p;
@@ -372,36 +428,38 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             p.adj2 = dir == RCA_DIR_IN ? e->in_adj : e->und_adj;
             p.n_nodes = e->n_nodes;
             p.s = s;
-            p.varlen = varlen;
-            p.min_hops = varlen ? pl->min_hops : L;
-            p.max_hops = L;
-            p.node_simple = pl->node_simple; p.dest_kind = pl->dest_kind; p.has_inter = pl->has_inter;
-            p.pos_kind_prev = varlen ? pl->pos_kind[s - 1] : -1;
-            p.pos_kind_cur = varlen ? pl->pos_kind[s] : -1;
+            p.chain_flag = s < L ? 1 : 2;
+            p.need_inter = varlen && pl->has_inter;
             p.with_states = pl->with_states;
             p.row_len = row_len_of(pl, s);
+            for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
+            p.epoch = e->epoch;
+            p.lut_shift = e->lut_shift;
             p.seeds = d_seeds; p.seed_ts = d_ts;
             p.frontier = e->frontier; p.fcap = e->fcap;
             p.out = e->out; p.ocap = e->ocap;
             p.ctl = e->ctl; p.tstate = e->tstate;
-            p.ktab = e->ktab; p.n_kinds = e->n_kinds; p.nkp = nkp; p.nka = nka; p.lut_shift = e->lut_shift;
-            p.st_off = e->st_off; p.st_rec = e->st_rec; p.epoch = e->epoch;
-            int grid;
+            p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
+            p.ptab = e->ptab;
+            p.st_off = e->st_off; p.st_rec = e->st_rec;
+            const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
             const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
-            if (dir == RCA_DIR_OUT) {
-                if (varlen) { grid = max_grid(e, expand_level<false, true>, dyn); } else { grid = max_grid(e, expand_level<false, false>, dyn); }
+            const long long first = std::max<long long>(1, (n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
+            if (fused) {
+                int grid = max_grid(e, ks.fused, dyn);
+                if (s == 1) grid = (int)std::min<long long>(grid, first);
+                ks.fused<<<grid, kThreads, dyn, e->stream>>>(p);
+                launches++;
             } else {
-                if (varlen) { grid = max_grid(e, expand_level<true, true>, dyn); } else { grid = max_grid(e, expand_level<true, false>, dyn); }
+                int grid = max_grid(e, ks.count, dyn);
+                if (s == 1) grid = (int)std::min<long long>(grid, first);
+                ks.count<<<grid, kThreads, dyn, e->stream>>>(p);
+                scan_groups<<<1, 1024, 0, e->stream>>>(p);
+                grid = max_grid(e, ks.fill, dyn);
+                if (s == 1) grid = (int)std::min<long long>(grid, first);
+                ks.fill<<<grid, kThreads, dyn, e->stream>>>(p);
+                launches += 3;
             }
-            if (s == 1) grid = (int)std::min<long long>(grid, std::max<long long>(1, (n_seeds + kTile * kWarps - 1) / (kTile * kWarps)));
-            if (dir == RCA_DIR_OUT) {
-                if (varlen) expand_level<false, true><<<grid, kThreads, dyn, e->stream>>>(p);
-                else expand_level<false, false><<<grid, kThreads, dyn, e->stream>>>(p);
-            } else {
-                if (varlen) expand_level<true, true><<<grid, kThreads, dyn, e->stream>>>(p);
-                else expand_level<true, false><<<grid, kThreads, dyn, e->stream>>>(p);
-            }
-            launches++;
             CK(cudaGetLastError());
             CK(cudaEventRecord(e->ev_lv[s], e->stream));
         }
@@ -423,9 +481,11 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     e->res_levels = L;
     long long total = 0;
     for (int s = 0; s <= RCA_MAX_HOPS; s++) { e->res_rows[s] = 0; e->res_row_len[s] = row_len_of(pl, s); e->res_base[s] = 0; }
+    unsigned long long obase = 0;
     for (int s = 1; s <= L; s++) {
         e->res_rows[s] = (long long)e->h_ctl->N[s];
-        e->res_base[s] = e->h_ctl->obase[s];
+        e->res_base[s] = obase;
+        obase += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s);
         total += e->res_rows[s];
     }
     e->have_result = true;

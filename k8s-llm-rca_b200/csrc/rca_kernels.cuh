@@ -1,36 +1,39 @@
 // rca_kernels.cuh - sm_100a kernels of the path engine.
 //
-// One kernel does all the graph work: expand_level<> turns the frontier of partial paths at depth
-// s-1 into the frontier at depth s and, in the same pass, emits the finished path instances of
-// length s.  It replaces what Neo4j does for the reference's MATCH statements
-// (find_metapath/find_srckind_metapath_neo4j.py:95-129, generate_query/generate_query.py:241-260)
-// and, with `with_states`, the per-node state query of check_state/analyze_root_cause.py:70-79.
+// One step of a plan ("level s") turns the frontier of partial paths at depth s-1 into the
+// frontier at depth s and emits the finished path instances of length s.  It replaces what Neo4j
+// does for the reference's MATCH statements (find_metapath/find_srckind_metapath_neo4j.py:95-129,
+// generate_query/generate_query.py:241-260) and, with `with_states`, the per-node state query of
+// check_state/analyze_root_cause.py:70-79.
 //
-// Shape of one launch: persistent CTAs of 8 warps; every WARP works on its own tile of 32
-// frontier entries (tiles are handed out in index order through an atomic ticket, one at a time:
-// a tile claimed early but processed late would stall the look-back of every later tile), so
-// there is no block-wide barrier after the set-up.
-//   set-up    - one cp.async.bulk (TMA bulk copy) per CTA stages the plan's kind tables (kind
-//               boundaries, per-kind attribute word, node-block -> kind table) in shared memory.
-//   prologue  - lane l owns entry l of the tile: one 16 B load of the entry, one 8 B load of the
-//               adjacency range of its tail node, then the parent chain is walked to recover the
-//               nodes / relationships already on the path (into the warp's shared memory).
-//               Warp scan of the row lengths numbers the tile's candidates 0..C-1; entries without
-//               a row are compacted away.
-//   pass 1    - candidates are taken 32 at a time (a "window").  The owning entry of every lane's
-//               candidate comes from one shared-memory load, one warp OR-reduction and a popcount
-//               (entry starts inside the window form a bit mask) - no per-candidate search.  One
-//               coalesced 4 B / 8 B adjacency load per lane, then the path predicates against
-//               shared memory.  Survivor ballots (continue / emit) are cached per window.
-//   look-back - the tile publishes its two counts in one 128-bit word and obtains the exclusive
-//               prefix over all earlier tiles (decoupled look-back, all 32 lanes polling 32
-//               predecessors).  Tile order is fixed, so every survivor's slot is a pure function
-//               of the input: deterministic output with no sort and no global scan kernel.  Words
-//               carry the call's epoch, so the state array is never cleared between calls.
-//   pass 2    - windows without survivors are skipped from the cached ballots.  Continuing
-//               survivors write their 16 B frontier entry (tail, parent, rel, aux).  Emitting
-//               survivors are queued in shared memory and written 32 rows at a time with every
-//               lane busy: row = nodes, rels [, one HasState probe per node, missing-state mask].
+// Work decomposition (all variants): every WARP owns a tile of 32 frontier entries.
+//   prologue  - lane l owns entry l: one 16 B load of the entry, one 8 B load of the adjacency
+//               range of its tail node, then the parent chain is walked to recover the nodes /
+//               relationships already on the path (into the warp's shared memory).  A warp scan of
+//               the row lengths numbers the tile's candidates 0..C-1 (so hub rows spread over all
+//               lanes); entries without a row are compacted away.
+//   windows   - candidates are taken 32 at a time.  The owning entry of every lane's candidate
+//               comes from one shared-memory load, one warp OR-reduction and a popcount (entry
+//               starts inside the window form a bit mask) - no per-candidate search.  Then one
+//               coalesced 4 B / 8 B adjacency load per lane and the path predicates: visited test
+//               against shared memory, node -> kind through a block table, and one byte of the
+//               per-level kind-action table (continue / emit / interior / dead) that the host
+//               derived from the plan.  Kind tables reach shared memory by cp.async.bulk (TMA).
+//   slots     - survivors are ranked with ballots/popcounts inside the tile; the tile's base comes
+//               from a prefix over tiles in index order, so every survivor's slot is a pure
+//               function of the input: deterministic output, no sort.
+//   writes    - continuing survivors write a 16 B frontier entry (tail, parent, rel, aux);
+//               emitting survivors are queued in shared memory and written 32 rows at a time with
+//               every lane busy: row = nodes, rels [, one HasState probe per node, missing mask].
+//
+// Two ways to get the tile prefix:
+//   split (large frontiers): count_level -> scan_groups -> fill_level.  count_level stores per-tile
+//     counts and adds them into group sums (32 tiles per group); scan_groups (one CTA) scans the
+//     group sums and publishes the level totals; fill_level re-walks the tile and writes, its base
+//     = group prefix + a warp reduction over the counts of the earlier tiles of its group.  No
+//     inter-tile waiting anywhere.
+//   fused (small seed sets, where launches dominate): fused_level does count, decoupled look-back
+//     over 128-bit epoch-tagged tile states, and fill in one launch.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -42,17 +45,28 @@ namespace rca {
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kTile = 32;             // frontier entries per tile (one warp)
+constexpr int kGroup = 32;            // tiles per group (split path)
 constexpr int kLv = RCA_MAX_HOPS + 2;
-constexpr int kLutEntries = 1024;     // node id block -> kind of its first id
-constexpr int kLutWords = kLutEntries / 4;
-constexpr int kKtabWords = RCA_MAX_KINDS + 4 + RCA_MAX_KINDS + kLutWords;
-constexpr int kFlagWin = 64;          // windows per tile whose pass-1 ballots are cached
 constexpr int kQueue = 64;            // emission queue entries per warp
+#ifndef RCA_MINB
+#define RCA_MINB 6
+#endif
 
-// kind attribute word of a plan
-constexpr unsigned kAttrExcl = 1u;
-constexpr unsigned kAttrInter = 2u;
-constexpr int kAttrReachShift = 8;    // bit (8 + r - 1): dest kind reachable within <= r hops
+// plan table in device memory, staged into shared memory per CTA (all offsets multiples of 16 B)
+constexpr int kKindPad = RCA_MAX_KINDS + 4;                                   // kind_start ints, INT_MAX padded
+constexpr int kLutEntries = 4096;                                             // node id block -> kind of its first id
+constexpr int kPtKs = 0;
+constexpr int kPtAct = kPtKs + 4 * kKindPad;                                  // (RCA_MAX_HOPS+1) rows of RCA_MAX_KINDS bytes
+constexpr int kPtLut = kPtAct + (RCA_MAX_HOPS + 1) * RCA_MAX_KINDS;
+constexpr int kPtBytes = kPtLut + kLutEntries;
+
+// kind-action byte of one (level, kind)
+constexpr unsigned kActCont = 1u;     // a path may continue through a node of this kind at this level
+constexpr unsigned kActEmit = 2u;     // a path ending at a node of this kind at this level is a result
+constexpr unsigned kActInter = 4u;    // kind is one of $intermediateKinds
+constexpr unsigned kActDead = 8u;     // kind may not appear at this position at all
+
+constexpr int kModeChain = 0, kModeSimple = 1, kModeRelUnique = 2;
 
 struct StRec {                        // one HasState interval: exactly one 32 B sector
     long long tmin, tmax;
@@ -61,12 +75,10 @@ struct StRec {                        // one HasState interval: exactly one 32 B
 };
 
 struct Ctl {                          // device control block, one per engine
-    unsigned long long F[kLv];        // frontier size per level
-    unsigned long long fbase[kLv];    // first frontier entry of the level in the arena
-    unsigned long long N[kLv];        // rows emitted per level
-    unsigned long long obase[kLv];    // first output word of the level in the arena
+    unsigned long long F[kLv];        // frontier size per level (level s occupies arena entries sum F[1..s-1] ..)
+    unsigned long long N[kLv];        // rows emitted per level  (level s occupies output words sum N[j]*row_len[j] ..)
     unsigned long long E[kLv];        // candidates scanned per level
-    unsigned int ticket[kLv];
+    unsigned int ticket[kLv];         // fused path: tile tickets
     unsigned int overflow;            // bit0 frontier arena, bit1 output arena
     unsigned int pad;
 };
@@ -82,13 +94,13 @@ struct LevelParams {
     int n_nodes;
     // plan
     int s;                            // level being produced (1..)
-    int varlen;
-    int min_hops, max_hops;           // chain: both == n_steps
-    int node_simple, dest_kind, has_inter;
-    int pos_kind_prev, pos_kind_cur;  // required kind at positions s-1 (seeds only) and s; -1 any
+    int chain_flag;                   // chain plans: 1 = every candidate continues, 2 = every candidate is a row
+    int need_inter;                   // emit only if an interior node so far is of an intermediate kind
     int with_states;
     int row_len;                      // words per emitted row at this level
-    unsigned epoch;                   // tag of this call's tile-state words (never 0)
+    int row_len_lv[RCA_MAX_HOPS + 1]; // ... and at every level (arena bases are sums over earlier levels)
+    unsigned epoch;                   // fused path: tag of this call's tile-state words (never 0)
+    int lut_shift;
     // per-call buffers
     const int *seeds;
     const long long *seed_ts;
@@ -97,9 +109,11 @@ struct LevelParams {
     int *out;
     unsigned long long ocap;
     Ctl *ctl;
-    ulonglong2 *tstate;
-    const int *ktab;                  // [nkp] kind_start (padded), [nka] attribute words, [kLutWords] block->kind
-    int n_kinds, nkp, nka, lut_shift;
+    ulonglong2 *tstate;               // fused path: tile states
+    uint2 *tcount;                    // split path: (continue, emit) counts per tile slot
+    ulonglong2 *gsum;                 // split path: sums per group of 32 tile slots (zeroed per call)
+    ulonglong2 *gscan;                // split path: exclusive prefix of gsum within the level
+    const unsigned char *ptab;        // plan table (layout above)
     // HasState intervals
     const int *st_off;
     const StRec *st_rec;
@@ -144,11 +158,42 @@ __device__ __forceinline__ void st_state(ulonglong2 *p, unsigned long long x, un
     asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" :: "l"(p), "l"(x), "l"(y) : "memory");
 }
 
+// Shared-memory copies of the plan tables of one launch.
+struct Tables {
+    const int *ks;                    // kind_start, INT_MAX padded
+    const unsigned char *act_q;       // kind-action row of level s-1 (seed checks)
+    const unsigned char *act_s;       // kind-action row of level s
+    const unsigned char *lut;
+    int lut_shift;
+};
+struct TablesSm {
+    alignas(16) int ks[kKindPad];
+    alignas(16) unsigned char act[2 * RCA_MAX_KINDS];
+    alignas(16) unsigned char lut[kLutEntries];
+    alignas(8) unsigned long long bar;
+};
+
+// One elected thread starts the three bulk copies; everybody waits on the mbarrier after a CTA sync.
+__device__ __forceinline__ Tables stage_tables(TablesSm &sm, const LevelParams &p) {
+    if (threadIdx.x == 0) {
+        mbar_init(&sm.bar, 1);
+        mbar_expect_tx(&sm.bar, 4 * kKindPad + 2 * RCA_MAX_KINDS + kLutEntries);
+        bulk_g2s(sm.ks, p.ptab + kPtKs, 4 * kKindPad, &sm.bar);
+        bulk_g2s(sm.act, p.ptab + kPtAct + (p.s - 1) * RCA_MAX_KINDS, 2 * RCA_MAX_KINDS, &sm.bar);
+        bulk_g2s(sm.lut, p.ptab + kPtLut, kLutEntries, &sm.bar);
+    }
+    __syncthreads();
+    mbar_wait(&sm.bar, 0);
+    Tables t;
+    t.ks = sm.ks; t.act_q = sm.act; t.act_s = sm.act + RCA_MAX_KINDS; t.lut = sm.lut; t.lut_shift = p.lut_shift;
+    return t;
+}
+
 // kind of node v through the block table: lut[v >> sh] is the kind of the first id of v's block,
-// then walk up while the next kind starts at or before v (kind_start is padded with INT_MAX)
-__device__ __forceinline__ int kind_lut(const int *ks, const unsigned char *lut, int sh, int v) {
-    int k = lut[v >> sh];
-    while (ks[k + 1] <= v) k++;
+// then walk up while the next kind starts at or before v
+__device__ __forceinline__ int kind_lut(const Tables &T, int v) {
+    int k = T.lut[v >> T.lut_shift];
+    while (T.ks[k + 1] <= v) k++;
     return k;
 }
 
@@ -167,6 +212,373 @@ __device__ __forceinline__ void state_probe(const int *st_off, const StRec *rec,
         }
     }
 }
+
+// ------------------------------------------------------------------------------------------------
+// Per-warp shared memory (carved from dynamic shared memory): this struct, then 2*s rows of 32 ints
+// (nodes and relationships already on each path of the tile).
+struct WarpSm {
+    int coff[kTile + 34];             // first candidate of each compacted entry, then C, then INT_MAX
+    int crow[kTile];                  // adjacency slot of a candidate = crow[o] + c
+    int cidx[kTile];                  // lane (entry index within the tile) of compacted entry o
+    int aux[kTile];                   // kind | interior-flag << 16 of the entry's tail
+    int root[kTile];                  // seed index of the path
+    int q_o[kQueue], q_v[kQueue], q_r[kQueue];
+};
+__host__ __device__ constexpr int warp_smem_ints(int s) { return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile; }
+
+struct Warp {                         // a warp's view of its tile
+    WarpSm *W;
+    int *anc_n, *anc_r;
+    int lane;
+    unsigned lt;
+};
+
+// Prologue of one tile; returns the number of candidates C.
+template <int MODE>
+__device__ __forceinline__ int tile_prologue(const LevelParams &p, const Tables &T, const Warp &w, unsigned tile,
+                                             unsigned long long Fq, const unsigned long long *fb) {
+    const int s = p.s, q = s - 1, lane = w.lane;
+    WarpSm &W = *w.W;
+    const unsigned long long i = (unsigned long long)tile * kTile + lane;
+    int deg = 0, beg = 0, tail = 0, par = 0, rel = 0, aux = 0;
+    if (i < Fq) {
+        bool live = true;
+        if (q == 0) {
+            tail = __ldg(p.seeds + i);
+            par = (int)i;
+            live = tail >= 0 && tail < p.n_nodes;
+            if (live && MODE != kModeChain) {
+                const int k = kind_lut(T, tail);
+                aux = k;
+                live = !(T.act_q[k] & kActDead);
+            }
+        } else {
+            const int4 e = p.frontier[fb[q] + i];
+            tail = e.x; par = e.y; rel = e.z; aux = e.w;
+        }
+        if (live) {
+            if (p.typed) {
+                if (tail >= p.row_lo && tail < p.row_hi) {
+                    const int2 rg = __ldg(p.rng + (tail - p.row_lo));
+                    beg = rg.x; deg = rg.y - rg.x;
+                }
+            } else {
+                const int2 rg = __ldg(p.rng + tail);
+                beg = rg.x;
+                deg = (p.entity_only ? rg.y : __ldg(p.rng + tail + 1).x) - rg.x;
+            }
+        }
+    }
+    int incl = deg;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    const int C = __shfl_sync(0xffffffffu, incl, 31);
+    const unsigned nzmask = __ballot_sync(0xffffffffu, deg > 0);
+    const int nz = __popc(nzmask);
+    __syncwarp();                                     // the previous tile's readers are done
+    if (deg > 0) {
+        const int o = __popc(nzmask & w.lt), off = incl - deg;
+        W.coff[o] = off;
+        W.crow[o] = beg - off;
+        W.cidx[o] = lane;
+        W.aux[o] = aux;
+        w.anc_n[q * kTile + o] = tail;
+        if (q > 0) {
+            w.anc_r[q * kTile + o] = rel;
+            for (int d = q - 1; d >= 1; d--) {
+                const int4 a = p.frontier[fb[d] + (unsigned)par];
+                w.anc_n[d * kTile + o] = a.x;
+                w.anc_r[d * kTile + o] = a.z;
+                par = a.y;
+            }
+            w.anc_n[o] = __ldg(p.seeds + par);
+        }
+        W.root[o] = par;
+    }
+    W.coff[nz + lane] = (lane == 0) ? C : 0x7fffffff;            // coff[nz] = C, then sentinels
+    if (lane < 2) W.coff[nz + 32 + lane] = 0x7fffffff;
+    __syncwarp();
+    return C;
+}
+
+// owner of every lane's candidate in window `it`, given the owner jlo of the candidate just
+// before the window: count the entry starts at or before the lane's candidate
+__device__ __forceinline__ int window_owner(const WarpSm &W, int it, int &jlo, int lane) {
+    const unsigned d = (unsigned)(W.coff[jlo + 1 + lane] - (it << 5));
+    const unsigned mask = __reduce_or_sync(0xffffffffu, d < 32u ? (1u << d) : 0u);
+    const int o = jlo + __popc(mask & (0xffffffffu >> (31 - lane)));
+    jlo += __popc(mask);
+    return o;
+}
+
+// Classify the lane's candidate of window `it`: bit0 continue, bit1 emit.
+// QT: number of earlier path nodes minus one when known at compile time (0..3), else -1.
+template <bool ADJ2, int MODE, int QT>
+__device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, const Warp &w, int o, int c, int C,
+                                        int &v, int &r, int &na) {
+    v = 0; r = 0; na = 0;
+    if (c >= C) return 0;
+    const int slot = w.W->crow[o] + c;
+    if (ADJ2) {
+        const int2 a = __ldg(p.adj2 + slot);
+        v = a.x; r = a.y;
+    } else {
+        v = __ldg(p.adj1 + slot);
+        r = slot;
+    }
+    if (MODE == kModeChain) return p.chain_flag;
+    bool dead = false;
+    if (MODE == kModeSimple) {
+        if (QT >= 0) {
+#pragma unroll
+            for (int d = 0; d <= QT; d++) dead |= (w.anc_n[d * kTile + o] == v);
+        } else {
+            for (int d = 0; d < p.s; d++) dead |= (w.anc_n[d * kTile + o] == v);
+        }
+    } else {
+        for (int d = 1; d < p.s; d++) dead |= (w.anc_r[d * kTile + o] == r);
+    }
+    if (dead) return 0;
+    const int k = kind_lut(T, v);
+    const unsigned a = T.act_s[k];
+    const int inter = w.W->aux[o] >> 16;
+    na = k | ((inter | (int)((a >> 2) & 1u)) << 16);
+    return (int)(a & kActCont) | (((a & kActEmit) && (!p.need_inter || inter)) ? 2 : 0);
+}
+
+// Emit queue entries 0..n-1 as rows run_e .. run_e+n-1 (one row per lane).
+__device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, int n, unsigned long long ob_s,
+                                           unsigned long long run_e) {
+    const int s = p.s, q = s - 1;
+    if (w.lane < n) {
+        const WarpSm &W = *w.W;
+        const int o = W.q_o[w.lane], v = W.q_v[w.lane], r = W.q_r[w.lane];
+        const unsigned long long w0 = ob_s + (run_e + w.lane) * (unsigned long long)p.row_len;
+        if (w0 + p.row_len <= p.ocap) {
+            int *row = p.out + w0;
+            for (int d = 0; d <= q; d++) row[d] = w.anc_n[d * kTile + o];
+            row[s] = v;
+            for (int d = 1; d <= q; d++) row[s + d] = w.anc_r[d * kTile + o];
+            row[2 * s] = r;
+            if (p.with_states) {
+                const long long ts = __ldg(p.seed_ts + W.root[o]);
+                unsigned miss = 0;
+                for (int d = 0; d <= s; d++) {
+                    int first, cnt;
+                    const int nd = (d <= q) ? w.anc_n[d * kTile + o] : v;
+                    state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
+                    row[2 * s + 1 + d] = first;
+                    miss |= (cnt == 0 ? 1u : 0u) << d;
+                }
+                row[3 * s + 2] = (int)miss;
+            }
+        }
+    }
+}
+
+// Walk the tile's windows, classify, and write the survivors starting at the tile's bases.
+template <bool ADJ2, int MODE, int QT>
+__device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T, const Warp &w, unsigned tile, int C,
+                                          unsigned long long fb_s, unsigned long long ob_s,
+                                          unsigned long long run_f, unsigned long long run_e) {
+    WarpSm &W = *w.W;
+    const int lane = w.lane;
+    const int n_it = (C + 31) >> 5;
+    int jlo = 0, qn = 0;
+    for (int it = 0; it < n_it; ++it) {
+        const int o = window_owner(W, it, jlo, lane);
+        int v, r, na;
+        const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + lane, C, v, r, na);
+        const unsigned bf = __ballot_sync(0xffffffffu, fl & 1), be = __ballot_sync(0xffffffffu, fl & 2);
+        if (fl & 1) {
+            const unsigned long long pos = fb_s + run_f + __popc(bf & w.lt);
+            if (pos < p.fcap) p.frontier[pos] = make_int4(v, (int)(tile * kTile + W.cidx[o]), r, na);
+        }
+        run_f += __popc(bf);
+        if (be) {                                     // rows are queued and written 32 at a time
+            if (fl & 2) {
+                const int k = qn + __popc(be & w.lt);
+                W.q_o[k] = o; W.q_v[k] = v; W.q_r[k] = r;
+            }
+            qn += __popc(be);
+            __syncwarp();
+            if (qn >= 32) {
+                flush_rows(p, w, 32, ob_s, run_e);
+                run_e += 32;
+                __syncwarp();
+                const int rest = qn - 32;
+                int to = 0, tv = 0, tr = 0;
+                if (lane < rest) { to = W.q_o[32 + lane]; tv = W.q_v[32 + lane]; tr = W.q_r[32 + lane]; }
+                __syncwarp();
+                if (lane < rest) { W.q_o[lane] = to; W.q_v[lane] = tv; W.q_r[lane] = tr; }
+                qn = rest;
+                __syncwarp();
+            }
+        }
+    }
+    if (qn) flush_rows(p, w, qn, ob_s, run_e);
+}
+
+// Walk the tile's windows and count the survivors.
+template <bool ADJ2, int MODE, int QT>
+__device__ __forceinline__ void tile_count(const LevelParams &p, const Tables &T, const Warp &w, int C, int &cf,
+                                           int &ce) {
+    const int n_it = (C + 31) >> 5;
+    int jlo = 0;
+    cf = 0; ce = 0;
+    for (int it = 0; it < n_it; ++it) {
+        const int o = window_owner(*w.W, it, jlo, w.lane);
+        int v, r, na;
+        const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + w.lane, C, v, r, na);
+        cf += __popc(__ballot_sync(0xffffffffu, fl & 1));
+        ce += __popc(__ballot_sync(0xffffffffu, fl & 2));
+    }
+}
+
+// CTA-uniform read of the overflow flag (it can be raised while a fused launch is running, so
+// every thread must act on the same value before the first CTA barrier)
+__device__ __forceinline__ bool overflow_seen(const Ctl *ctl) {
+    __shared__ unsigned s_ov;
+    if (threadIdx.x == 0) s_ov = *reinterpret_cast<const volatile unsigned *>(&ctl->overflow);
+    __syncthreads();
+    return s_ov != 0;
+}
+
+// Common set-up of the three level kernels: tables, per-warp shared memory, arena bases.
+struct LevelCtx {
+    Tables T;
+    Warp w;
+    unsigned long long Fq, fb_s, ob_s;
+    unsigned ntiles;
+    unsigned long long slot0;         // first tile slot of this level (multiple of kGroup)
+};
+__device__ __forceinline__ LevelCtx level_setup(const LevelParams &p, TablesSm &tsm, unsigned long long *s_fb,
+                                                int *s_dyn) {
+    LevelCtx c;
+    const int tid = threadIdx.x, s = p.s, q = s - 1;
+    Ctl *ctl = p.ctl;
+    if (tid < kLv) {                                  // arena base of every level below s, from the totals so far
+        unsigned long long fb = 0;
+        for (int j = 1; j < tid && j < s; j++) fb += ctl->F[j];
+        s_fb[tid] = fb;
+    }
+    c.T = stage_tables(tsm, p);                       // contains the CTA barrier that also publishes s_fb
+    c.w.lane = tid & 31;
+    c.w.lt = (1u << c.w.lane) - 1u;
+    c.w.W = reinterpret_cast<WarpSm *>(s_dyn + (tid >> 5) * warp_smem_ints(s));
+    c.w.anc_n = reinterpret_cast<int *>(c.w.W + 1);
+    c.w.anc_r = c.w.anc_n + s * kTile;
+    unsigned long long fb_s = 0, ob_s = 0;
+    for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
+    c.fb_s = fb_s; c.ob_s = ob_s;
+    c.Fq = ctl->F[q];
+    c.ntiles = (unsigned)((c.Fq + kTile - 1) / kTile);
+    // tile slots: levels are laid out by cumulative entry count, rounded up to a group, plus one
+    // group of slack per level, so the slot ranges of different levels never overlap
+    const unsigned long long vpos = (q == 0) ? 0ull : ctl->F[0] + (fb_s - ctl->F[q]);
+    c.slot0 = ((vpos / kTile + kGroup - 1) / kGroup + (unsigned long long)q) * kGroup;
+    return c;
+}
+
+// ------------------------------------------------------------------------------------------------
+// split path, step 1: per-tile survivor counts, added into the group sums
+template <bool ADJ2, int MODE, int QT>
+__global__ void __launch_bounds__(kThreads, RCA_MINB) count_level(const __grid_constant__ LevelParams p) {
+    extern __shared__ int s_dyn[];
+    __shared__ TablesSm tsm;
+    __shared__ unsigned long long s_fb[kLv];
+    if (overflow_seen(p.ctl)) return;
+    const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
+    unsigned long long scanned = 0;
+    const unsigned nwarps = gridDim.x * kWarps;
+    for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
+        const int C = tile_prologue<MODE>(p, c.T, c.w, tile, c.Fq, s_fb);
+        scanned += (unsigned long long)C;
+        int cf, ce;
+        tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce);
+        if (c.w.lane == 0) {
+            const unsigned long long slot = c.slot0 + tile;
+            p.tcount[slot] = make_uint2((unsigned)cf, (unsigned)ce);
+            if (cf) atomicAdd(&p.gsum[slot / kGroup].x, (unsigned long long)cf);
+            if (ce) atomicAdd(&p.gsum[slot / kGroup].y, (unsigned long long)ce);
+        }
+    }
+    if (c.w.lane == 0 && scanned) atomicAdd(&p.ctl->E[p.s], scanned);
+}
+
+// split path, step 2 (one CTA): exclusive scan of the group sums, level totals, overflow check
+__global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ LevelParams p) {
+    __shared__ unsigned long long s_w[2][32];
+    __shared__ unsigned long long s_run[2];
+    Ctl *ctl = p.ctl;
+    if (ctl->overflow) return;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, s = p.s, q = s - 1;
+    unsigned long long fb_s = 0, ob_s = 0;
+    for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
+    const unsigned long long Fq = ctl->F[q];
+    const unsigned long long ntiles = (Fq + kTile - 1) / kTile;
+    const unsigned long long vpos = (q == 0) ? 0ull : ctl->F[0] + (fb_s - ctl->F[q]);
+    const unsigned long long g0 = (vpos / kTile + kGroup - 1) / kGroup + (unsigned long long)q;
+    const unsigned long long ng = (ntiles + kGroup - 1) / kGroup;
+    if (tid == 0) { s_run[0] = 0; s_run[1] = 0; }
+    __syncthreads();
+    for (unsigned long long base = 0; base < ng; base += 1024) {
+        const unsigned long long g = base + tid;
+        ulonglong2 v = make_ulonglong2(0, 0);
+        if (g < ng) v = p.gsum[g0 + g];
+        unsigned long long a = v.x, b = v.y;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long na = __shfl_up_sync(0xffffffffu, a, o), nb = __shfl_up_sync(0xffffffffu, b, o);
+            if (lane >= o) { a += na; b += nb; }
+        }
+        if (lane == 31) { s_w[0][wid] = a; s_w[1][wid] = b; }
+        __syncthreads();
+        unsigned long long wa = s_run[0], wb = s_run[1];
+        for (int k = 0; k < wid; k++) { wa += s_w[0][k]; wb += s_w[1][k]; }
+        if (g < ng) p.gscan[g0 + g] = make_ulonglong2(wa + a - v.x, wb + b - v.y);
+        __syncthreads();
+        if (tid == 1023) { s_run[0] = wa + a; s_run[1] = wb + b; }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        ctl->F[s] = s_run[0];
+        ctl->N[s] = s_run[1];
+        unsigned ov = 0;
+        if (fb_s + s_run[0] > p.fcap) ov |= 1u;
+        if (ob_s + s_run[1] * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
+        if (ov) ctl->overflow = ov;
+    }
+}
+
+// split path, step 3: re-walk every tile and write its survivors at (group prefix + in-group prefix)
+template <bool ADJ2, int MODE, int QT>
+__global__ void __launch_bounds__(kThreads, RCA_MINB) fill_level(const __grid_constant__ LevelParams p) {
+    extern __shared__ int s_dyn[];
+    __shared__ TablesSm tsm;
+    __shared__ unsigned long long s_fb[kLv];
+    if (overflow_seen(p.ctl)) return;
+    const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
+    const unsigned nwarps = gridDim.x * kWarps;
+    for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
+        const unsigned long long slot = c.slot0 + tile, g = slot / kGroup;
+        const unsigned in_g = (unsigned)(slot % kGroup);
+        // counts of the earlier tiles of the group (slot0 is group-aligned, so they belong to this level)
+        uint2 mine = make_uint2(0, 0);
+        if ((unsigned)c.w.lane < in_g) mine = p.tcount[g * kGroup + c.w.lane];
+        const ulonglong2 gp = p.gscan[g];
+        const unsigned long long run_f = gp.x + __reduce_add_sync(0xffffffffu, mine.x);
+        const unsigned long long run_e = gp.y + __reduce_add_sync(0xffffffffu, mine.y);
+        const int C = tile_prologue<MODE>(p, c.T, c.w, tile, c.Fq, s_fb);
+        tile_fill<ADJ2, MODE, QT>(p, c.T, c.w, tile, C, c.fb_s, c.ob_s, run_f, run_e);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused path: count, decoupled look-back, fill in one launch (small seed sets)
 
 // tile-state word: x = status:2 | epoch:30 | f:32 (continuing entries), y = e (emitted rows)
 constexpr unsigned kStAgg = 1u, kStPre = 2u;
@@ -187,30 +599,31 @@ __device__ __forceinline__ void tile_lookback(ulonglong2 *ts, unsigned tile, uns
     if (lane == 0) st_state(ts + tile, st_pack(kStAgg, epoch, agg_f), agg_e);
     unsigned long long run_f = 0, run_e = 0;
     int base = (int)tile - 1;
+    const unsigned ep = epoch & 0x3fffffffu;
     while (true) {
         const int t = base - (int)lane;
         unsigned status = kStPre;                           // virtual zero prefix before tile 0
         unsigned long long f = 0, e = 0;
         if (t >= 0) {
-            ulonglong2 w;
-            do {
-                w = ld_state(ts + t);
+            while (true) {
+                const ulonglong2 w = ld_state(ts + t);
                 status = (unsigned)(w.x >> 62);
-            } while (status == 0 || ((unsigned)(w.x >> 32) & 0x3fffffffu) != (epoch & 0x3fffffffu));
-            f = w.x & 0xffffffffull;
-            e = w.y;
+                if (status != 0 && ((unsigned)(w.x >> 32) & 0x3fffffffu) == ep) { f = w.x & 0xffffffffull; e = w.y; break; }
+                __nanosleep(64);                            // not published yet
+            }
         }
+        // lanes nearer than the first published prefix hold tile aggregates (each far below 2^32,
+        // so 32-bit warp adds are exact); that prefix itself is 64-bit and comes by broadcast
         const unsigned m = __ballot_sync(0xffffffffu, status == kStPre);
         const int first = m ? (__ffs(m) - 1) : 32;
-        if ((int)lane > first) { f = 0; e = 0; }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            f += __shfl_xor_sync(0xffffffffu, f, o);
-            e += __shfl_xor_sync(0xffffffffu, e, o);
+        const bool is_agg = (int)lane < first;
+        run_f += __reduce_add_sync(0xffffffffu, is_agg ? (unsigned)f : 0u);
+        run_e += __reduce_add_sync(0xffffffffu, is_agg ? (unsigned)e : 0u);
+        if (m) {
+            run_f += __shfl_sync(0xffffffffu, f, first);
+            run_e += __shfl_sync(0xffffffffu, e, first);
+            break;
         }
-        run_f += f;
-        run_e += e;
-        if (m) break;
         base -= 32;
     }
     pre_f = run_f;
@@ -218,310 +631,43 @@ __device__ __forceinline__ void tile_lookback(ulonglong2 *ts, unsigned tile, uns
     if (lane == 0) st_state(ts + tile, st_pack(kStPre, epoch, run_f + agg_f), run_e + agg_e);
 }
 
-// ------------------------------------------------------------------------------------------------
-// Per-warp shared memory (carved from dynamic shared memory): fixed part, then 2*s rows of 32 ints.
-struct WarpSm {
-    int coff[kTile + 34];             // first candidate of each compacted entry, then C, then INT_MAX
-    int crow[kTile];                  // adjacency slot of a candidate = crow[o] + c
-    int cidx[kTile];                  // lane (entry index within the tile) of compacted entry o
-    int aux[kTile];
-    int root[kTile];                  // seed index of the path
-    unsigned flag[3][kFlagWin];       // per window: continue bits, emit bits, owner before the window
-    int q_o[kQueue], q_v[kQueue], q_r[kQueue];
-};
-__host__ __device__ constexpr int warp_smem_ints(int s) { return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile; }
-
-// Everything one candidate needs to know about the plan at this level.
-struct EvalCtx {
-    const int *ks;
-    const unsigned *kattr;
-    const unsigned char *lut;
-    const int *anc_n, *anc_r;         // [s][kTile] each, in the warp's shared memory
-    const int *aux;
-    int lut_shift, s, q, min_hops, max_hops, node_simple, dest_kind, has_inter, pos_kind_cur;
-};
-
-// flags: bit0 continue, bit1 emit.  o = compacted owner entry, (v, r) = neighbour and relationship.
-template <bool VARLEN>
-__device__ __forceinline__ int eval_candidate(const EvalCtx &x, int o, int v, int r, int &naux) {
-    naux = 0;
-    if (!VARLEN) return (x.s < x.max_hops) ? 1 : 2;
-    bool dead = false;
-    if (x.node_simple) {
-        for (int d = 0; d <= x.q; d++) dead |= (x.anc_n[d * kTile + o] == v);
-    } else {
-        for (int d = 1; d <= x.q; d++) dead |= (x.anc_r[d * kTile + o] == r);
-    }
-    if (dead) return 0;
-    const int k = kind_lut(x.ks, x.lut, x.lut_shift, v);
-    const unsigned at = x.kattr[k];
-    if ((at & kAttrExcl) || (x.pos_kind_cur >= 0 && x.pos_kind_cur != k)) return 0;
-    const int inter_so_far = x.aux[o] >> 16;
-    naux = k | ((inter_so_far | ((at & kAttrInter) ? 1 : 0)) << 16);
-    int fl = 0;
-    if (x.s >= x.min_hops && (x.dest_kind < 0 || k == x.dest_kind) && (!x.has_inter || inter_so_far)) fl |= 2;
-    if (x.s < x.max_hops && ((at >> (kAttrReachShift + x.max_hops - x.s - 1)) & 1u)) fl |= 1;
-    return fl;
-}
-
-// ADJ2: adjacency entries are (neighbour, rel) pairs (in / undirected tables); otherwise 4-byte
-// out_dst entries whose slot is the relationship id.   VARLEN: variable-length plan predicates.
-// Dynamic shared memory: kWarps * warp_smem_ints(s) ints.
-template <bool ADJ2, bool VARLEN>
-__global__ void __launch_bounds__(kThreads) expand_level(const __grid_constant__ LevelParams p) {
+template <bool ADJ2, int MODE, int QT>
+__global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_constant__ LevelParams p) {
     extern __shared__ int s_dyn[];
-    __shared__ alignas(16) int s_ktab[kKtabWords];
-    __shared__ alignas(8) unsigned long long s_bar;
+    __shared__ TablesSm tsm;
     __shared__ unsigned long long s_fb[kLv];
-
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const unsigned lt = (1u << lane) - 1u;
-    const int s = p.s, q = s - 1;
     Ctl *ctl = p.ctl;
     // an arena overflowed at an earlier level: entries past its end were never written, the host
     // will grow the arena and run the plan again (checked before any ticket is taken)
-    if (ctl->overflow) return;
-
-    // ---- set-up: stage the plan's kind tables with one TMA bulk copy; read level bases meanwhile
-    const unsigned ktab_bytes = (unsigned)(p.nkp + p.nka + kLutWords) * 4u;
-    if (tid == 0) {
-        mbar_init(&s_bar, 1);
-        mbar_expect_tx(&s_bar, ktab_bytes);
-        bulk_g2s(s_ktab, p.ktab, ktab_bytes, &s_bar);
-    }
-    if (tid < kLv) s_fb[tid] = ctl->fbase[tid];
-    WarpSm &W = *reinterpret_cast<WarpSm *>(s_dyn + wid * warp_smem_ints(s));
-    int *anc_n = reinterpret_cast<int *>(&W + 1), *anc_r = anc_n + s * kTile;
-    const unsigned long long Fq = ctl->F[q];
-    const unsigned ntiles = (unsigned)((Fq + kTile - 1) / kTile);
-    const unsigned long long fb_s = ctl->fbase[s], ob_s = ctl->obase[s];
-    // tile-state slots: levels are laid out by cumulative entry count plus one slot of slack per
-    // level, so the slot ranges of different levels never overlap
-    ulonglong2 *tstate = p.tstate + ((q == 0 ? 0ull : ctl->F[0] + ctl->fbase[q]) / kTile) + q;
-    __syncthreads();
-    mbar_wait(&s_bar, 0);
-
-    EvalCtx x;
-    x.ks = s_ktab;
-    x.kattr = reinterpret_cast<const unsigned *>(s_ktab + p.nkp);
-    x.lut = reinterpret_cast<const unsigned char *>(s_ktab + p.nkp + p.nka);
-    x.anc_n = anc_n; x.anc_r = anc_r; x.aux = W.aux;
-    x.lut_shift = p.lut_shift; x.s = s; x.q = q; x.min_hops = p.min_hops; x.max_hops = p.max_hops;
-    x.node_simple = p.node_simple; x.dest_kind = p.dest_kind; x.has_inter = p.has_inter;
-    x.pos_kind_cur = p.pos_kind_cur;
-
+    if (overflow_seen(ctl)) return;
+    const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
+    const int s = p.s, lane = c.w.lane;
+    ulonglong2 *tstate = p.tstate + c.slot0;
     unsigned long long scanned = 0;
     unsigned ov = 0;
     while (true) {
+        // one ticket per tile, taken only when the warp is ready for it: a tile claimed ahead of
+        // time would publish its counts late and stall the look-back of every later tile
+        // (measured: prefetching the next ticket made the kernel 4x slower)
         unsigned tile = 0;
         if (lane == 0) tile = atomicAdd(&ctl->ticket[s], 1u);
         tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= ntiles) break;
-
-        // ---------------------------------------------------------------- prologue: row range per entry
-        const unsigned long long i = (unsigned long long)tile * kTile + lane;
-        int deg = 0, beg = 0, tail = 0, par = 0, rel = 0, aux = 0;
-        if (i < Fq) {
-            bool live = true;
-            if (q == 0) {
-                tail = __ldg(p.seeds + i);
-                par = (int)i;
-                live = tail >= 0 && tail < p.n_nodes;
-                if (live && VARLEN) {
-                    const int k = kind_lut(x.ks, x.lut, x.lut_shift, tail);
-                    aux = k;
-                    live = !(x.kattr[k] & kAttrExcl) && (p.pos_kind_prev < 0 || p.pos_kind_prev == k);
-                }
-            } else {
-                const int4 e = p.frontier[s_fb[q] + i];
-                tail = e.x; par = e.y; rel = e.z; aux = e.w;
-            }
-            if (live) {
-                if (p.typed) {
-                    if (tail >= p.row_lo && tail < p.row_hi) {
-                        const int2 rg = __ldg(p.rng + (tail - p.row_lo));
-                        beg = rg.x; deg = rg.y - rg.x;
-                    }
-                } else {
-                    const int2 rg = __ldg(p.rng + tail);
-                    beg = rg.x;
-                    deg = (p.entity_only ? rg.y : __ldg(p.rng + tail + 1).x) - rg.x;
-                }
-            }
-        }
-        // ---- warp scan of the row lengths; entries without a row are compacted away
-        int incl = deg;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int n = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += n;
-        }
-        const int C = __shfl_sync(0xffffffffu, incl, 31);
-        const unsigned nzmask = __ballot_sync(0xffffffffu, deg > 0);
-        const int nz = __popc(nzmask);
-        __syncwarp();                                 // the previous tile's readers are done
-        if (deg > 0) {
-            const int o = __popc(nzmask & lt), off = incl - deg;
-            W.coff[o] = off;
-            W.crow[o] = beg - off;
-            W.cidx[o] = lane;
-            W.aux[o] = aux;
-            anc_n[q * kTile + o] = tail;              // nodes / relationships already on this path
-            if (q > 0) {
-                anc_r[q * kTile + o] = rel;
-                for (int d = q - 1; d >= 1; d--) {
-                    const int4 a = p.frontier[s_fb[d] + (unsigned)par];
-                    anc_n[d * kTile + o] = a.x;
-                    anc_r[d * kTile + o] = a.z;
-                    par = a.y;
-                }
-                anc_n[o] = __ldg(p.seeds + par);
-            }
-            W.root[o] = par;
-        }
-        W.coff[nz + lane] = (lane == 0) ? C : 0x7fffffff;       // coff[nz] = C, then 31 sentinels
-        if (lane < 2) W.coff[nz + 32 + lane] = 0x7fffffff;
-        __syncwarp();
+        if (tile >= c.ntiles) break;
+        const int C = tile_prologue<MODE>(p, c.T, c.w, tile, c.Fq, s_fb);
         scanned += (unsigned long long)C;
-
-        // owner of every lane's candidate in window `it`, given the owner jlo of the candidate
-        // just before the window: count the entry starts at or before the lane's candidate
-        auto owners = [&](int it, int &jlo) -> int {
-            const unsigned d = (unsigned)(W.coff[jlo + 1 + lane] - (it << 5));
-            const unsigned mask = __reduce_or_sync(0xffffffffu, d < 32u ? (1u << d) : 0u);
-            const int o = jlo + __popc(mask & (0xffffffffu >> (31 - lane)));
-            jlo += __popc(mask);
-            return o;
-        };
-        auto fetch = [&](int o, int c, int &v, int &r) {
-            const int slot = W.crow[o] + c;
-            if (ADJ2) {
-                const int2 a = __ldg(p.adj2 + slot);
-                v = a.x; r = a.y;
-            } else {
-                v = __ldg(p.adj1 + slot);
-                r = slot;
-            }
-        };
-
-        // ---------------------------------------------------------------- pass 1: classify and count
-        const int n_it = (C + 31) >> 5;
-        int cf = 0, ce = 0, jcap = 0;
-        {
-            int jlo = 0;
-            for (int it = 0; it < n_it; ++it) {
-                if (it == kFlagWin) jcap = jlo;
-                const int jstart = jlo;
-                const int o = owners(it, jlo);
-                const int c = (it << 5) + lane;
-                int fl = 0;
-                if (c < C) {
-                    int v, r, na;
-                    fetch(o, c, v, r);
-                    fl = eval_candidate<VARLEN>(x, o, v, r, na);
-                }
-                const unsigned bf = __ballot_sync(0xffffffffu, fl & 1), be = __ballot_sync(0xffffffffu, fl & 2);
-                cf += __popc(bf);
-                ce += __popc(be);
-                if (it < kFlagWin && lane == 0) { W.flag[0][it] = bf; W.flag[1][it] = be; W.flag[2][it] = (unsigned)jstart; }
-            }
-        }
+        int cf, ce;
+        tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce);
         unsigned long long run_f, run_e;
         tile_lookback(tstate, tile, p.epoch, (unsigned long long)cf, (unsigned long long)ce, run_f, run_e);
         if (run_f + cf > 0xffffffffull) ov |= 1u;     // the 32-bit count field of the state word
-        if (fb_s + run_f + cf > p.fcap) ov |= 1u;
-        if (ob_s + (run_e + ce) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
-        if (tile == ntiles - 1 && lane == 0) {        // the last tile knows the level totals
+        if (c.fb_s + run_f + cf > p.fcap) ov |= 1u;
+        if (c.ob_s + (run_e + ce) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
+        if (tile == c.ntiles - 1 && lane == 0) {      // the last tile knows the level totals
             ctl->F[s] = run_f + cf;
             ctl->N[s] = run_e + ce;
-            ctl->fbase[s + 1] = fb_s + run_f + cf;
-            ctl->obase[s + 1] = ob_s + (run_e + ce) * (unsigned long long)p.row_len;
         }
         __syncwarp();
-
-        // ---------------------------------------------------------------- pass 2: write survivors
-        // rows are queued and written 32 at a time so that every lane has a row to build
-        int qn = 0;
-        auto flush = [&](int n) {                     // emit queue entries 0..n-1 as rows run_e..run_e+n-1
-            if (lane < n) {
-                const int o = W.q_o[lane], v = W.q_v[lane], r = W.q_r[lane];
-                const unsigned long long w0 = ob_s + (run_e + lane) * (unsigned long long)p.row_len;
-                if (w0 + p.row_len <= p.ocap) {
-                    int *row = p.out + w0;
-                    for (int d = 0; d <= q; d++) row[d] = anc_n[d * kTile + o];
-                    row[s] = v;
-                    for (int d = 1; d <= q; d++) row[s + d] = anc_r[d * kTile + o];
-                    row[2 * s] = r;
-                    if (p.with_states) {
-                        const long long ts = __ldg(p.seed_ts + W.root[o]);
-                        unsigned miss = 0;
-                        for (int d = 0; d <= s; d++) {
-                            int first, cnt;
-                            const int nd = (d <= q) ? anc_n[d * kTile + o] : v;
-                            state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
-                            row[2 * s + 1 + d] = first;
-                            miss |= (cnt == 0 ? 1u : 0u) << d;
-                        }
-                        row[3 * s + 2] = (int)miss;
-                    }
-                }
-            }
-            run_e += n;
-        };
-        {
-            int jlo = jcap;
-            for (int it = 0; it < n_it; ++it) {
-                unsigned bf, be;
-                int o = 0, v = 0, r = 0, na = 0;
-                const int c = (it << 5) + lane;
-                if (it < kFlagWin) {
-                    bf = W.flag[0][it]; be = W.flag[1][it];
-                    if (!(bf | be)) continue;
-                    int j = (int)W.flag[2][it];
-                    o = owners(it, j);
-                    if (((bf | be) >> lane) & 1u) {
-                        fetch(o, c, v, r);
-                        if (VARLEN && ((bf >> lane) & 1u)) {     // a continuing entry carries its kind and interior flag
-                            const int k = kind_lut(x.ks, x.lut, x.lut_shift, v);
-                            na = k | (((W.aux[o] >> 16) | ((x.kattr[k] & kAttrInter) ? 1 : 0)) << 16);
-                        }
-                    }
-                } else {                                          // beyond the ballot cache: classify again
-                    o = owners(it, jlo);
-                    int fl = 0;
-                    if (c < C) {
-                        fetch(o, c, v, r);
-                        fl = eval_candidate<VARLEN>(x, o, v, r, na);
-                    }
-                    bf = __ballot_sync(0xffffffffu, fl & 1); be = __ballot_sync(0xffffffffu, fl & 2);
-                }
-                if ((bf >> lane) & 1u) {
-                    const unsigned long long pos = fb_s + run_f + __popc(bf & lt);
-                    if (pos < p.fcap) p.frontier[pos] = make_int4(v, (int)(tile * kTile + W.cidx[o]), r, na);
-                }
-                run_f += __popc(bf);
-                if (be) {
-                    if ((be >> lane) & 1u) {
-                        const int k = qn + __popc(be & lt);
-                        W.q_o[k] = o; W.q_v[k] = v; W.q_r[k] = r;
-                    }
-                    qn += __popc(be);
-                    __syncwarp();
-                    if (qn >= 32) {
-                        flush(32);
-                        __syncwarp();
-                        const int rest = qn - 32;
-                        int to = 0, tv = 0, tr = 0;
-                        if (lane < rest) { to = W.q_o[32 + lane]; tv = W.q_v[32 + lane]; tr = W.q_r[32 + lane]; }
-                        __syncwarp();
-                        if (lane < rest) { W.q_o[lane] = to; W.q_v[lane] = tv; W.q_r[lane] = tr; }
-                        qn = rest;
-                        __syncwarp();
-                    }
-                }
-            }
-            if (qn) flush(qn);
-        }
+        tile_fill<ADJ2, MODE, QT>(p, c.T, c.w, tile, C, c.fb_s, c.ob_s, run_f, run_e);
     }
     if (lane == 0) {
         if (scanned) atomicAdd(&ctl->E[s], scanned);

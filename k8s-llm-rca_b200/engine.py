@@ -20,7 +20,8 @@ _DIRS = {"out": DIR_OUT, "in": DIR_IN, "und": DIR_UND}
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
-EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_reserve", "rca_expand",
+EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold", "rca_reserve",
+           "rca_expand",
            "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_version")
 
 
@@ -68,7 +69,7 @@ def load_library(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("RCA_B200_LIB") or LIB_PATH     # the env var is for kernel experiments only
     if not os.path.exists(p):
         raise RuntimeError(f"{p} is missing: build the CUDA library first (__graft_entry__.build()); "
                            "this package has no CPU path")
@@ -80,6 +81,7 @@ def load_library(path: str | None = None):
     lib.rca_close.argtypes = [C.c_void_p]
     lib.rca_set_stream.argtypes = [C.c_void_p, C.c_uint64]
     lib.rca_reserve.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+    lib.rca_set_fused_threshold.argtypes = [C.c_void_p, C.c_int64]
     lib.rca_expand.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
                                C.POINTER(StatsDesc)]
     lib.rca_result_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
@@ -245,6 +247,10 @@ class Engine:
 
     def set_stream(self, cuda_stream: int):
         self._ck(self.lib.rca_set_stream(self.h, int(cuda_stream)))
+
+    def set_fused_threshold(self, max_seeds: int):
+        """Seed sets up to this size run the single-launch-per-hop kernels (see include/rca_b200.h)."""
+        self._ck(self.lib.rca_set_fused_threshold(self.h, int(max_seeds)))
 
     def reserve(self, frontier_entries: int, output_words: int):
         self._ck(self.lib.rca_reserve(self.h, int(frontier_entries), int(output_words)))

@@ -7,18 +7,22 @@ from conftest import rows_to_set, sort_rows
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def eng_small(snap_small):
+# every parity test runs twice: through the fused single-launch kernels (small seed sets) and
+# through the count / scan / fill kernels (large seed sets); the threshold is forced either way
+@pytest.fixture(scope="module", params=["fused", "split"])
+def eng_small(snap_small, request):
     from k8s_llm_rca_b200 import engine
     e = engine.Engine(snap_small)
+    e.set_fused_threshold(1 << 40 if request.param == "fused" else 0)
     yield e
     e.close()
 
 
-@pytest.fixture(scope="module")
-def eng_10k(snap_10k):
+@pytest.fixture(scope="module", params=["fused", "split"])
+def eng_10k(snap_10k, request):
     from k8s_llm_rca_b200 import engine
     e = engine.Engine(snap_10k)
+    e.set_fused_threshold(1 << 40 if request.param == "fused" else 0)
     yield e
     e.close()
 
@@ -107,13 +111,15 @@ def test_scratch_arena_growth(snap_small, csr_oracle_lib):
     """A tiny reservation forces the overflow -> grow -> re-run path; results must not change."""
     from k8s_llm_rca_b200 import engine
     orc = csr_oracle_lib.CsrOracle(snap_small)
-    eng = engine.Engine(snap_small)
-    eng.reserve(64, 256)
     pod, node, ev, ns = _kinds(snap_small, "Pod", "Node", "Event", "Namespace")
-    res = check_varlen(eng, orc, snap_small.nodes_of_kind(pod), "und", 3, dest_kind=node, excl_kinds=[ev, ns],
-                       entity_only=True)
-    assert res.retries >= 1
-    eng.close()
+    for threshold in (1 << 40, 0):
+        eng = engine.Engine(snap_small)
+        eng.set_fused_threshold(threshold)
+        eng.reserve(64, 256)
+        res = check_varlen(eng, orc, snap_small.nodes_of_kind(pod), "und", 3, dest_kind=node, excl_kinds=[ev, ns],
+                           entity_only=True)
+        assert res.retries >= 1
+        eng.close()
 
 
 def _chain_for(snap, *steps):

@@ -15,6 +15,7 @@ reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 chains = len(sys.argv) > 3 and sys.argv[3] == "chains"
 w = workloads.Config3(n_objects=n_obj, n_events=int(n_obj * 0.108696))
 eng = E.Engine(w.snap)
+eng.reserve(48_000_000, 160_000_000)   # no overflow retries: call k, level s is kernel 4k+s-1
 pods, ev, ts = w.batch(0)
 for i in range(reps):
     r = eng.expand(w.varlen, pods, ts)
