@@ -54,9 +54,10 @@ typedef struct {
     const int32_t *out_rng;         /* [n_nodes+1][2] (begin, entity_end)                        */
     const int32_t *out_dst;         /* [n_rels]; slot == relationship id                         */
     const int32_t *in_rng;          /* [n_nodes+1][2]                                            */
-    const int32_t *in_adj;          /* [n_rels][2] (src, rel)                                    */
+    const int32_t *in_adj;          /* [n_rels][2] (src, rel | 1<<30)                            */
     const int32_t *und_rng;         /* [n_nodes+1][2]                                            */
-    const int32_t *und_adj;         /* [n_und][2] (neighbour, rel)                               */
+    const int32_t *und_adj;         /* [n_und][2] (neighbour, rel; bit 30 set: hop runs against
+                                       the relationship's stored direction)                     */
     const int32_t *typed_out;       /* [n_typed_out][2] (begin, end) into out_dst                */
     const int64_t *typed_out_base;  /* [n_etypes+1]                                              */
     const int32_t *typed_in;        /* [n_typed_in][2] (begin, end) into in_adj                  */
@@ -64,6 +65,7 @@ typedef struct {
     const int32_t *st_off;          /* [n_nodes+1] HasState interval lists                       */
     const int64_t *st_tmin, *st_tmax;/* [n_states] milliseconds; interval is [tmin, tmax)        */
     const int32_t *st_node;         /* [n_states] STATE node id                                  */
+    const int32_t *rel_et;          /* [n_rels] edge type of every relationship                  */
 } rca_snapshot_t;
 
 /* One query plan.  A VARLEN plan is the reference's variable-length metapath query
@@ -82,8 +84,11 @@ typedef struct {
     int32_t node_simple;            /* all(node ... single(...)) : no node repeats (:98)         */
     int32_t dest_kind;              /* n2.kind = $destKind (:97); -1 = any                       */
     int32_t has_inter;              /* size($intermediateKinds) > 0 (:100-102)                   */
-    int32_t prune;                  /* drop partial paths whose tail kind cannot reach dest_kind
-                                       in the hops that remain (schema-level, result-neutral)   */
+    int32_t prune;                  /* drop partial paths that provably cannot reach dest_kind in
+                                       the hops that remain: schema reachability, refined by the
+                                       edge type a path arrived over (stepping straight back over
+                                       an edge type that is functional on that side is impossible).
+                                       Result-neutral.                                           */
     int32_t pos_kind[RCA_MAX_HOPS + 1]; /* kind required at path position p, -1 = any (:127)     */
     uint8_t kind_excl[RCA_MAX_KINDS];   /* 1: kind may appear nowhere on a path (:99)            */
     uint8_t kind_inter[RCA_MAX_KINDS];  /* 1: kind is in $intermediateKinds                      */

@@ -38,6 +38,8 @@ struct rca_engine {
     int2 *typed_out = nullptr, *typed_in = nullptr;
     int *out_dst = nullptr, *st_off = nullptr;
     StRec *st_rec = nullptr;              // HasState intervals, one 32 B record each
+    unsigned char *rel_et = nullptr;      // edge type per relationship (only when there are <= 256 edge types)
+    std::vector<int> et_max_out, et_max_in;   // largest number of relationships of the type at one start / end node
     // scratch
     int4 *frontier = nullptr;
     unsigned long long fcap = 0;
@@ -163,6 +165,19 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         for (size_t j = 0; j < rec.size(); j++) rec[j] = StRec{s->st_tmin[j], s->st_tmax[j], s->st_node[j], {0, 0, 0}};
         OCK(upload(&g->st_rec, rec.data(), rec.size()));
     }
+    if (s->n_etypes <= 256 && s->rel_et) {
+        std::vector<unsigned char> et((size_t)s->n_rels);
+        for (size_t j = 0; j < et.size(); j++) et[j] = (unsigned char)s->rel_et[j];
+        OCK(upload(&g->rel_et, et.data(), et.size()));
+    }
+    g->et_max_out.assign(s->n_etypes, 0);
+    g->et_max_in.assign(s->n_etypes, 0);
+    for (int t = 0; t < s->n_etypes; t++) {
+        for (long long j = s->typed_out_base[t]; j < s->typed_out_base[t + 1]; j++)
+            g->et_max_out[t] = std::max(g->et_max_out[t], s->typed_out[2 * j + 1] - s->typed_out[2 * j]);
+        for (long long j = s->typed_in_base[t]; j < s->typed_in_base[t + 1]; j++)
+            g->et_max_in[t] = std::max(g->et_max_in[t], s->typed_in[2 * j + 1] - s->typed_in[2 * j]);
+    }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
     OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
     OCK(cudaMalloc((void **)&g->ptab, kPtBytes));
@@ -177,7 +192,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_rec, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
+                   e->st_off, e->st_rec, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
@@ -252,6 +267,58 @@ static void reach_bits(const rca_engine *e, const rca_plan_t *pl, unsigned *reac
             if (in_d[k]) reach[k] |= 1u << (r - 1);
         }
     }
+}
+
+// Arrival-aware refinement of reach_bits.  An arrival a = (edge type t, d) means the path's last
+// hop followed a relationship of type t along (d = 0) or against (d = 1) its stored direction.
+// rows[s][2t+d] = 1 if such a path, now s hops long, may still end at dest_kind within L hops.
+// The one thing this knows beyond kind-level reachability: the next hop cannot go straight back
+// over type t when t is functional on that side (no node has two such relationships), because
+// the only candidate is the relationship just used, and a MATCH pattern never reuses one.
+// Returns false (rows all 1) when the refinement does not apply.
+static bool arrival_reach(const rca_engine *e, const rca_plan_t *pl, int L, unsigned char *rows) {
+    const int nt = e->n_etypes, A = 2 * nt;
+    std::memset(rows, 1, (size_t)(RCA_MAX_HOPS + 1) * kArrBytes);
+    bool constrained = false;
+    for (int i = 0; i <= L; i++) constrained |= pl->pos_kind[i] >= 0;
+    if (!pl->prune || pl->dest_kind < 0 || constrained || nt > 256 || !e->rel_et) return false;
+    auto head = [&](int a) { return (a & 1) ? e->et_src[a >> 1] : e->et_dst[a >> 1]; };
+    auto tail = [&](int a) { return (a & 1) ? e->et_dst[a >> 1] : e->et_src[a >> 1]; };
+    auto allowed = [&](int a) {
+        const int t = a >> 1, d = a & 1;
+        if (pl->entity_only && e->et_cls[t]) return false;
+        if (pl->direction == RCA_DIR_OUT && d) return false;
+        if (pl->direction == RCA_DIR_IN && !d) return false;
+        return true;
+    };
+    auto step_ok = [&](int a, int b) {           // may arrival b follow arrival a ?
+        if (!allowed(b) || tail(b) != head(a)) return false;
+        if ((b >> 1) == (a >> 1) && (b & 1) != (a & 1)) {     // straight back over the same type
+            const int t = a >> 1;
+            const int deg = (a & 1) ? e->et_max_out[t] : e->et_max_in[t];
+            if (deg <= 1) return false;
+        }
+        return true;
+    };
+    std::vector<unsigned char> prev(A, 0), cur(A, 0);
+    const bool dest_ok = !pl->kind_excl[pl->dest_kind];
+    for (int r = 1; r <= L; r++) {
+        for (int a = 0; a < A; a++) {
+            unsigned char hit = prev[a];
+            for (int b = 0; b < A && !hit; b++) {
+                if (!step_ok(a, b)) continue;
+                const int hb = head(b);
+                if (hb == pl->dest_kind && dest_ok) hit = 1;
+                else if (r > 1 && !pl->kind_excl[hb] && prev[b]) hit = 1;
+            }
+            cur[a] = hit;
+        }
+        // a path s = L - r hops long has r hops left
+        unsigned char *row = rows + (size_t)(L - r) * kArrBytes;
+        for (int a = 0; a < A; a++) row[a] = cur[a];
+        prev = cur;
+    }
+    return true;
 }
 
 static int validate_plan(rca_engine *e, const rca_plan_t *pl) {
@@ -345,7 +412,9 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         }
     }
 
-    // ---- plan table: kind boundaries, one kind-action row per level, node-block -> kind table
+    // ---- plan table: kind boundaries, one kind-action row per level, node-block -> kind table,
+    //      one arrival row per level
+    bool arr_prune = false;
     {
         unsigned char *t = e->h_ptab;
         std::memset(t, 0, kPtBytes);
@@ -367,6 +436,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             }
         }
         std::memcpy(t + kPtLut, e->kind_lut.data(), kLutEntries);
+        arr_prune = varlen && arrival_reach(e, pl, L, t + kPtArr);
         CK(cudaMemcpyAsync(e->ptab, t, kPtBytes, cudaMemcpyHostToDevice, e->stream));
     }
 
@@ -441,6 +511,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             p.ctl = e->ctl; p.tstate = e->tstate;
             p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
             p.ptab = e->ptab;
+            p.rel_et = e->rel_et; p.arr_prune = arr_prune;
             p.st_off = e->st_off; p.st_rec = e->st_rec;
             const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
             const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);

@@ -58,7 +58,11 @@ constexpr int kLutEntries = 4096;                                             //
 constexpr int kPtKs = 0;
 constexpr int kPtAct = kPtKs + 4 * kKindPad;                                  // (RCA_MAX_HOPS+1) rows of RCA_MAX_KINDS bytes
 constexpr int kPtLut = kPtAct + (RCA_MAX_HOPS + 1) * RCA_MAX_KINDS;
-constexpr int kPtBytes = kPtLut + kLutEntries;
+constexpr int kArrBytes = 2 * 256;                                            // one byte per (edge type, direction)
+constexpr int kPtArr = kPtLut + kLutEntries;                                  // (RCA_MAX_HOPS+1) rows of kArrBytes
+constexpr int kPtBytes = kPtArr + (RCA_MAX_HOPS + 1) * kArrBytes;
+constexpr int kRelRev = 1 << 30;      // rel word of in / undirected tables: hop runs against the stored direction
+constexpr int kRelMask = kRelRev - 1;
 
 // kind-action byte of one (level, kind)
 constexpr unsigned kActCont = 1u;     // a path may continue through a node of this kind at this level
@@ -114,6 +118,8 @@ struct LevelParams {
     ulonglong2 *gsum;                 // split path: sums per group of 32 tile slots (zeroed per call)
     ulonglong2 *gscan;                // split path: exclusive prefix of gsum within the level
     const unsigned char *ptab;        // plan table (layout above)
+    const unsigned char *rel_et;      // edge type of every relationship (null: more than 256 edge types)
+    int arr_prune;                    // refine 'continue' by the arrival table (edge type, direction)
     // HasState intervals
     const int *st_off;
     const StRec *st_rec;
@@ -164,28 +170,32 @@ struct Tables {
     const unsigned char *act_q;       // kind-action row of level s-1 (seed checks)
     const unsigned char *act_s;       // kind-action row of level s
     const unsigned char *lut;
+    const unsigned char *arr;         // [2*t + d]: a path that arrived over edge type t (d = 1: against its
+                                      // direction) at level s can still reach the destination kind
     int lut_shift;
 };
 struct TablesSm {
     alignas(16) int ks[kKindPad];
     alignas(16) unsigned char act[2 * RCA_MAX_KINDS];
     alignas(16) unsigned char lut[kLutEntries];
+    alignas(16) unsigned char arr[kArrBytes];
     alignas(8) unsigned long long bar;
 };
 
-// One elected thread starts the three bulk copies; everybody waits on the mbarrier after a CTA sync.
+// One elected thread starts the four bulk copies; everybody waits on the mbarrier after a CTA sync.
 __device__ __forceinline__ Tables stage_tables(TablesSm &sm, const LevelParams &p) {
     if (threadIdx.x == 0) {
         mbar_init(&sm.bar, 1);
-        mbar_expect_tx(&sm.bar, 4 * kKindPad + 2 * RCA_MAX_KINDS + kLutEntries);
+        mbar_expect_tx(&sm.bar, 4 * kKindPad + 2 * RCA_MAX_KINDS + kLutEntries + kArrBytes);
         bulk_g2s(sm.ks, p.ptab + kPtKs, 4 * kKindPad, &sm.bar);
         bulk_g2s(sm.act, p.ptab + kPtAct + (p.s - 1) * RCA_MAX_KINDS, 2 * RCA_MAX_KINDS, &sm.bar);
         bulk_g2s(sm.lut, p.ptab + kPtLut, kLutEntries, &sm.bar);
+        bulk_g2s(sm.arr, p.ptab + kPtArr + p.s * kArrBytes, kArrBytes, &sm.bar);
     }
     __syncthreads();
     mbar_wait(&sm.bar, 0);
     Tables t;
-    t.ks = sm.ks; t.act_q = sm.act; t.act_s = sm.act + RCA_MAX_KINDS; t.lut = sm.lut; t.lut_shift = p.lut_shift;
+    t.ks = sm.ks; t.act_q = sm.act; t.act_s = sm.act + RCA_MAX_KINDS; t.lut = sm.lut; t.arr = sm.arr; t.lut_shift = p.lut_shift;
     return t;
 }
 
@@ -322,9 +332,10 @@ __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, c
     v = 0; r = 0; na = 0;
     if (c >= C) return 0;
     const int slot = w.W->crow[o] + c;
+    int against = 0;
     if (ADJ2) {
         const int2 a = __ldg(p.adj2 + slot);
-        v = a.x; r = a.y;
+        v = a.x; r = a.y & kRelMask; against = (a.y >> 30) & 1;
     } else {
         v = __ldg(p.adj1 + slot);
         r = slot;
@@ -346,7 +357,9 @@ __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, c
     const unsigned a = T.act_s[k];
     const int inter = w.W->aux[o] >> 16;
     na = k | ((inter | (int)((a >> 2) & 1u)) << 16);
-    return (int)(a & kActCont) | (((a & kActEmit) && (!p.need_inter || inter)) ? 2 : 0);
+    int fl = (int)(a & kActCont) | (((a & kActEmit) && (!p.need_inter || inter)) ? 2 : 0);
+    if ((fl & 1) && p.arr_prune && !T.arr[2 * __ldg(p.rel_et + r) + against]) fl &= ~1;
+    return fl;
 }
 
 // Emit queue entries 0..n-1 as rows run_e .. run_e+n-1 (one row per lane).

@@ -40,7 +40,8 @@ class SnapshotDesc(C.Structure):
                 ("und_rng", C.c_void_p), ("und_adj", C.c_void_p),
                 ("typed_out", C.c_void_p), ("typed_out_base", C.c_void_p),
                 ("typed_in", C.c_void_p), ("typed_in_base", C.c_void_p),
-                ("st_off", C.c_void_p), ("st_tmin", C.c_void_p), ("st_tmax", C.c_void_p), ("st_node", C.c_void_p)]
+                ("st_off", C.c_void_p), ("st_tmin", C.c_void_p), ("st_tmax", C.c_void_p), ("st_node", C.c_void_p),
+                ("rel_et", C.c_void_p)]
 
 
 class PlanDesc(C.Structure):
@@ -215,7 +216,7 @@ class Engine:
         self._gen = 0
         names = ("kind_start", "et_src", "et_dst", "et_cls", "out_rng", "out_dst", "in_rng", "in_adj", "und_rng",
                  "und_adj", "typed_out", "typed_out_base", "typed_in", "typed_in_base", "st_off", "st_tmin",
-                 "st_tmax", "st_node")
+                 "st_tmax", "st_node", "rel_et")
         dt = {"typed_out_base": np.int64, "typed_in_base": np.int64, "st_tmin": np.int64, "st_tmax": np.int64}
         keep = {n: np.ascontiguousarray(getattr(snap, n), dtype=dt.get(n, np.int32)) for n in names}
         d = SnapshotDesc()

@@ -14,6 +14,8 @@ Numbering rules (they are what makes results comparable across implementations):
   Types whose endpoints are both entity kinds come first ("class 0"); types that touch a
   STATE kind (HasState, HasEvent) come last ("class 1").
 * relationship id = slot in the out-CSR, rows sorted by (src, etype, dst, input order).
+* in the (neighbour, rel) pairs of the in- and undirected tables, bit 30 of the rel word is set
+  when the hop runs against the relationship's stored direction (REL_REVERSED); ids stay < 2^30.
 
 Every adjacency row therefore lists its entity-entity part first; ``*_rng[v] = (begin,
 entity_end)`` and the full row ends at ``*_rng[v+1][0]``.
@@ -28,6 +30,8 @@ import numpy as np
 
 I32 = np.int32
 I64 = np.int64
+REL_REVERSED = 1 << 30
+REL_MASK = REL_REVERSED - 1
 
 
 @dataclass
@@ -122,7 +126,7 @@ class Snapshot:
     def device_bytes(self) -> int:
         tot = 0
         for a in ("kind_start", "et_src", "et_dst", "out_rng", "out_dst", "in_rng", "in_adj", "und_rng",
-                  "und_adj", "typed_out", "typed_in", "st_off", "st_tmin", "st_tmax", "st_node"):
+                  "und_adj", "typed_out", "typed_in", "st_off", "st_tmin", "st_tmax", "st_node", "rel_et"):
             tot += getattr(self, a).nbytes
         return tot
 
@@ -193,7 +197,7 @@ class Snapshot:
         # ---- in-CSC: (src, rel) pairs, rows sorted by (dst, etype, src, rel)
         rel = np.arange(E, dtype=I64)
         p_in = np.lexsort((rel, src, et, dst))
-        s.in_adj = np.stack([src[p_in], rel[p_in]], axis=1).astype(I32) if E else np.zeros((0, 2), I32)
+        s.in_adj = np.stack([src[p_in], rel[p_in] | REL_REVERSED], axis=1).astype(I32) if E else np.zeros((0, 2), I32)
         s.in_rng = _ranges(dst[p_in], ecls[p_in], V)
 
         # ---- undirected rows: class-0 out, class-0 in, class-1 out, class-1 in; a self-loop is
@@ -201,7 +205,7 @@ class Snapshot:
         keep_in = src != dst
         u_node = np.concatenate([src, dst[keep_in]])
         u_nbr = np.concatenate([dst, src[keep_in]])
-        u_rel = np.concatenate([rel, rel[keep_in]])
+        u_rel = np.concatenate([rel, rel[keep_in] | REL_REVERSED])
         u_cls = np.concatenate([ecls, ecls[keep_in]])
         u_part = np.concatenate([np.zeros(E, I64), np.ones(int(keep_in.sum()), I64)])
         u_et = np.concatenate([et, et[keep_in]])

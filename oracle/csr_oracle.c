@@ -26,6 +26,7 @@
 #endif
 
 #define ORC_MAX_HOPS 8
+#define ORC_REL_MASK 0x3fffffff   /* snapshot format: bit 30 of an in_adj rel word marks a reversed hop */
 
 typedef struct {
     int32_t n_nodes, n_kinds;
@@ -117,7 +118,7 @@ static void varlen_visit(walk_t *w, int s) {
     if (q->direction == 1 || q->direction == 2) {
         int32_t b = g->in_rng[2 * u], e = q->entity_only ? g->in_rng[2 * u + 1] : g->in_rng[2 * (u + 1)];
         for (int32_t j = b; j < e; j++) {
-            int32_t v = g->in_adj[2 * j], r = g->in_adj[2 * j + 1];
+            int32_t v = g->in_adj[2 * j], r = g->in_adj[2 * j + 1] & ORC_REL_MASK;
             if (q->direction == 2 && v == u) continue;                /* a loop is traversed once */
             varlen_try(w, s, v, r);
         }
@@ -214,7 +215,7 @@ int64_t orc_chain(const orc_graph_t *g, const int32_t *et, const int32_t *dir, i
                 if (cur[s] >= end[s]) { s--; continue; }
                 int32_t j = cur[s]++, v, r;
                 mysc++;
-                if (dir[s]) { v = g->in_adj[2 * j]; r = g->in_adj[2 * j + 1]; } else { v = g->out_dst[j]; r = j; }
+                if (dir[s]) { v = g->in_adj[2 * j]; r = g->in_adj[2 * j + 1] & ORC_REL_MASK; } else { v = g->out_dst[j]; r = j; }
                 if (g->rel_et[r] != et[s]) continue;
                 nodes[s + 1] = v; rels[s] = r;
                 if (s + 1 == n_steps) { buf_push(&lv[n_steps], nodes, rels, n_steps); continue; }
