@@ -146,6 +146,33 @@ int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows);
 int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, int64_t n, int on_device,
                      int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
 
+/* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
+ * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory
+ * that every GPU which loads the library keeps until the process exits. */
+#define RCA_STATIC_MAX_SEEDS 262144
+#define RCA_STATIC_MAX_FRONTIER 262144
+#define RCA_STATIC_SCRATCH_BYTES (5u << 20)
+
+/* No counterpart in the reference.  rca_expand for callers that cannot allocate device memory:
+ * a service whose device-memory budget was handed to a pool at start-up, a latency path where
+ * cudaMalloc (which may synchronise the whole device) is not allowed, a process under a memory
+ * cap.  Same plans, same results and row order as rca_expand at these sizes, but
+ *   - it calls no cudaMalloc / cudaFree and no allocating library routine: its scratch is a fixed
+ *     array inside the library, limited by the three constants above; a plan that needs more is
+ *     refused with RCA_ERR_ARG / RCA_ERR_NOMEM and a message naming the limit - nothing grows;
+ *   - seeds, timestamps and rows are the CALLER's DEVICE buffers: dev_seeds[n_seeds],
+ *     dev_seed_ts[n_seeds] (only with plan->with_states), dev_rows[rows_capacity_words].  Rows of
+ *     length 1 come first, then length 2, ...; stats->emitted[s] and stats->row_len[s] say how
+ *     many and how wide, so level s starts at word sum_{j<s} emitted[j] * row_len[j];
+ *   - the first call on a device looks up the scratch array's device address; make that first
+ *     call before starting any stream capture;
+ *   - all calls on one GPU share the one scratch array, which keeps what the previous call left in
+ *     it (the call resets what it needs).  Two calls that overlap on the same GPU - from two
+ *     engines, threads or streams - corrupt each other: run them one after the other. */
+int rca_expand_static(rca_engine_t *e, const rca_plan_t *plan, const int32_t *dev_seeds, int64_t n_seeds,
+                      const int64_t *dev_seed_ts, int32_t *dev_rows, int64_t rows_capacity_words,
+                      rca_stats_t *stats);
+
 /* library / build information, e.g. "rca_b200 0.1 sm_100a" */
 const char *rca_version(void);
 

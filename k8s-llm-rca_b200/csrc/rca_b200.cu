@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -638,5 +639,191 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
         if (out_ids) CK(cudaMemcpyAsync(out_ids, d_ids, 4 * (size_t)n * RCA_STATE_LIMIT, cudaMemcpyDeviceToHost, e->stream));
     }
     CK(cudaStreamSynchronize(e->stream));
+    return RCA_OK;
+}
+
+
+// ================================================================================================
+// rca_expand_static: the same expansion for callers that must not allocate.
+//
+// Who needs this: code that runs where device memory may not be requested - a service that gave
+// its whole device-memory budget to a pool at start-up, a handler on a latency path where
+// cudaMalloc (which may synchronise the device) is forbidden, a process under a hard memory cap.
+// rca_expand grows its scratch arenas with cudaMalloc when a query needs more room; this entry
+// point never does.  Its scratch - control block, plan table, tile states and the frontier of
+// partial paths - is the fixed array below, which lives in the library image: every GPU that
+// loads the library holds RCA_STATIC_SCRATCH_BYTES of it until the process exits.
+//
+// The array's name is only a host-side handle for the symbol.  Kernels need its address in device
+// memory, which cudaGetSymbolAddress returns once per device (with that device current); that
+// happens on the first call for a device, see static_scratch_for().
+static __device__ __align__(256) unsigned char g_static_scratch[RCA_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr size_t kSsCtl = 0;                                                    // Ctl
+constexpr size_t kSsPtab = 512;                                                 // plan table
+constexpr size_t kSsTstate = kSsPtab + ((kPtBytes + 255) / 256) * 256;          // tile-state words
+constexpr size_t kSsSlots = (RCA_STATIC_MAX_SEEDS + RCA_STATIC_MAX_FRONTIER) / kTile + (size_t)kGroup * (kLv + 2);
+constexpr size_t kSsFrontier = kSsTstate + ((kSsSlots * sizeof(ulonglong2) + 255) / 256) * 256;
+constexpr size_t kSsEnd = kSsFrontier + (size_t)RCA_STATIC_MAX_FRONTIER * sizeof(int4);
+static_assert(sizeof(Ctl) <= kSsPtab, "control block does not fit its slot");
+static_assert(kSsEnd <= RCA_STATIC_SCRATCH_BYTES, "RCA_STATIC_SCRATCH_BYTES is too small for the stated maxima");
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char *g_static_ptr[kMaxDevices] = {nullptr};
+unsigned g_static_epoch[kMaxDevices] = {0};
+
+// Device address of the scratch array on `device` (which must be the current device); resolved once.
+cudaError_t static_scratch_for(int device, unsigned char **out) {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[device]) {
+        void *p = nullptr;
+        cudaError_t rc = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (rc != cudaSuccess) return rc;
+        g_static_ptr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_static_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int rca_expand_static(rca_engine_t *e, const rca_plan_t *pl, const int32_t *dev_seeds, int64_t n_seeds,
+                                 const int64_t *dev_seed_ts, int32_t *dev_rows, int64_t rows_capacity_words,
+                                 rca_stats_t *stats) {
+    if (!e) return RCA_ERR_ARG;
+    if (!pl || n_seeds < 0 || (n_seeds > 0 && !dev_seeds) || rows_capacity_words < 0 || (rows_capacity_words > 0 && !dev_rows))
+        return fail(e, RCA_ERR_ARG, "rca_expand_static: null plan, seeds or row buffer");
+    if (n_seeds > RCA_STATIC_MAX_SEEDS)
+        return fail(e, RCA_ERR_ARG, "rca_expand_static: %lld seeds exceed the fixed scratch (RCA_STATIC_MAX_SEEDS = %d); "
+                    "use rca_expand or split the seeds", (long long)n_seeds, RCA_STATIC_MAX_SEEDS);
+    if (pl->with_states && n_seeds > 0 && !dev_seed_ts) return fail(e, RCA_ERR_ARG, "rca_expand_static: with_states needs seed_ts");
+    if (e->device < 0 || e->device >= kMaxDevices) return fail(e, RCA_ERR_ARG, "rca_expand_static: device %d not supported", e->device);
+    int rc = validate_plan(e, pl);
+    if (rc) return rc;
+    CK(cudaSetDevice(e->device));
+    unsigned char *ss = nullptr;
+    CK(static_scratch_for(e->device, &ss));
+    const bool varlen = pl->kind == RCA_PLAN_VARLEN;
+    const int L = varlen ? pl->max_hops : pl->n_steps;
+    const int mode = !varlen ? kModeChain : (pl->node_simple ? kModeSimple : kModeRelUnique);
+
+    // tile-state words are recognised by the call's tag, so they are not cleared between calls;
+    // the array starts as zeros (static storage) and is cleared again only if the tag wraps
+    unsigned epoch;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        epoch = ++g_static_epoch[e->device];
+        if ((epoch & 0x3fffffffu) == 0) {
+            CK(cudaMemsetAsync(ss + kSsTstate, 0, kSsSlots * sizeof(ulonglong2), e->stream));
+            epoch = g_static_epoch[e->device] = 1;
+        }
+    }
+
+    // plan table and control block: built in the engine's pinned staging buffers (allocated by
+    // rca_open), copied into the scratch; the control block copy is what zeroes counters and tickets
+    bool arr_prune = false;
+    {
+        unsigned char *t = e->h_ptab;
+        std::memset(t, 0, kPtBytes);
+        int *ks = reinterpret_cast<int *>(t + kPtKs);
+        for (int k = 0; k < kKindPad; k++) ks[k] = k <= e->n_kinds ? e->kind_start[k] : 0x7fffffff;
+        if (varlen) {
+            unsigned reach[RCA_MAX_KINDS];
+            reach_bits(e, pl, reach);
+            for (int s = 0; s <= L; s++) {
+                unsigned char *row = t + kPtAct + s * RCA_MAX_KINDS;
+                for (int k = 0; k < e->n_kinds; k++) {
+                    const bool dead = pl->kind_excl[k] || (pl->pos_kind[s] >= 0 && pl->pos_kind[s] != k);
+                    unsigned a = dead ? kActDead : 0u;
+                    if (!dead && s < L && ((reach[k] >> (L - s - 1)) & 1u)) a |= kActCont;
+                    if (!dead && s >= pl->min_hops && (pl->dest_kind < 0 || pl->dest_kind == k)) a |= kActEmit;
+                    if (pl->kind_inter[k]) a |= kActInter;
+                    row[k] = (unsigned char)a;
+                }
+            }
+        }
+        std::memcpy(t + kPtLut, e->kind_lut.data(), kLutEntries);
+        arr_prune = varlen && arrival_reach(e, pl, L, t + kPtArr);
+        CK(cudaMemcpyAsync(ss + kSsPtab, t, kPtBytes, cudaMemcpyHostToDevice, e->stream));
+    }
+    std::memset(e->h_ctl, 0, sizeof(Ctl));
+    e->h_ctl->F[0] = (unsigned long long)n_seeds;
+    CK(cudaEventRecord(e->ev0, e->stream));
+    CK(cudaMemcpyAsync(ss + kSsCtl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaEventRecord(e->ev_lv[0], e->stream));
+    int launches = 0;
+    for (int s = 1; s <= L; s++) {
+        LevelParams p;
+        std::memset(&p, 0, sizeof p);
+        int dir;
+        if (varlen) {
+            dir = pl->direction;
+            p.rng = dir == RCA_DIR_OUT ? e->out_rng : dir == RCA_DIR_IN ? e->in_rng : e->und_rng;
+            p.entity_only = pl->entity_only;
+        } else {
+            const int t = pl->step_etype[s - 1];
+            dir = pl->step_dir[s - 1];
+            const int rowk = dir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
+            p.typed = 1;
+            p.rng = (dir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
+            p.row_lo = e->kind_start[rowk];
+            p.row_hi = e->kind_start[rowk + 1];
+        }
+        p.adj1 = e->out_dst;
+        p.adj2 = dir == RCA_DIR_IN ? e->in_adj : e->und_adj;
+        p.n_nodes = e->n_nodes;
+        p.s = s;
+        p.chain_flag = s < L ? 1 : 2;
+        p.need_inter = varlen && pl->has_inter;
+        p.with_states = pl->with_states;
+        p.row_len = row_len_of(pl, s);
+        for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
+        p.epoch = epoch;
+        p.lut_shift = e->lut_shift;
+        p.seeds = dev_seeds; p.seed_ts = (const long long *)dev_seed_ts;
+        p.frontier = reinterpret_cast<int4 *>(ss + kSsFrontier); p.fcap = RCA_STATIC_MAX_FRONTIER;
+        p.out = dev_rows; p.ocap = (unsigned long long)rows_capacity_words;
+        p.ctl = reinterpret_cast<Ctl *>(ss + kSsCtl);
+        p.tstate = reinterpret_cast<ulonglong2 *>(ss + kSsTstate);
+        p.ptab = ss + kSsPtab;
+        p.rel_et = e->rel_et; p.arr_prune = arr_prune;
+        p.st_off = e->st_off; p.st_rec = e->st_rec;
+        const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
+        const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
+        int grid = max_grid(e, ks.fused, dyn);
+        if (s == 1) grid = (int)std::min<long long>(grid, std::max<long long>(1, (n_seeds + kTile * kWarps - 1) / (kTile * kWarps)));
+        ks.fused<<<grid, kThreads, dyn, e->stream>>>(p);
+        launches++;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(e->ev_lv[s], e->stream));
+    }
+    CK(cudaEventRecord(e->ev1, e->stream));
+    CK(cudaMemcpyAsync(e->h_ctl, ss + kSsCtl, sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+    const unsigned ov = e->h_ctl->overflow;
+    if (ov & 1u)
+        return fail(e, RCA_ERR_NOMEM, "rca_expand_static: the plan needs more than the %d partial paths the fixed scratch holds "
+                    "(RCA_STATIC_MAX_FRONTIER); use rca_expand or split the seeds", RCA_STATIC_MAX_FRONTIER);
+    if (ov & 2u)
+        return fail(e, RCA_ERR_NOMEM, "rca_expand_static: the row buffer (%lld words) is too small for the result",
+                    (long long)rows_capacity_words);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->frontier[0] = n_seeds;
+        for (int s = 1; s <= L; s++) {
+            stats->frontier[s] = (int64_t)e->h_ctl->F[s];
+            stats->scanned[s] = (int64_t)e->h_ctl->E[s];
+            stats->emitted[s] = (int64_t)e->h_ctl->N[s];
+            stats->total += stats->emitted[s];
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, e->ev_lv[s - 1], e->ev_lv[s]) == cudaSuccess) stats->level_ms[s] = t;
+        }
+        for (int s = 0; s <= L; s++) stats->row_len[s] = row_len_of(pl, s);
+        stats->kernel_ms = ms;
+        stats->launches = launches;
+    }
     return RCA_OK;
 }

@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold", "rca_reserve",
-           "rca_expand",
+           "rca_expand", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_version")
 
 
@@ -85,6 +85,8 @@ def load_library(path: str | None = None):
     lib.rca_set_fused_threshold.argtypes = [C.c_void_p, C.c_int64]
     lib.rca_expand.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
                                C.POINTER(StatsDesc)]
+    lib.rca_expand_static.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                      C.c_int64, C.POINTER(StatsDesc)]
     lib.rca_result_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
                                      C.POINTER(C.c_int32)]
     lib.rca_result_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -272,6 +274,21 @@ class Engine:
         self._ck(self.lib.rca_expand(self.h, C.byref(plan), sp, n, tp, on_dev, C.byref(st)))
         levels = plan.max_hops if plan.kind == PLAN_VARLEN else plan.n_steps
         return ExpandResult(self, st, levels)
+
+    def expand_static(self, plan: PlanDesc, dev_seeds, dev_seed_ts, dev_rows):
+        """rca_expand_static: expansion that allocates nothing (fixed scratch inside the library; see
+        include/rca_b200.h for the limits and the sharing rule).  All three buffers are device
+        tensors owned by the caller: int32 seeds, int64 timestamps (or None), int32 row buffer.
+        Returns a StatsDesc; rows of length s start at word sum_{j<s} emitted[j]*row_len[j]."""
+        for t in (dev_seeds, dev_rows) + ((dev_seed_ts,) if dev_seed_ts is not None else ()):
+            if not (hasattr(t, "is_cuda") and t.is_cuda and t.is_contiguous()):
+                raise ValueError("expand_static takes contiguous device tensors")
+        st = StatsDesc()
+        self._ck(self.lib.rca_expand_static(
+            self.h, C.byref(plan), dev_seeds.data_ptr(), int(dev_seeds.numel()),
+            dev_seed_ts.data_ptr() if dev_seed_ts is not None else None,
+            dev_rows.data_ptr(), int(dev_rows.numel()), C.byref(st)))
+        return st
 
     def state_lookup(self, nodes, ts, with_ids=True):
         """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids)."""
