@@ -146,6 +146,11 @@ int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows);
 int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, int64_t n, int on_device,
                      int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
 
+/* replaces the query text of find_loose_states, analyze_root_cause.py:51-60 (and, with both bounds
+ * equal, find_strict_states): intervals with tmin <= tmin_le[i] and tmax > tmax_gt[i]. */
+int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt, int64_t n,
+                     int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
+
 /* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
  * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory
  * that every GPU which loads the library keeps until the process exits. */

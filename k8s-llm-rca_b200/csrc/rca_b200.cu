@@ -602,18 +602,18 @@ extern "C" int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows) {
     return RCA_OK;
 }
 
-extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, int64_t n, int on_device,
-                                int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
+static int state_query(rca_engine_t *e, const char *who, const int32_t *nodes, const int64_t *ta, const int64_t *tb, int64_t n,
+                       int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
     if (!e) return RCA_ERR_ARG;
-    if (n < 0 || (n > 0 && (!nodes || !ts || !out_first || !out_cnt))) return fail(e, RCA_ERR_ARG, "rca_state_lookup: null argument");
+    if (n < 0 || (n > 0 && (!nodes || !ta || !tb || !out_first || !out_cnt))) return fail(e, RCA_ERR_ARG, "%s: null argument", who);
     if (n == 0) return RCA_OK;
     CK(cudaSetDevice(e->device));
     const int *d_nodes = nodes;
-    const long long *d_ts = (const long long *)ts;
+    const long long *d_ta = (const long long *)ta, *d_tb = (const long long *)tb;
     int *d_first = out_first, *d_cnt = out_cnt, *d_ids = out_ids;
     if (!on_device) {
-        // staging layout: ts[n] (8 B) | nodes[n] | first[n] | cnt[n] | ids[n][LIMIT]
-        const size_t need = (size_t)n * (8 + 4 + 4 + 4 + 4 * RCA_STATE_LIMIT);
+        // staging layout: ta[n] | tb[n] (8 B each) | nodes[n] | first[n] | cnt[n] | ids[n][LIMIT]
+        const size_t need = (size_t)n * (16 + 4 + 4 + 4 + 4 * RCA_STATE_LIMIT);
         if (need > e->io_cap) {
             CK(cudaStreamSynchronize(e->stream));
             if (e->io_buf) CK(cudaFree(e->io_buf));
@@ -622,16 +622,18 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
             e->io_cap = need;
         }
         char *b = (char *)e->io_buf;
-        d_ts = (long long *)b;
-        d_nodes = (int *)(b + 8 * (size_t)n);
-        d_first = (int *)(b + 12 * (size_t)n);
-        d_cnt = (int *)(b + 16 * (size_t)n);
-        d_ids = out_ids ? (int *)(b + 20 * (size_t)n) : nullptr;
-        CK(cudaMemcpyAsync((void *)d_ts, ts, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+        d_ta = (long long *)b;
+        d_tb = (long long *)(b + 8 * (size_t)n);
+        d_nodes = (int *)(b + 16 * (size_t)n);
+        d_first = (int *)(b + 20 * (size_t)n);
+        d_cnt = (int *)(b + 24 * (size_t)n);
+        d_ids = out_ids ? (int *)(b + 28 * (size_t)n) : nullptr;
+        CK(cudaMemcpyAsync((void *)d_ta, ta, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemcpyAsync((void *)d_tb, tb, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
         CK(cudaMemcpyAsync((void *)d_nodes, nodes, 4 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
     }
-    state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_rec, e->n_nodes,
-                                                                    d_nodes, d_ts, n, d_first, d_cnt, d_ids);
+    state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_rec, e->n_nodes, d_nodes, d_ta, d_tb, n,
+                                                                    d_first, d_cnt, d_ids);
     CK(cudaGetLastError());
     if (!on_device) {
         CK(cudaMemcpyAsync(out_first, d_first, 4 * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
@@ -642,6 +644,15 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
     return RCA_OK;
 }
 
+extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, int64_t n, int on_device,
+                                int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
+    return state_query(e, "rca_state_lookup", nodes, ts, ts, n, on_device, out_first, out_cnt, out_ids);
+}
+
+extern "C" int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt,
+                                int64_t n, int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
+    return state_query(e, "rca_state_window", nodes, tmin_le, tmax_gt, n, on_device, out_first, out_cnt, out_ids);
+}
 
 // ================================================================================================
 // rca_expand_static: the same expansion for callers that must not allocate.

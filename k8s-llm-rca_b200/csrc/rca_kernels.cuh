@@ -688,16 +688,18 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
     }
 }
 
-// Stand-alone HasState predicate (analyze_root_cause.py:70-79), one thread per (entity, timestamp).
-__global__ void state_lookup(const int *st_off, const StRec *rec, int n_nodes, const int *nodes, const long long *ts,
-                             long long n, int *out_first, int *out_cnt, int *out_ids) {
+// Stand-alone HasState predicate, one thread per query: intervals of entity nodes[i] with
+// tmin <= ta[i] and tmax > tb[i].  ta == tb is the strict form (analyze_root_cause.py:70-79);
+// (ta, tb) = (window end, window start) is the loose form (:51-60).
+__global__ void state_lookup(const int *st_off, const StRec *rec, int n_nodes, const int *nodes, const long long *ta,
+                             const long long *tb, long long n, int *out_first, int *out_cnt, int *out_ids) {
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= n) return;
     int v = nodes[i], c = 0, f = -1;
     if (v >= 0 && v < n_nodes) {
-        const long long t = ts[i];
+        const long long a = ta[i], b = tb[i];
         for (int j = st_off[v]; j < st_off[v + 1]; j++) {
-            if (rec[j].tmin <= t && rec[j].tmax > t) {
+            if (rec[j].tmin <= a && rec[j].tmax > b) {
                 const int sn = rec[j].node;
                 if (c == 0) f = sn;
                 if (out_ids && c < RCA_STATE_LIMIT) out_ids[i * RCA_STATE_LIMIT + c] = sn;

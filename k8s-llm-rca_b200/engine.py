@@ -22,7 +22,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold", "rca_reserve",
            "rca_expand", "rca_expand_static",
-           "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_version")
+           "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_version")
 
 
 class RcaError(RuntimeError):
@@ -92,6 +92,8 @@ def load_library(path: str | None = None):
     lib.rca_result_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.rca_state_lookup.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
+    lib.rca_state_window.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]
     if path is None:
         _lib = lib
     return lib
@@ -290,14 +292,20 @@ class Engine:
             dev_rows.data_ptr(), int(dev_rows.numel()), C.byref(st)))
         return st
 
-    def state_lookup(self, nodes, ts, with_ids=True):
-        """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids)."""
+    def state_lookup(self, nodes, ts, with_ids=True, ts_hi=None):
+        """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids).
+        With ts_hi: intervals with tmin <= ts and tmax > ts_hi (the reference's 'loose' form)."""
         nodes = np.ascontiguousarray(nodes, dtype=np.int32)
         ts = np.ascontiguousarray(ts, dtype=np.int64)
         n = len(nodes)
         first = np.empty(n, np.int32)
         cnt = np.empty(n, np.int32)
         ids = np.empty((n, STATE_LIMIT), np.int32) if with_ids else None
-        self._ck(self.lib.rca_state_lookup(self.h, nodes.ctypes.data, ts.ctypes.data, n, 0, first.ctypes.data,
-                                           cnt.ctypes.data, ids.ctypes.data if with_ids else None))
+        if ts_hi is None:
+            self._ck(self.lib.rca_state_lookup(self.h, nodes.ctypes.data, ts.ctypes.data, n, 0, first.ctypes.data,
+                                               cnt.ctypes.data, ids.ctypes.data if with_ids else None))
+        else:
+            hi = np.ascontiguousarray(ts_hi, dtype=np.int64)
+            self._ck(self.lib.rca_state_window(self.h, nodes.ctypes.data, ts.ctypes.data, hi.ctypes.data, n, 0,
+                                               first.ctypes.data, cnt.ctypes.data, ids.ctypes.data if with_ids else None))
         return first, cnt, ids

@@ -1,0 +1,350 @@
+"""Drop-in for the reference's query executor (common/neo4j_query_executor.py:6-24).
+
+    GpuQueryExecutor(uri, user, password)      # same constructor shape
+        .run_query(query, parameters=None)     # -> list[Record], fully materialised
+        .close()
+
+`uri` names a snapshot instead of a bolt address:
+    snapshot://<name>            a Snapshot registered in this process with register_snapshot()
+    snapshot://<name>#metagraph  the schema graph derived from it (what the reference keeps in its
+                                 second Neo4j database, test_all.py:21)
+    synth://?objects=N&events=M&seed=S[#metagraph]   a generated graph (synth.generate)
+
+`QueryRunner` is the host logic between Cypher text and the engine: it compiles the text
+(cypher.py), resolves labels / kinds / edge types against the snapshot, asks a backend for paths,
+chains and state intervals, and shapes the rows into Records.  The product has one backend,
+`GpuBackend` (the C ABI); there is no CPU backend in this package.
+"""
+from __future__ import annotations
+
+import itertools
+from urllib.parse import parse_qs, urlparse
+
+import numpy as np
+
+from . import cypher as cy
+from . import engine as E
+from .graphtypes import Node, Path, Record, Relationship
+from .props import ts_to_ms
+
+
+class ServiceUnavailable(Exception):
+    """Raised by the constructor when the uri cannot be resolved - the counterpart of the driver's
+    verify_connectivity() failing (neo4j_query_executor.py:9)."""
+
+
+_REGISTRY: dict = {}
+
+
+def register_snapshot(name: str, snap) -> None:
+    _REGISTRY[name] = snap
+
+
+def resolve_snapshot(uri: str):
+    u = urlparse(uri)
+    if u.scheme == "snapshot":
+        name = u.netloc or u.path.lstrip("/")
+        if name not in _REGISTRY:
+            raise ServiceUnavailable(f"no snapshot registered under {name!r} (uri {uri!r})")
+        snap = _REGISTRY[name]
+    elif u.scheme == "synth":
+        q = parse_qs(u.query)
+        key = ("synth", u.query)
+        if key not in _REGISTRY:
+            from . import synth
+            _REGISTRY[key] = synth.generate(int(q.get("objects", ["1000"])[0]),
+                                            int(q["events"][0]) if "events" in q else None,
+                                            int(q.get("seed", ["20240001"])[0]))
+        snap = _REGISTRY[key]
+    else:
+        raise ServiceUnavailable(f"cannot resolve {uri!r}: expected snapshot://<name> or synth://?objects=..")
+    if u.fragment == "metagraph":
+        key = ("meta", id(snap))
+        if key not in _REGISTRY:
+            _REGISTRY[key] = snap.derive_metagraph()
+        snap = _REGISTRY[key]
+    elif u.fragment:
+        raise ServiceUnavailable(f"unknown fragment #{u.fragment} in {uri!r}")
+    return snap
+
+
+# ------------------------------------------------------------------------------------------ backend
+class GpuBackend:
+    """Executes plans through the C ABI (engine.Engine).  The only backend of the product."""
+
+    def __init__(self, snap, device: int = 0):
+        self.snap = snap
+        self.engine = E.Engine(snap, device)
+
+    def close(self):
+        self.engine.close()
+
+    def varlen(self, seeds, direction, max_hops, min_hops, dest_kind, excl_kinds, inter_kinds, entity_only,
+               node_simple, pos_kind):
+        plan = E.varlen_plan(direction, max_hops, min_hops=min_hops, dest_kind=dest_kind, excl_kinds=excl_kinds,
+                             inter_kinds=inter_kinds, entity_only=entity_only, node_simple=node_simple,
+                             pos_kind=pos_kind)
+        return self.engine.expand(plan, np.ascontiguousarray(seeds, dtype=np.int32)).all_rows()
+
+    def chain(self, seeds, etypes, dirs):
+        res = self.engine.expand(E.chain_plan(etypes, dirs), np.ascontiguousarray(seeds, dtype=np.int32))
+        return res.rows(len(etypes))
+
+    def states(self, nodes, tmin_le, tmax_gt):
+        return self.engine.state_lookup(nodes, tmin_le, ts_hi=tmax_gt)
+
+
+# ------------------------------------------------------------------------------------------ runner
+class QueryRunner:
+    def __init__(self, snap, backend):
+        self.snap = snap
+        self.backend = backend
+        self._label = {k.label: i for i, k in enumerate(snap.kinds)}
+        self._kconst = [snap.props.kind_const_props(k) for k in range(snap.n_kinds)]
+
+    # -- public
+    def run(self, query, parameters=None):
+        params = dict(parameters or {})
+        plan = cy.compile_query(query, params)
+        if isinstance(plan, cy.NodeScanPlan):
+            return self._node_scan(plan, params)
+        if isinstance(plan, cy.VarLenPlan):
+            return self._varlen(plan, params)
+        if isinstance(plan, cy.ChainPlan):
+            return self._chain(plan, params)
+        if isinstance(plan, cy.StatePlan):
+            return self._state(plan, params)
+        raise cy.CypherSyntaxError("unsupported query")
+
+    # -- helpers
+    def _kinds_with(self, prop, value):
+        return [k for k in range(self.snap.n_kinds) if self._kconst[k].get(prop) == value]
+
+    def _project(self, ret, envs, params):
+        """RETURN items over a list of environments (var -> entity), DISTINCT and LIMIT applied."""
+        keys = [alias or src for (_, alias, src) in ret.items]
+        out, seen = [], set()
+        for env in envs:
+            vals = tuple(cy.eval_expr(e, env, params) for (e, _, _) in ret.items)
+            if ret.distinct:
+                try:
+                    if vals in seen:
+                        continue
+                    seen.add(vals)
+                except TypeError:
+                    pass
+            out.append(Record(keys, vals))
+            if ret.limit is not None and len(out) >= ret.limit:
+                break
+        return out
+
+    # -- S1 / S6
+    def _node_scan(self, plan, params):
+        s = self.snap
+        if plan.label is not None:
+            if plan.label not in self._label:
+                return []
+            ranges = [s.kind_range(self._label[plan.label])]
+            kinds = [self._label[plan.label]]
+        else:
+            ranges = [(0, s.n_nodes)]
+            kinds = list(range(s.n_kinds))
+        if plan.id_equals is not None:
+            cand = [v for k in kinds for v in s.props.find_by_id(k, plan.id_equals)]
+        else:
+            cand = itertools.chain.from_iterable(range(lo, hi) for lo, hi in ranges)
+
+        def envs():
+            for v in cand:
+                env = {plan.var: Node(s, v)}
+                if plan.where is None or cy.eval_expr(plan.where, env, params) is True:
+                    yield env
+        return self._project(plan.ret, envs(), params)
+
+    # -- S3a-d
+    def _varlen(self, plan, params):
+        s = self.snap
+        prop = plan.kind_prop
+        src_kinds = self._kinds_with(prop, plan.src_kind)
+        dest_kinds = self._kinds_with(prop, plan.dest_kind) if plan.dest_kind is not None else [-1]
+        if not src_kinds or not dest_kinds:
+            return []
+        excl = set()
+        if plan.excl_kinds:
+            # `not node.kind in [...]` is null - hence not true - for a node without the property
+            excl = {k for k in range(s.n_kinds) if self._kconst[k].get(prop) is None or self._kconst[k].get(prop) in plan.excl_kinds}
+        inter = [k for k in range(s.n_kinds) if self._kconst[k].get(prop) in plan.inter_kinds] if plan.inter_kinds else []
+        if plan.inter_kinds and not inter:
+            return []                                  # any(...) over kinds that do not exist is false
+        pos_sets = None
+        if plan.pos_kinds is not None:
+            pos_sets = [None if pk is None else self._kinds_with(prop, pk) for pk in plan.pos_kinds]
+            if any(ps is not None and not ps for ps in pos_sets):
+                return []
+        entity_only = bool(excl) and all(k in excl for k in range(s.n_kinds) if s.kinds[k].is_state)
+        seeds = np.concatenate([s.nodes_of_kind(k) for k in src_kinds])
+        paths = []
+        if pos_sets is not None:                       # fixed-length pattern: one run per combination of kinds
+            runs = [(pc[-1], list(pc)) for pc in itertools.product(*[ps if ps is not None else [-1] for ps in pos_sets])]
+        else:
+            runs = [(dk, None) for dk in dest_kinds]
+        for dk, pc in runs:
+            levels = self.backend.varlen(seeds, plan.direction, plan.max_hops, plan.min_hops, dk, sorted(excl), inter,
+                                         entity_only, plan.node_simple, pc)
+            for length, rows in levels.items():
+                for r in rows[:, :2 * length + 1].tolist():
+                    paths.append((tuple(r[:length + 1]), tuple(r[length + 1:])))
+        if len(runs) > 1:
+            paths = sorted(set(paths))
+
+        def envs():
+            for nodes, rels in paths:
+                p = Path([Node(s, v) for v in nodes], [Relationship(s, r) for r in rels])
+                env = {}
+                if plan.path_var:
+                    env[plan.path_var] = p
+                if plan.pos_kinds is not None:
+                    for name, n in zip(plan.node_vars, p.nodes):
+                        if name:
+                            env[name] = n
+                    for name, r in zip(plan.rel_vars, p.relationships):
+                        if name:
+                            env[name] = r
+                else:
+                    if plan.node_vars[0]:
+                        env[plan.node_vars[0]] = p.nodes[0]
+                    if plan.node_vars[1]:
+                        env[plan.node_vars[1]] = p.nodes[-1]
+                yield env
+        return self._project(plan.ret, envs(), params)
+
+    # -- S2 / S4
+    def _seed_nodes(self, plan, kind, params):
+        s = self.snap
+        lo, hi = s.kind_range(kind)
+        w = plan.seed_where
+        if w is None:
+            return np.arange(lo, hi, dtype=np.int32)
+        # fast path: <seed>.message CONTAINS <text> over the message arena
+        if w[0] == "cmp" and w[1] == "contains" and w[2] == ("prop", ("var", plan.seed_var), "message"):
+            text = cy.eval_expr(w[3], {}, params)
+            ids, msgs = s.props.messages()
+            if text is None:
+                return np.zeros(0, np.int32)
+            hit = [int(v) for v, m in zip(ids.tolist(), msgs) if lo <= v < hi and m is not None and text in m]
+            return np.array(hit, dtype=np.int32)
+        if w[0] == "cmp" and w[1] == "=" and w[2] == ("prop", ("var", plan.seed_var), "id"):
+            val = cy.eval_expr(w[3], {}, params)
+            return np.array(sorted(s.props.find_by_id(kind, val)), dtype=np.int32)
+        hit = [v for v in range(lo, hi) if cy.eval_expr(w, {plan.seed_var: Node(s, v)}, params) is True]
+        return np.array(hit, dtype=np.int32)
+
+    def _chain(self, plan, params):
+        s = self.snap
+        for lab in plan.labels.values():
+            if lab is not None and lab not in self._label:
+                return []
+        want = {v: (self._label[lab] if lab is not None else None) for v, lab in plan.labels.items()}
+        # candidate edge types per step, then every combination that forms one walk
+        cands = []
+        for st, (frm, to, d) in zip(plan.steps, plan.walk):
+            c = [t for t, e in enumerate(s.etypes)
+                 if e.rel_type in st.rel_types and (st.key is None or e.key == st.key)
+                 and want[st.start_var] in (None, e.src_kind) and want[st.end_var] in (None, e.dst_kind)]
+            cands.append(c)
+        combos = []
+
+        def rec(i, cur_kind, acc):
+            if i == len(plan.steps):
+                combos.append(list(acc))
+                return
+            d = plan.walk[i][2]
+            for t in cands[i]:
+                e = s.etypes[t]
+                near, far = (e.src_kind, e.dst_kind) if d == "out" else (e.dst_kind, e.src_kind)
+                if cur_kind is not None and near != cur_kind:
+                    continue
+                acc.append((t, near))
+                rec(i + 1, far, acc)
+                acc.pop()
+        rec(0, want[plan.seed_var], [])
+        col = {plan.seed_var: 0}
+        for i, (_, to, _) in enumerate(plan.walk):
+            col[to] = i + 1
+        L = len(plan.steps)
+        dirs = [d for (_, _, d) in plan.walk]
+        seeds_of = {k: self._seed_nodes(plan, k, params) for k in sorted({c[0][1] for c in combos})}
+        if plan.seed_limit is not None and seeds_of:
+            # WITH <seed> LIMIT n: which rows survive is unspecified in Cypher; the lowest node ids here
+            keep = np.sort(np.concatenate(list(seeds_of.values())))[:plan.seed_limit]
+            seeds_of = {k: v[np.isin(v, keep)] for k, v in seeds_of.items()}
+        all_rows = []
+        for combo in combos:
+            seeds = seeds_of[combo[0][1]]
+            if len(seeds) == 0:
+                continue
+            rows = self.backend.chain(seeds, [t for t, _ in combo], dirs)
+            if len(rows):
+                all_rows.append(rows)
+        if not all_rows:
+            return []
+        rows = np.concatenate(all_rows) if len(all_rows) > 1 else all_rows[0]
+
+        def envs():
+            for r in rows.tolist():
+                env = {v: Node(s, r[c]) for v, c in col.items()}
+                for i, st in enumerate(plan.steps):
+                    if st.rel_var:
+                        env[st.rel_var] = Relationship(s, r[L + 1 + i])
+                yield env
+        return self._project(plan.ret, envs(), params)
+
+    # -- S5 / S5'
+    def _state(self, plan, params):
+        s = self.snap
+        if plan.entity_label not in self._label:
+            return []
+        ek = self._label[plan.entity_label]
+        if plan.state_label is not None and plan.state_label not in self._label:
+            return []
+        ents = s.props.find_by_id(ek, plan.entity_id)
+        if not ents:
+            return []
+        try:
+            lo, hi = ts_to_ms(plan.lo), ts_to_ms(plan.hi)
+        except (ValueError, TypeError) as exc:
+            raise cy.CypherSyntaxError(
+                f"state query: {exc} - the engine compares timestamps as integers, which equals the reference's "
+                f"string comparison only for this fixed-width form") from None
+        nodes = np.array(ents, dtype=np.int32)
+        _, cnt, ids = self.backend.states(nodes, np.full(len(nodes), lo, np.int64), np.full(len(nodes), hi, np.int64))
+        found = []
+        for i in range(len(nodes)):
+            for sn in ids[i][:min(int(cnt[i]), ids.shape[1])].tolist():
+                if plan.state_label is None or int(s.kind_of(sn)) == self._label[plan.state_label]:
+                    found.append(sn)
+        found.sort()
+        envs = ({plan.entity_var: Node(s, int(nodes[0])), plan.state_var: Node(s, sn)} for sn in found)
+        return self._project(plan.ret, envs, params)
+
+
+# ------------------------------------------------------------------------------------------ executor
+class GpuQueryExecutor:
+    """Same surface as the reference's Neo4jQueryExecutor; `user` / `password` are accepted and
+    ignored (a snapshot has no authentication)."""
+
+    def __init__(self, uri, user=None, password=None, device: int = 0):
+        self.uri = uri
+        self.snapshot = resolve_snapshot(uri)          # raises ServiceUnavailable: 'verify_connectivity'
+        self.backend = GpuBackend(self.snapshot, device)
+        self.runner = QueryRunner(self.snapshot, self.backend)
+
+    def close(self):
+        if self.backend is not None:
+            self.backend.close()
+            self.backend = None
+
+    def run_query(self, query, parameters=None):
+        if self.backend is None:
+            raise ServiceUnavailable("executor is closed")
+        return self.runner.run(query, parameters)

@@ -63,6 +63,11 @@ class BaseProps:
         e = s.etypes[int(s.rel_et[r])]
         return {"key": e.key, "srcKind": s.kinds[e.src_kind].name, "destKind": s.kinds[e.dst_kind].name}
 
+    def kind_const_props(self, k):
+        """Properties that have the same value on every node of kind `k` (what lets a predicate
+        such as `n.kind = 'Pod'` be answered by kind, i.e. by node-id range)."""
+        return {}
+
     def find_by_id(self, kind_idx, id_str):
         """Nodes of kind `kind_idx` whose `id` property equals `id_str`."""
         lo, hi = self.snap.kind_range(kind_idx)
@@ -88,15 +93,31 @@ class MetaProps(BaseProps):
         k = self.snap.kinds[int(v)]
         return {"kind": k.name, "category": k.category}
 
+    def kind_const_props(self, k):
+        kd = self.snap.kinds[k]
+        return {"kind": kd.name, "category": kd.category}
+
 
 class TableProps(BaseProps):
     """Explicit per-node / per-relationship dictionaries (hand-made graphs in tests, dumps)."""
 
-    def __init__(self, snap, node_props, rel_props=None, node_labels=None):
+    def __init__(self, snap, node_props, rel_props=None, node_labels=None, kind_props=None):
         super().__init__(snap)
         self._n = node_props
         self._r = rel_props
         self._l = node_labels
+        self._k = kind_props
+
+    def kind_const_props(self, k):
+        if self._k is not None:
+            return self._k[k]
+        lo, hi = self.snap.kind_range(k)
+        if lo == hi:
+            return {}
+        common = dict(self._n[lo])
+        for v in range(lo + 1, hi):
+            common = {a: b for a, b in common.items() if self._n[v].get(a) == b}
+        return common
 
     def node_props(self, v):
         return self._n[int(v)]

@@ -290,6 +290,14 @@ class SynthProps(BaseProps):
             p["status"] = '{"phase": "%s"}' % ("Running", "Pending", "Failed")[j % 3]
         return p
 
+    def kind_const_props(self, k):
+        kind = self.snap.kinds[k]
+        if kind.is_state:
+            return {"kind": kind.name}
+        if kind.category == "NativeEntity":
+            return {"kind2": kind.name, "isNative": "true", "isAtomic": "false"}
+        return {"tag": kind.name, "isNative": "false", "isAtomic": "false"}
+
     @staticmethod
     def _name(kind, j):
         return f"{kind.name.lower()}-{j}"

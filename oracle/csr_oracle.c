@@ -236,15 +236,15 @@ int64_t orc_chain(const orc_graph_t *g, const int32_t *et, const int32_t *dir, i
 }
 
 /* HasState predicate, analyze_root_cause.py:70-79: for query i, intervals of entity nodes[i]
- * with tmin <= ts[i] < tmax.  first[i] = lowest matching STATE node id or -1, cnt[i] = number
+ * with tmin <= ts[i] and tmax > ts_hi[i] (ts_hi == ts: the strict form; :51-60 is the loose form).  first[i] = lowest matching STATE node id or -1, cnt[i] = number
  * of matches; ids (may be NULL) receives up to `limit` ids per query, -1 padded. */
-void orc_states(const orc_graph_t *g, const int32_t *nodes, const int64_t *ts, int64_t n, int limit,
+void orc_states(const orc_graph_t *g, const int32_t *nodes, const int64_t *ts, const int64_t *ts_hi, int64_t n, int limit,
                 int32_t *first, int32_t *cnt, int32_t *ids) {
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < n; i++) {
         int32_t v = nodes[i], c = 0, f = -1;
         for (int32_t j = g->st_off[v]; j < g->st_off[v + 1]; j++) {
-            if (g->st_tmin[j] <= ts[i] && g->st_tmax[j] > ts[i]) {
+            if (g->st_tmin[j] <= ts[i] && g->st_tmax[j] > ts_hi[i]) {
                 if (c == 0) f = g->st_node[j];
                 if (ids && c < limit) ids[i * limit + c] = g->st_node[j];
                 c++;

@@ -1,0 +1,59 @@
+"""TEST HELPER: the executor's backend interface implemented with the CPU oracle (oracle/csr.py).
+Lives under tests/ on purpose - the product package has no CPU backend."""
+import numpy as np
+
+
+class OracleBackend:
+    def __init__(self, snap):
+        from oracle.csr import CsrOracle
+        self.snap = snap
+        self.orc = CsrOracle(snap)
+
+    def close(self):
+        pass
+
+    def varlen(self, seeds, direction, max_hops, min_hops, dest_kind, excl_kinds, inter_kinds, entity_only,
+               node_simple, pos_kind):
+        levels, _ = self.orc.varlen(seeds, direction, max_hops, min_hops=min_hops, dest_kind=dest_kind,
+                                    excl_kinds=excl_kinds, inter_kinds=inter_kinds, entity_only=entity_only,
+                                    node_simple=node_simple, pos_kind=pos_kind)
+        return levels
+
+    def chain(self, seeds, etypes, dirs):
+        rows, _ = self.orc.chain(seeds, etypes, [{"out": 0, "in": 1}[d] for d in dirs])
+        return rows
+
+    def states(self, nodes, tmin_le, tmax_gt):
+        return self.orc.states(nodes, tmin_le, ts_hi=tmax_gt)
+
+
+def oracle_executor(snap):
+    """An object with run_query / close, like the executors, running on the oracle."""
+    from k8s_llm_rca_b200.executor import QueryRunner
+
+    class _Ex:
+        def __init__(self):
+            self.runner = QueryRunner(snap, OracleBackend(snap))
+
+        def run_query(self, query, parameters=None):
+            return self.runner.run(query, parameters)
+
+        def close(self):
+            pass
+    return _Ex()
+
+
+def record_key(rec):
+    """Canonical, comparable form of a Record (entities -> ids, paths -> id tuples)."""
+    from k8s_llm_rca_b200.graphtypes import Node, Path, Relationship
+    out = []
+    for v in rec:
+        if isinstance(v, Path):
+            out.append(("path",) + v.key())
+        elif isinstance(v, Node):
+            out.append(("node", v.id))
+        elif isinstance(v, Relationship):
+            out.append(("rel", v.id))
+        else:
+            out.append(("val", v))
+    return tuple(out)
