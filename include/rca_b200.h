@@ -120,7 +120,9 @@ const char *rca_last_error(const rca_engine_t *e);
 int rca_set_stream(rca_engine_t *e, uint64_t cuda_stream);
 /* Plans with at most `max_seeds` seeds run one fused launch per hop (fewest launches: the
  * per-incident latency case); larger seed sets run count / scan / fill launches per hop (no
- * inter-tile waiting: the throughput case).  Results are identical either way.  Default 16384.
+ * inter-tile waiting: the throughput case).  Results are identical either way.  Defaults: 16384
+ * for variable-length plans, 2^20 for typed chains (whose tiles are uniform, so the fused launch
+ * suits them much longer); this call sets both.
  * No counterpart in the reference: it is a tuning knob of this engine. */
 int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds);
 /* pre-size the scratch arenas: frontier entries (16 B each) and output words (4 B each) */

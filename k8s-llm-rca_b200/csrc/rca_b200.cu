@@ -53,7 +53,8 @@ struct rca_engine {
     unsigned long long ccap = 0;
     ulonglong2 *gsum = nullptr, *gscan = nullptr;   // split path: group sums (zeroed per call) and their scan
     unsigned long long gcap = 0;
-    long long fused_max_seeds = 16384;    // up to this many seeds a plan runs one fused launch per level
+    long long fused_max_seeds = 16384;    // up to this many seeds a variable-length plan runs one fused launch per level
+    long long chain_fused_max_seeds = 1 << 20;   // typed chains have uniform tiles: the fused launch suits them far longer
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
     unsigned char *ptab = nullptr, *h_ptab = nullptr;   // plan table (rca_kernels.cuh: kPt*)
@@ -237,8 +238,8 @@ extern "C" int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t ou
 // direction, through kinds the plan does not exclude, leads from kind k to dest_kind
 static void reach_bits(const rca_engine *e, const rca_plan_t *pl, unsigned *reach) {
     const int nk = e->n_kinds;
-    bool constrained = false;
-    for (int i = 0; i <= pl->max_hops; i++) constrained |= pl->pos_kind[i] >= 0;
+    bool constrained = false;                       // a required kind at position 0 only restricts the seeds
+    for (int i = 1; i <= pl->max_hops; i++) constrained |= pl->pos_kind[i] >= 0;
     if (!pl->prune || pl->dest_kind < 0 || constrained) {
         for (int k = 0; k < nk; k++) reach[k] = 0xffu;
         return;
@@ -270,52 +271,58 @@ static void reach_bits(const rca_engine *e, const rca_plan_t *pl, unsigned *reac
     }
 }
 
-// Arrival-aware refinement of reach_bits.  An arrival a = (edge type t, d) means the path's last
-// hop followed a relationship of type t along (d = 0) or against (d = 1) its stored direction.
-// rows[s][2t+d] = 1 if such a path, now s hops long, may still end at dest_kind within L hops.
-// The one thing this knows beyond kind-level reachability: the next hop cannot go straight back
-// over type t when t is functional on that side (no node has two such relationships), because
-// the only candidate is the relationship just used, and a MATCH pattern never reuses one.
-// Returns false (rows all 1) when the refinement does not apply.
-static bool arrival_reach(const rca_engine *e, const rca_plan_t *pl, int L, unsigned char *rows) {
-    const int nt = e->n_etypes, A = 2 * nt;
-    std::memset(rows, 1, (size_t)(RCA_MAX_HOPS + 1) * kArrBytes);
-    bool constrained = false;
-    for (int i = 0; i <= L; i++) constrained |= pl->pos_kind[i] >= 0;
-    if (!pl->prune || pl->dest_kind < 0 || constrained || nt > 256 || !e->rel_et) return false;
-    auto head = [&](int a) { return (a & 1) ? e->et_src[a >> 1] : e->et_dst[a >> 1]; };
-    auto tail = [&](int a) { return (a & 1) ? e->et_dst[a >> 1] : e->et_src[a >> 1]; };
-    auto allowed = [&](int a) {
+// Arrival model shared by the pruning tables.  An arrival a = 2*t + d means the path's last hop
+// followed a relationship of edge type t along (d = 0) or against (d = 1) its stored direction.
+struct ArrivalModel {
+    const rca_engine *e;
+    const rca_plan_t *pl;
+    int head(int a) const { return (a & 1) ? e->et_src[a >> 1] : e->et_dst[a >> 1]; }
+    int tail(int a) const { return (a & 1) ? e->et_dst[a >> 1] : e->et_src[a >> 1]; }
+    bool allowed(int a) const {
         const int t = a >> 1, d = a & 1;
         if (pl->entity_only && e->et_cls[t]) return false;
         if (pl->direction == RCA_DIR_OUT && d) return false;
         if (pl->direction == RCA_DIR_IN && !d) return false;
         return true;
-    };
-    auto step_ok = [&](int a, int b) {           // may arrival b follow arrival a ?
+    }
+    // may arrival b follow arrival a ?  The one thing this knows beyond kinds: the next hop cannot go
+    // straight back over the same edge type when that type is functional on that side (no node has
+    // two such relationships) - the only candidate is the relationship just used, and a MATCH
+    // pattern never reuses one.
+    bool step_ok(int a, int b) const {
         if (!allowed(b) || tail(b) != head(a)) return false;
-        if ((b >> 1) == (a >> 1) && (b & 1) != (a & 1)) {     // straight back over the same type
+        if ((b >> 1) == (a >> 1) && (b & 1) != (a & 1)) {
             const int t = a >> 1;
             const int deg = (a & 1) ? e->et_max_out[t] : e->et_max_in[t];
             if (deg <= 1) return false;
         }
         return true;
-    };
+    }
+};
+
+// rows[s][a] = 1 if a path that arrived by a and is now s hops long may still end at dest_kind within
+// L hops (arrival-aware refinement of reach_bits).  Returns false (rows all 1) when it does not apply.
+static bool arrival_reach(const rca_engine *e, const rca_plan_t *pl, int L, unsigned char *rows) {
+    const int nt = e->n_etypes, A = 2 * nt;
+    std::memset(rows, 1, (size_t)(RCA_MAX_HOPS + 1) * kArrBytes);
+    bool constrained = false;
+    for (int i = 1; i <= L; i++) constrained |= pl->pos_kind[i] >= 0;
+    if (!pl->prune || pl->dest_kind < 0 || constrained || nt > 256 || !e->rel_et) return false;
+    const ArrivalModel m{e, pl};
     std::vector<unsigned char> prev(A, 0), cur(A, 0);
     const bool dest_ok = !pl->kind_excl[pl->dest_kind];
     for (int r = 1; r <= L; r++) {
         for (int a = 0; a < A; a++) {
             unsigned char hit = prev[a];
             for (int b = 0; b < A && !hit; b++) {
-                if (!step_ok(a, b)) continue;
-                const int hb = head(b);
+                if (!m.step_ok(a, b)) continue;
+                const int hb = m.head(b);
                 if (hb == pl->dest_kind && dest_ok) hit = 1;
                 else if (r > 1 && !pl->kind_excl[hb] && prev[b]) hit = 1;
             }
             cur[a] = hit;
         }
-        // a path s = L - r hops long has r hops left
-        unsigned char *row = rows + (size_t)(L - r) * kArrBytes;
+        unsigned char *row = rows + (size_t)(L - r) * kArrBytes;      // a path L - r hops long has r hops left
         for (int a = 0; a < A; a++) row[a] = cur[a];
         prev = cur;
     }
@@ -374,7 +381,7 @@ static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
 
 extern "C" int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds) {
     if (!e || max_seeds < 0) return RCA_ERR_ARG;
-    e->fused_max_seeds = max_seeds;
+    e->fused_max_seeds = e->chain_fused_max_seeds = max_seeds;
     return RCA_OK;
 }
 
@@ -391,7 +398,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     const bool varlen = pl->kind == RCA_PLAN_VARLEN;
     const int L = varlen ? pl->max_hops : pl->n_steps;
     const int mode = !varlen ? kModeChain : (pl->node_simple ? kModeSimple : kModeRelUnique);
-    const bool fused = n_seeds <= e->fused_max_seeds;
+    const bool fused = n_seeds <= (varlen ? e->fused_max_seeds : e->chain_fused_max_seeds);
 
     // ---- seeds (and their timestamps) on the device
     const int *d_seeds = seeds;
@@ -439,6 +446,43 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         std::memcpy(t + kPtLut, e->kind_lut.data(), kLutEntries);
         arr_prune = varlen && arrival_reach(e, pl, L, t + kPtArr);
         CK(cudaMemcpyAsync(e->ptab, t, kPtBytes, cudaMemcpyHostToDevice, e->stream));
+    }
+
+    // ---- levels that can run as typed sub-launches: when only one or two (edge type, direction)
+    //      pairs can emit or continue at a level (always the case at the last level of a query with
+    //      a destination kind), scanning full adjacency rows is wasted work - the typed-range tables
+    //      lead straight to the useful relationships.  Result-neutral; split path only.
+    struct Sub { int t, d; };
+    std::vector<std::vector<Sub>> subs(L + 1);
+    std::vector<char> level_typed(L + 1, 0), level_dead(L + 1, 0);
+    if (varlen && !fused && arr_prune && mode == kModeSimple) {
+        const unsigned char *arr = e->h_ptab + kPtArr, *act = e->h_ptab + kPtAct;
+        const ArrivalModel m{e, pl};
+        const int A = 2 * e->n_etypes;
+        // forward pass: which arrivals can occur at depth s at all.  Depth 1: any allowed hop leaving a
+        // kind the seeds may have; depth s+1: any hop that may follow an arrival that continues at depth s.
+        std::vector<char> can(A, 0), nxt(A, 0);
+        for (int a = 0; a < A; a++) {
+            if (!m.allowed(a)) continue;
+            const int near = m.tail(a);
+            can[a] = !(act[0 * RCA_MAX_KINDS + near] & kActDead);          // row 0 holds the seed rules
+        }
+        for (int s = 1; s <= L; s++) {
+            std::fill(nxt.begin(), nxt.end(), 0);
+            for (int a = 0; a < A; a++) {
+                if (!can[a]) continue;
+                const unsigned k = act[s * RCA_MAX_KINDS + m.head(a)];
+                if (k & kActDead) continue;
+                const bool emit = (k & kActEmit) != 0;
+                const bool cont = (k & kActCont) && arr[(size_t)s * kArrBytes + a];
+                if (emit || cont) subs[s].push_back(Sub{a >> 1, a & 1});
+                if (cont)
+                    for (int b = 0; b < A; b++) if (!nxt[b] && m.step_ok(a, b)) nxt[b] = 1;
+            }
+            can = nxt;
+            level_dead[s] = subs[s].empty();
+            level_typed[s] = !subs[s].empty() && subs[s].size() <= 2;
+        }
     }
 
     // ---- scratch arenas: keep what earlier calls grew to, else a guess from the seed count
@@ -514,23 +558,42 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             p.ptab = e->ptab;
             p.rel_et = e->rel_et; p.arr_prune = arr_prune;
             p.st_off = e->st_off; p.st_rec = e->st_rec;
-            const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
             const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
             const long long first = std::max<long long>(1, (n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
             if (fused) {
+                const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
                 int grid = max_grid(e, ks.fused, dyn);
                 if (s == 1) grid = (int)std::min<long long>(grid, first);
                 ks.fused<<<grid, kThreads, dyn, e->stream>>>(p);
                 launches++;
+            } else if (level_dead[s]) {
+                // no (edge type, direction) can emit or continue here: the level and all later ones are empty
             } else {
-                int grid = max_grid(e, ks.count, dyn);
-                if (s == 1) grid = (int)std::min<long long>(grid, first);
-                ks.count<<<grid, kThreads, dyn, e->stream>>>(p);
-                scan_groups<<<1, 1024, 0, e->stream>>>(p);
-                grid = max_grid(e, ks.fill, dyn);
-                if (s == 1) grid = (int)std::min<long long>(grid, first);
-                ks.fill<<<grid, kThreads, dyn, e->stream>>>(p);
-                launches += 3;
+                const int n_sub = level_typed[s] ? (int)subs[s].size() : 1;
+                for (int j = 0; j < n_sub; j++) {
+                    int sdir = dir;
+                    if (level_typed[s]) {             // one typed step: ranges of (type, direction) over its near kind
+                        const int t = subs[s][j].t;
+                        sdir = subs[s][j].d ? RCA_DIR_IN : RCA_DIR_OUT;
+                        const int rowk = sdir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
+                        p.typed = 1;
+                        p.rng = (sdir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
+                        p.row_lo = e->kind_start[rowk];
+                        p.row_hi = e->kind_start[rowk + 1];
+                        p.adj2 = e->in_adj;
+                    }
+                    p.sub = j;
+                    const KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
+                    if (j) CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
+                    int grid = max_grid(e, ks.count, dyn);
+                    if (s == 1) grid = (int)std::min<long long>(grid, first);
+                    ks.count<<<grid, kThreads, dyn, e->stream>>>(p);
+                    scan_groups<<<1, 1024, 0, e->stream>>>(p);
+                    grid = max_grid(e, ks.fill, dyn);
+                    if (s == 1) grid = (int)std::min<long long>(grid, first);
+                    ks.fill<<<grid, kThreads, dyn, e->stream>>>(p);
+                    launches += 3;
+                }
             }
             CK(cudaGetLastError());
             CK(cudaEventRecord(e->ev_lv[s], e->stream));

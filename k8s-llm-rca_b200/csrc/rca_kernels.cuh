@@ -82,6 +82,7 @@ struct Ctl {                          // device control block, one per engine
     unsigned long long F[kLv];        // frontier size per level (level s occupies arena entries sum F[1..s-1] ..)
     unsigned long long N[kLv];        // rows emitted per level  (level s occupies output words sum N[j]*row_len[j] ..)
     unsigned long long E[kLv];        // candidates scanned per level
+    unsigned long long subF, subN;    // split path: entries / rows written by earlier sub-launches of the level
     unsigned int ticket[kLv];         // fused path: tile tickets
     unsigned int overflow;            // bit0 frontier arena, bit1 output arena
     unsigned int pad;
@@ -98,6 +99,7 @@ struct LevelParams {
     int n_nodes;
     // plan
     int s;                            // level being produced (1..)
+    int sub;                          // a level may run as several typed sub-launches (0, 1, ..): see rca_b200.cu
     int chain_flag;                   // chain plans: 1 = every candidate continues, 2 = every candidate is a row
     int need_inter;                   // emit only if an interior node so far is of an intermediate kind
     int with_states;
@@ -558,11 +560,15 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
         __syncthreads();
     }
     if (tid == 0) {
-        ctl->F[s] = s_run[0];
-        ctl->N[s] = s_run[1];
+        // sub-launch 0 starts the level; later ones append after what the earlier ones wrote
+        const unsigned long long base_f = p.sub ? ctl->F[s] : 0ull, base_n = p.sub ? ctl->N[s] : 0ull;
+        ctl->subF = base_f;
+        ctl->subN = base_n;
+        ctl->F[s] = base_f + s_run[0];
+        ctl->N[s] = base_n + s_run[1];
         unsigned ov = 0;
-        if (fb_s + s_run[0] > p.fcap) ov |= 1u;
-        if (ob_s + s_run[1] * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
+        if (fb_s + base_f + s_run[0] > p.fcap) ov |= 1u;
+        if (ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (ov) ctl->overflow = ov;
     }
 }
@@ -574,7 +580,9 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fill_level(const __grid_co
     __shared__ TablesSm tsm;
     __shared__ unsigned long long s_fb[kLv];
     if (overflow_seen(p.ctl)) return;
-    const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
+    LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
+    c.fb_s += p.ctl->subF;                            // after the earlier sub-launches of this level
+    c.ob_s += p.ctl->subN * (unsigned long long)p.row_len;
     const unsigned nwarps = gridDim.x * kWarps;
     for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
         const unsigned long long slot = c.slot0 + tile, g = slot / kGroup;

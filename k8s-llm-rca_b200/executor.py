@@ -186,6 +186,8 @@ class QueryRunner:
         paths = []
         if pos_sets is not None:                       # fixed-length pattern: one run per combination of kinds
             runs = [(pc[-1], list(pc)) for pc in itertools.product(*[ps if ps is not None else [-1] for ps in pos_sets])]
+        elif len(src_kinds) == 1:                      # all seeds are of one kind: say so (it sharpens the pruning)
+            runs = [(dk, [src_kinds[0]] + [-1] * plan.max_hops) for dk in dest_kinds]
         else:
             runs = [(dk, None) for dk in dest_kinds]
         for dk, pc in runs:

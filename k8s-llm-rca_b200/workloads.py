@@ -29,8 +29,10 @@ class Config3:
         self.max_hops = max_hops
         K = s.kind_index
         self.excl = [K("Event"), K("Namespace")]
+        # position 0 is fixed to Pod: it only restricts the seeds, and lets the schema-level pruning start
+        # from the kind the seeds really have
         self.varlen = E.varlen_plan("und", max_hops, dest_kind=K("Node"), excl_kinds=self.excl, entity_only=True,
-                                    with_states=with_states)
+                                    pos_kind=[K("Pod")], with_states=with_states)
         L = s.label_index
 
         def et(rel, a, b, key):
