@@ -236,11 +236,13 @@ struct WarpSm {
     int root[kTile];                  // seed index of the path
     int q_o[kQueue], q_v[kQueue], q_r[kQueue];
 };
-__host__ __device__ constexpr int warp_smem_ints(int s) { return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile; }
+// ... then a staging area for 32 finished rows (3s+3 words each at most), so that rows leave the SM
+// as whole 128 B lines instead of 4-byte stores scattered at row stride
+__host__ __device__ constexpr int warp_smem_ints(int s) { return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile + kTile * (3 * s + 3); }
 
 struct Warp {                         // a warp's view of its tile
     WarpSm *W;
-    int *anc_n, *anc_r;
+    int *anc_n, *anc_r, *stage;
     int lane;
     unsigned lt;
 };
@@ -364,34 +366,49 @@ __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, c
     return fl;
 }
 
-// Emit queue entries 0..n-1 as rows run_e .. run_e+n-1 (one row per lane).
+// Emit queue entries 0..n-1 as rows run_e .. run_e+n-1 (one row per lane; called by the whole warp).
+// State probes are shared: rows written together are siblings (same seed, usually the same second
+// node), so per column the lanes that hold the same node id elect one lane to probe and take its
+// answer by shuffle.
 __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, int n, unsigned long long ob_s,
                                            unsigned long long run_e) {
-    const int s = p.s, q = s - 1;
-    if (w.lane < n) {
-        const WarpSm &W = *w.W;
-        const int o = W.q_o[w.lane], v = W.q_v[w.lane], r = W.q_r[w.lane];
-        const unsigned long long w0 = ob_s + (run_e + w.lane) * (unsigned long long)p.row_len;
-        if (w0 + p.row_len <= p.ocap) {
-            int *row = p.out + w0;
-            for (int d = 0; d <= q; d++) row[d] = w.anc_n[d * kTile + o];
-            row[s] = v;
-            for (int d = 1; d <= q; d++) row[s + d] = w.anc_r[d * kTile + o];
-            row[2 * s] = r;
-            if (p.with_states) {
-                const long long ts = __ldg(p.seed_ts + W.root[o]);
-                unsigned miss = 0;
-                for (int d = 0; d <= s; d++) {
-                    int first, cnt;
-                    const int nd = (d <= q) ? w.anc_n[d * kTile + o] : v;
-                    state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
-                    row[2 * s + 1 + d] = first;
-                    miss |= (cnt == 0 ? 1u : 0u) << d;
-                }
-                row[3 * s + 2] = (int)miss;
+    const int s = p.s, q = s - 1, rl = p.row_len;
+    const WarpSm &W = *w.W;
+    const bool active = w.lane < n;
+    const unsigned long long w0 = ob_s + run_e * (unsigned long long)rl;       // first word of the n rows
+    if (w0 + (unsigned long long)n * rl > p.ocap) return;        // overflow was flagged with the counts: the run is void
+    int o = 0, v = 0, r = 0;
+    int *row = w.stage + w.lane * rl;
+    if (active) {
+        o = W.q_o[w.lane]; v = W.q_v[w.lane]; r = W.q_r[w.lane];
+        for (int d = 0; d <= q; d++) row[d] = w.anc_n[d * kTile + o];
+        row[s] = v;
+        for (int d = 1; d <= q; d++) row[s + d] = w.anc_r[d * kTile + o];
+        row[2 * s] = r;
+    }
+    if (p.with_states) {
+        const long long ts = active ? __ldg(p.seed_ts + W.root[o]) : 0;
+        unsigned miss = 0;
+        for (int d = 0; d <= s; d++) {
+            const int nd = active ? ((d <= q) ? w.anc_n[d * kTile + o] : v) : -1;
+            // same node AND same timestamp -> same answer (rows of one seed share the timestamp)
+            const unsigned same = __match_any_sync(0xffffffffu, nd) & __match_any_sync(0xffffffffu, ts);
+            const int leader = __ffs(same) - 1;
+            int first = -1, cnt = 0;
+            if (w.lane == leader && nd >= 0) state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
+            first = __shfl_sync(0xffffffffu, first, leader);
+            cnt = __shfl_sync(0xffffffffu, cnt, leader);
+            if (active) {
+                row[2 * s + 1 + d] = first;
+                miss |= (cnt == 0 ? 1u : 0u) << d;
             }
         }
+        if (active) row[3 * s + 2] = (int)miss;
     }
+    __syncwarp();
+    int *dst = p.out + w0;
+    for (int k = w.lane; k < n * rl; k += 32) dst[k] = w.stage[k];              // the n rows are contiguous in the output
+    __syncwarp();
 }
 
 // Walk the tile's windows, classify, and write the survivors starting at the tile's bases.
@@ -486,6 +503,7 @@ __device__ __forceinline__ LevelCtx level_setup(const LevelParams &p, TablesSm &
     c.w.W = reinterpret_cast<WarpSm *>(s_dyn + (tid >> 5) * warp_smem_ints(s));
     c.w.anc_n = reinterpret_cast<int *>(c.w.W + 1);
     c.w.anc_r = c.w.anc_n + s * kTile;
+    c.w.stage = c.w.anc_r + s * kTile;
     unsigned long long fb_s = 0, ob_s = 0;
     for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
     c.fb_s = fb_s; c.ob_s = ob_s;
