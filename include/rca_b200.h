@@ -153,6 +153,20 @@ int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, i
 int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt, int64_t n,
                      int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
 
+/* Message arena for rca_text_contains: n_msgs UTF-8 strings, concatenated in `bytes`, message i =
+ * bytes[off[i] .. off[i+1]), belonging to node node_ids[i] (ascending node ids give 'lowest id first'
+ * answers).  Copied to the device; replaces nothing in the reference - there the text lives in Neo4j. */
+int rca_text_load(rca_engine_t *e, const uint8_t *bytes, const int64_t *off, const int32_t *node_ids, int64_t n_msgs);
+/* replaces the predicate `N1.message CONTAINS $message` of find_srckind_metapath_neo4j.py:78 and
+ * `evt.message CONTAINS <msg>` of generate_query.py:225, for n_pat patterns at once (case-sensitive
+ * byte-wise substring test).  out_first_node[i] = lowest node id whose message contains pattern i, or
+ * -1 (the canonical answer to 'WITH evt LIMIT 1').  out_pairs (nullable): up to pairs_cap (pattern
+ * index, node id) pairs in unspecified order; *n_pairs = matches found, which may exceed pairs_cap
+ * (the list is then truncated - call again with a larger buffer).  An empty pattern matches every
+ * message; it is reported through out_first_node only. */
+int rca_text_contains(rca_engine_t *e, const uint8_t *pat_bytes, const int64_t *pat_off, int64_t n_pat,
+                      int32_t *out_first_node, int32_t *out_pairs, int64_t pairs_cap, int64_t *n_pairs);
+
 /* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
  * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory
  * that every GPU which loads the library keeps until the process exits. */

@@ -62,6 +62,10 @@ struct rca_engine {
     long long seeds_cap = 0;
     long long *ts_buf = nullptr;
     long long ts_cap = 0;
+    unsigned char *msg_bytes = nullptr;   // message arena for rca_text_contains
+    long long *msg_off = nullptr;
+    std::vector<int> msg_node;            // message index -> node id (host)
+    long long n_msgs = 0;
     void *io_buf = nullptr;               // staging for rca_state_lookup with host buffers
     size_t io_cap = 0;
     // last result
@@ -195,7 +199,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
                    e->st_off, e->st_rec, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
-                   e->seeds_buf, e->ts_buf, e->io_buf};
+                   e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
     if (e->h_ptab) cudaFreeHost(e->h_ptab);
@@ -715,6 +719,126 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
 extern "C" int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt,
                                 int64_t n, int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
     return state_query(e, "rca_state_window", nodes, tmin_le, tmax_gt, n, on_device, out_first, out_cnt, out_ids);
+}
+
+// ---- message CONTAINS on the device
+extern "C" int rca_text_load(rca_engine_t *e, const uint8_t *bytes, const int64_t *off, const int32_t *node_ids, int64_t n_msgs) {
+    if (!e) return RCA_ERR_ARG;
+    if (n_msgs < 0 || (n_msgs > 0 && (!bytes || !off || !node_ids))) return fail(e, RCA_ERR_ARG, "rca_text_load: null argument");
+    if (n_msgs > 0x7ffffff0LL) return fail(e, RCA_ERR_ARG, "rca_text_load: too many messages");
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    if (e->msg_bytes) { CK(cudaFree(e->msg_bytes)); e->msg_bytes = nullptr; }
+    if (e->msg_off) { CK(cudaFree(e->msg_off)); e->msg_off = nullptr; }
+    e->n_msgs = 0;
+    const long long total = n_msgs ? off[n_msgs] : 0;
+    CK(upload(&e->msg_bytes, bytes, (size_t)total));
+    CK(upload(&e->msg_off, off, (size_t)n_msgs + 1));
+    e->msg_node.assign(node_ids, node_ids + n_msgs);
+    e->n_msgs = n_msgs;
+    return RCA_OK;
+}
+
+extern "C" int rca_text_contains(rca_engine_t *e, const uint8_t *pat_bytes, const int64_t *pat_off, int64_t n_pat,
+                                 int32_t *out_first_node, int32_t *out_pairs, int64_t pairs_cap, int64_t *n_pairs) {
+    if (!e) return RCA_ERR_ARG;
+    if (n_pat < 0 || (n_pat > 0 && (!pat_bytes || !pat_off || !out_first_node)) || pairs_cap < 0 || (pairs_cap > 0 && !out_pairs))
+        return fail(e, RCA_ERR_ARG, "rca_text_contains: null argument");
+    if (n_pairs) *n_pairs = 0;
+    if (n_pat == 0) return RCA_OK;
+    CK(cudaSetDevice(e->device));
+    // distinct lengths, their top powers, and the hash table of the patterns (host, cold path)
+    std::vector<int> lens;
+    std::vector<unsigned long long> hashes((size_t)n_pat);
+    long long pairs_found = 0;
+    std::vector<int> first((size_t)n_pat, 0x7fffffff);
+    std::vector<int> host_pairs;
+    for (int64_t i = 0; i < n_pat; i++) {
+        const long long len = pat_off[i + 1] - pat_off[i];
+        if (len < 0 || len > 0x7fffffff) return fail(e, RCA_ERR_ARG, "rca_text_contains: bad pattern offsets");
+        unsigned long long h = 0;
+        for (long long k = 0; k < len; k++) h = h * kRkBase + pat_bytes[pat_off[i] + k];
+        hashes[i] = h;
+        if (len > 0) lens.push_back((int)len);
+    }
+    std::sort(lens.begin(), lens.end());
+    lens.erase(std::unique(lens.begin(), lens.end()), lens.end());
+    std::vector<unsigned long long> pow_top(lens.size());
+    for (size_t d = 0; d < lens.size(); d++) {
+        unsigned long long v = 1;
+        for (int k = 1; k < lens[d]; k++) v *= kRkBase;
+        pow_top[d] = v;
+    }
+    unsigned tsize = 64;
+    while (tsize < 4 * (unsigned long long)n_pat) tsize <<= 1;
+    std::vector<unsigned long long> tab_hash(tsize, 0);
+    std::vector<int> tab_pat(tsize, -1);
+    for (int64_t i = 0; i < n_pat; i++) {
+        const int len = (int)(pat_off[i + 1] - pat_off[i]);
+        if (len == 0) continue;                               // the empty string is contained in every message
+        unsigned long long x = hashes[i] ^ ((unsigned long long)len * 0x9e3779b97f4a7c15ull);
+        x ^= x >> 29; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 32;
+        unsigned sl = (unsigned)x & (tsize - 1);
+        while (tab_pat[sl] >= 0) sl = (sl + 1) & (tsize - 1);
+        tab_pat[sl] = (int)i;
+        tab_hash[sl] = hashes[i];
+    }
+    // one staging allocation for everything this call needs on the device
+    const size_t pbytes = (size_t)pat_off[n_pat];
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    size_t o_pat = 0, o_poff = al(pbytes), o_lens = o_poff + al((n_pat + 1) * 8), o_pow = o_lens + al(lens.size() * 4 + 4),
+           o_th = o_pow + al(lens.size() * 8 + 8), o_tp = o_th + al((size_t)tsize * 8), o_first = o_tp + al((size_t)tsize * 4),
+           o_np = o_first + al((size_t)n_pat * 4), o_pairs = o_np + 256, need = o_pairs + al((size_t)pairs_cap * 8);
+    if (need > e->io_cap) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->io_buf) CK(cudaFree(e->io_buf));
+        e->io_buf = nullptr; e->io_cap = 0;
+        CK(cudaMalloc(&e->io_buf, need));
+        e->io_cap = need;
+    }
+    char *b = (char *)e->io_buf;
+    CK(cudaMemcpyAsync(b + o_pat, pat_bytes, pbytes, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_poff, pat_off, (n_pat + 1) * 8, cudaMemcpyHostToDevice, e->stream));
+    if (!lens.empty()) {
+        CK(cudaMemcpyAsync(b + o_lens, lens.data(), lens.size() * 4, cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemcpyAsync(b + o_pow, pow_top.data(), lens.size() * 8, cudaMemcpyHostToDevice, e->stream));
+    }
+    CK(cudaMemcpyAsync(b + o_th, tab_hash.data(), (size_t)tsize * 8, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_tp, tab_pat.data(), (size_t)tsize * 4, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_first, first.data(), (size_t)n_pat * 4, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemsetAsync(b + o_np, 0, 8, e->stream));
+    unsigned long long found = 0;
+    if (!lens.empty() && e->n_msgs > 0) {
+        TextParams tp;
+        tp.msg = e->msg_bytes; tp.msg_off = e->msg_off; tp.n_msgs = e->n_msgs;
+        tp.pat = (const unsigned char *)(b + o_pat); tp.pat_off = (const long long *)(b + o_poff);
+        tp.lens = (const int *)(b + o_lens); tp.pow_top = (const unsigned long long *)(b + o_pow); tp.n_lens = (int)lens.size();
+        tp.tab_hash = (const unsigned long long *)(b + o_th); tp.tab_pat = (const int *)(b + o_tp); tp.tab_mask = tsize - 1;
+        tp.first = (int *)(b + o_first); tp.pairs = (int2 *)(b + o_pairs); tp.cap = (unsigned long long)pairs_cap;
+        tp.n_pairs = (unsigned long long *)(b + o_np);
+        const long long threads = e->n_msgs * (long long)lens.size();
+        contains_scan<<<(unsigned)((threads + 255) / 256), 256, 0, e->stream>>>(tp);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(first.data(), b + o_first, (size_t)n_pat * 4, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaMemcpyAsync(&found, b + o_np, 8, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        const unsigned long long got = std::min<unsigned long long>(found, (unsigned long long)pairs_cap);
+        if (got) {
+            CK(cudaMemcpyAsync(out_pairs, b + o_pairs, got * 8, cudaMemcpyDeviceToHost, e->stream));
+            CK(cudaStreamSynchronize(e->stream));
+            for (unsigned long long k = 0; k < got; k++) out_pairs[2 * k + 1] = e->msg_node[out_pairs[2 * k + 1]];   // message index -> node id
+        }
+    } else {
+        CK(cudaStreamSynchronize(e->stream));
+    }
+    pairs_found = (long long)found;
+    for (int64_t i = 0; i < n_pat; i++) {
+        const bool empty = pat_off[i + 1] == pat_off[i];
+        if (empty) out_first_node[i] = e->n_msgs ? e->msg_node[0] : -1;      // callers expand 'every message' themselves
+        else out_first_node[i] = first[i] == 0x7fffffff ? -1 : e->msg_node[first[i]];
+    }
+    if (n_pairs) *n_pairs = pairs_found;
+    return RCA_OK;
 }
 
 // ================================================================================================

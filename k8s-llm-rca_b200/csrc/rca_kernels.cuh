@@ -738,4 +738,70 @@ __global__ void state_lookup(const int *st_off, const StRec *rec, int n_nodes, c
     out_cnt[i] = c;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Batched `message CONTAINS pattern` (find_metapath/find_srckind_metapath_neo4j.py:78,
+// generate_query/generate_query.py:225): which EVENT messages contain which of P patterns.
+// Rabin-Karp: one thread per (message, distinct pattern length) rolls a 64-bit polynomial hash over
+// the message's windows of that length and probes an open-addressing table of pattern hashes; a hit
+// is verified byte by byte, then recorded: atomicMin of the message index per pattern (the
+// canonical 'LIMIT 1' answer) and a (pattern, message) pair appended to a list.
+constexpr unsigned long long kRkBase = 0x100000001b3ull;          // odd multiplier (FNV prime)
+
+struct TextParams {
+    const unsigned char *msg;         // message bytes, concatenated
+    const long long *msg_off;         // [M+1]
+    long long n_msgs;
+    const unsigned char *pat;         // pattern bytes, concatenated (distinct patterns)
+    const long long *pat_off;         // [P+1]
+    const int *lens;                  // [D] distinct pattern lengths (> 0)
+    const unsigned long long *pow_top;// [D] base^(len-1)
+    int n_lens;
+    const unsigned long long *tab_hash;   // [T] hash of the pattern in the slot
+    const int *tab_pat;               // [T] pattern index or -1 (empty); T is a power of two
+    unsigned tab_mask;
+    int *first;                       // [P] lowest matching message index (init INT_MAX)
+    int2 *pairs;                      // [cap] (pattern, message)
+    unsigned long long cap;
+    unsigned long long *n_pairs;      // matches found (may exceed cap: then the list is truncated)
+};
+
+__device__ __forceinline__ unsigned rk_slot(unsigned long long h, int len, unsigned mask) {
+    unsigned long long x = h ^ ((unsigned long long)len * 0x9e3779b97f4a7c15ull);
+    x ^= x >> 29; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 32;
+    return (unsigned)x & mask;
+}
+
+__global__ void __launch_bounds__(256) contains_scan(const __grid_constant__ TextParams p) {
+    const long long gid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long m = gid / p.n_lens;
+    if (m >= p.n_msgs) return;
+    const int d = (int)(gid - m * p.n_lens);
+    const int len = p.lens[d];
+    const long long b = p.msg_off[m];
+    const int n = (int)(p.msg_off[m + 1] - b);
+    if (n < len) return;
+    const unsigned char *t = p.msg + b;
+    const unsigned long long top = p.pow_top[d];
+    unsigned long long h = 0;
+    for (int i = 0; i < len; i++) h = h * kRkBase + t[i];
+    for (int pos = 0;; pos++) {
+        for (unsigned sl = rk_slot(h, len, p.tab_mask);; sl = (sl + 1) & p.tab_mask) {
+            const int pi = p.tab_pat[sl];
+            if (pi < 0) break;
+            if (p.tab_hash[sl] != h) continue;
+            const long long pb = p.pat_off[pi];
+            if ((int)(p.pat_off[pi + 1] - pb) != len) continue;
+            bool eq = true;
+            for (int i = 0; i < len && eq; i++) eq = p.pat[pb + i] == t[pos + i];
+            if (eq) {
+                atomicMin(p.first + pi, (int)m);
+                const unsigned long long k = atomicAdd(p.n_pairs, 1ull);
+                if (k < p.cap) p.pairs[k] = make_int2(pi, (int)m);
+            }
+        }
+        if (pos + len >= n) break;
+        h = (h - t[pos] * top) * kRkBase + t[pos + len];
+    }
+}
+
 }  // namespace rca

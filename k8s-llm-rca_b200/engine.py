@@ -22,7 +22,8 @@ LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold", "rca_reserve",
            "rca_expand", "rca_expand_static",
-           "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_version")
+           "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_text_load",
+           "rca_text_contains", "rca_version")
 
 
 class RcaError(RuntimeError):
@@ -94,6 +95,9 @@ def load_library(path: str | None = None):
                                      C.c_void_p]
     lib.rca_state_window.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
+    lib.rca_text_load.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    lib.rca_text_contains.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                                      C.POINTER(C.c_int64)]
     if path is None:
         _lib = lib
     return lib
@@ -291,6 +295,52 @@ class Engine:
             dev_seed_ts.data_ptr() if dev_seed_ts is not None else None,
             dev_rows.data_ptr(), int(dev_rows.numel()), C.byref(st)))
         return st
+
+    def text_load(self, node_ids, messages):
+        """Upload the message arena (node id, message string) for contains(); sorted by node id."""
+        order = np.argsort(np.asarray(node_ids), kind="stable")
+        ids = np.ascontiguousarray(np.asarray(node_ids, dtype=np.int32)[order])
+        enc = [(messages[i] or "").encode("utf-8") for i in order.tolist()]
+        off = np.zeros(len(enc) + 1, dtype=np.int64)
+        np.cumsum([len(b) for b in enc], out=off[1:])
+        blob = np.frombuffer(b"".join(enc), dtype=np.uint8) if off[-1] else np.zeros(1, np.uint8)
+        blob = np.ascontiguousarray(blob)
+        self._ck(self.lib.rca_text_load(self.h, blob.ctypes.data, off.ctypes.data, ids.ctypes.data, len(enc)))
+        self._text_nodes = ids
+
+    def contains(self, patterns, pairs_cap=None):
+        """Batched `message CONTAINS pattern`: -> (first node id per pattern or -1, {pattern index: sorted
+        node ids})."""
+        enc = [t.encode("utf-8") for t in patterns]
+        uniq = {}
+        for b in enc:
+            uniq.setdefault(b, len(uniq))
+        ulist = list(uniq)
+        off = np.zeros(len(ulist) + 1, dtype=np.int64)
+        np.cumsum([len(b) for b in ulist], out=off[1:])
+        blob = np.ascontiguousarray(np.frombuffer(b"".join(ulist), dtype=np.uint8)) if off[-1] else np.zeros(1, np.uint8)
+        first = np.empty(len(ulist), np.int32)
+        cap = int(pairs_cap or max(1024, 16 * len(ulist)))
+        while True:
+            pairs = np.empty((cap, 2), np.int32)
+            n = C.c_int64(0)
+            self._ck(self.lib.rca_text_contains(self.h, blob.ctypes.data, off.ctypes.data, len(ulist), first.ctypes.data,
+                                                pairs.ctypes.data, cap, C.byref(n)))
+            if n.value <= cap:
+                break
+            cap = int(n.value) + 16
+        pairs = np.unique(pairs[:n.value], axis=0) if n.value else np.zeros((0, 2), np.int32)
+        by_u = {}
+        for u, node in pairs.tolist():
+            by_u.setdefault(u, []).append(node)
+        idx = [uniq[b] for b in enc]
+        hits = {}
+        for i, u in enumerate(idx):
+            if len(ulist[u]) == 0:
+                hits[i] = self._text_nodes.tolist()
+            elif u in by_u:
+                hits[i] = by_u[u]
+        return first[idx], hits
 
     def state_lookup(self, nodes, ts, with_ids=True, ts_hi=None):
         """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids).

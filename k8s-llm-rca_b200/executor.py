@@ -75,6 +75,7 @@ class GpuBackend:
     def __init__(self, snap, device: int = 0):
         self.snap = snap
         self.engine = E.Engine(snap, device)
+        self._text_loaded = False
 
     def close(self):
         self.engine.close()
@@ -92,6 +93,14 @@ class GpuBackend:
 
     def states(self, nodes, tmin_le, tmax_gt):
         return self.engine.state_lookup(nodes, tmin_le, ts_hi=tmax_gt)
+
+    def contains(self, texts):
+        """{index of text: sorted node ids whose `message` contains it} - on the device."""
+        if not self._text_loaded:
+            ids, msgs = self.snap.props.messages()
+            self.engine.text_load(ids, msgs)
+            self._text_loaded = True
+        return self.engine.contains(texts)[1]
 
 
 # ------------------------------------------------------------------------------------------ runner
@@ -230,11 +239,10 @@ class QueryRunner:
         # fast path: <seed>.message CONTAINS <text> over the message arena
         if w[0] == "cmp" and w[1] == "contains" and w[2] == ("prop", ("var", plan.seed_var), "message"):
             text = cy.eval_expr(w[3], {}, params)
-            ids, msgs = s.props.messages()
             if text is None:
                 return np.zeros(0, np.int32)
-            hit = [int(v) for v, m in zip(ids.tolist(), msgs) if lo <= v < hi and m is not None and text in m]
-            return np.array(hit, dtype=np.int32)
+            hit = [v for v in self.backend.contains([text]).get(0, []) if lo <= v < hi]
+            return np.array(sorted(hit), dtype=np.int32)
         if w[0] == "cmp" and w[1] == "=" and w[2] == ("prop", ("var", plan.seed_var), "id"):
             val = cy.eval_expr(w[3], {}, params)
             return np.array(sorted(s.props.find_by_id(kind, val)), dtype=np.int32)

@@ -26,6 +26,15 @@ class OracleBackend:
     def states(self, nodes, tmin_le, tmax_gt):
         return self.orc.states(nodes, tmin_le, ts_hi=tmax_gt)
 
+    def contains(self, texts):
+        ids, msgs = self.snap.props.messages()
+        out = {}
+        for i, t in enumerate(texts):
+            hit = sorted(int(v) for v, m in zip(ids.tolist(), msgs) if m is not None and t in m)
+            if hit:
+                out[i] = hit
+        return out
+
 
 def oracle_executor(snap):
     """An object with run_query / close, like the executors, running on the oracle."""

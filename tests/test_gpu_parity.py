@@ -255,3 +255,26 @@ def test_metagraph_on_gpu(snap_10k, csr_oracle_lib):
     res = check_varlen(eng, orc, seeds, "und", 3, dest_kind=nfs, excl_kinds=[ev, ns], inter_kinds=[pvc, pv])
     assert res.total >= 1
     eng.close()
+
+
+def test_message_contains_scan(snap_10k):
+    """Batched CONTAINS on the device == Python's `in` over the same messages."""
+    from k8s_llm_rca_b200 import engine
+    eng = engine.Engine(snap_10k)
+    ids, msgs = snap_10k.props.messages()
+    eng.text_load(ids, msgs)
+    rng = np.random.default_rng(8)
+    pats = [msgs[i] for i in rng.integers(0, len(msgs), size=40)]                      # whole messages
+    pats += [msgs[i][5:25] for i in rng.integers(0, len(msgs), size=20)]               # inner substrings
+    pats += ["not found", "configmap", "MountVolume", '"', "zzz-no-such-text", "", "d", "0/", "é"]
+    pats += [pats[0], pats[41]]                                                        # duplicates
+    first, hits = eng.contains(pats)
+    for i, t in enumerate(pats):
+        want = sorted(int(v) for v, m in zip(ids.tolist(), msgs) if t in m)
+        assert hits.get(i, []) == want, (i, t)
+        assert first[i] == (want[0] if want else -1)
+    assert len(hits[pats.index("not found")]) > 100 and pats.index("zzz-no-such-text") not in hits
+    # a tiny pair buffer must grow, not truncate
+    first2, hits2 = eng.contains(pats, pairs_cap=8)
+    assert hits2 == hits and np.array_equal(first, first2)
+    eng.close()
