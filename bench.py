@@ -40,12 +40,14 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms.  It is started before the warm-up
+    (nvidia-smi needs a few hundred ms to produce its first line) and the samples are cut to the
+    timed window by their timestamps."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.t0, self.t1 = index, [], None, None, None
 
     def start(self):
         try:
@@ -59,23 +61,31 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def window(self, t0, t1):
+        self.t0, self.t1 = t0, t1
 
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)                      # let the last sample of the window arrive
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
         self.t.join(timeout=2)
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        rows = [r for (t, r) in self.rows if len(r) >= 7 and (self.t0 is None or self.t0 - 0.05 <= t <= self.t1 + 0.15)]
+        in_window = True
+        if not rows:
+            rows, in_window = [r for (_, r) in self.rows if len(r) >= 7], False
+        sm = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if r[2].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
+        reasons = sorted({names[i] for r in rows for i in range(4) if r[3 + i].lower() == "active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "samples_in_timed_window": in_window}
 
 
 def run_reference(args, rank, world):
@@ -115,13 +125,16 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--objects", type=int, default=1_000_000)
     ap.add_argument("--events", type=int, default=108_696)
     ap.add_argument("--cpu-sample", type=int, default=50_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--latency-incidents", type=int, default=10_000,
+                    help="config 5: incidents replayed as one batch (drawn with replacement); 0 skips the latency leg")
+    ap.add_argument("--latency-singles", type=int, default=200, help="incidents replayed one by one for p50/p99")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -206,15 +219,15 @@ def main():
             ms = sum(a.elapsed_time(b) for a, b in evs)
             return ms, inst, launches, per_level
 
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
         for _ in range(args.warmup):
             step(True)
         for _ in range(args.warmup):
             step(False)
-
-        sampler = ClockSampler(local_rank)
         barrier()
-        if rank == 0:
-            sampler.start()
+        t_win0 = time.time()
         ms_res, inst_res, launches, per_level = timed(True, args.steps)
         barrier()
         d2h[0] = 0
@@ -222,6 +235,7 @@ def main():
         ms_e2e, inst_e2e, _, _ = timed(False, args.steps)
         wall_e2e = time.perf_counter() - t0
         barrier()
+        sampler.window(t_win0, time.time())
         clocks = sampler.stop() if rank == 0 else None
 
     # max over ranks of the device time, sum over ranks of the instances
@@ -232,6 +246,43 @@ def main():
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     ms_res, ms_e2e = red.tolist()
     inst_res, inst_e2e = tot.tolist()
+
+    # ---- config 5: per-incident RCA graph latency (LLM answers recorded), one by one and batched
+    latency = None
+    if args.latency_incidents > 0:
+        from k8s_llm_rca_b200 import executor, replay
+        executor.register_snapshot("bench", w.snap)
+        sx = executor.GpuQueryExecutor("snapshot://bench", device=local_rank)
+        mx = executor.GpuQueryExecutor("snapshot://bench#metagraph", device=local_rank)
+        rp = replay.IncidentReplayer(sx, mx)
+        rng = np.random.default_rng(5)
+        msgs = w.snap.props.msgs
+        draw = [msgs[i] for i in rng.integers(0, len(msgs), size=args.latency_incidents)]
+        mine = draw[rank::world]
+        rp.run_batch(mine[:64])                                   # warm-up: message arena upload, metapath cache
+        barrier()
+        t0 = time.perf_counter()
+        out = rp.run_batch(mine)
+        torch.cuda.synchronize()
+        bt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(bt, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            lat = []
+            for m in draw[:args.latency_singles]:
+                t1 = time.perf_counter()
+                rp.run_one(m)
+                lat.append((time.perf_counter() - t1) * 1e3)
+            lat = np.array(lat)
+            latency = {"single_p50_ms": float(np.percentile(lat, 50)), "single_p99_ms": float(np.percentile(lat, 99)),
+                       "single_n": int(len(lat)), "batch_incidents": args.latency_incidents,
+                       "batch_total_ms": float(bt) * 1e3, "batch_ms_per_incident": float(bt) * 1e3 / args.latency_incidents,
+                       "rows_in_batch": int(sum(len(r["rows"]) for r in out)),
+                       "what": "per incident: CONTAINS seed lookup + source kind + metapath ladder + instance query + "
+                               "message filter + state check per node, LLM answers recorded; single = through "
+                               "run_query one statement at a time, batch = one launch set for all incidents"}
+        sx.close()
+        mx.close()
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -265,6 +316,7 @@ def main():
                          "peak_source": peak_src, "bytes_per_launch": kbytes // kcalls,
                          "ms_per_launch": kms / kcalls, "share_of_step": kms / step_ms_sum if step_ms_sum else None},
             "clocks": clocks,
+            "latency": latency,
         }
         if world == 1 and not args.no_cpu_baseline:
             from oracle.csr import CsrOracle, build
