@@ -95,6 +95,8 @@ typedef struct {
     /* --- both --- */
     int32_t with_states;            /* fuse the HasState predicate (analyze_root_cause.py:70-79)
                                        into emission: rows grow by (len+1) state ids + 1 mask    */
+    int32_t count_only;             /* count path instances per length but do not write rows (no
+                                       output arena needed; for very large enumerations)         */
 } rca_plan_t;
 
 /* Counters of the last rca_expand, all exact (they come from the kernels' own count pass). */

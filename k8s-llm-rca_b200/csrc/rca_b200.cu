@@ -550,6 +550,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
             p.chain_flag = s < L ? 1 : 2;
             p.need_inter = varlen && pl->has_inter;
             p.with_states = pl->with_states;
+            p.count_only = pl->count_only;
             p.row_len = row_len_of(pl, s);
             for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
             p.epoch = e->epoch;
@@ -627,7 +628,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         obase += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s);
         total += e->res_rows[s];
     }
-    e->have_result = true;
+    e->have_result = !pl->count_only;
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->frontier[0] = n_seeds;
@@ -975,6 +976,7 @@ extern "C" int rca_expand_static(rca_engine_t *e, const rca_plan_t *pl, const in
         p.chain_flag = s < L ? 1 : 2;
         p.need_inter = varlen && pl->has_inter;
         p.with_states = pl->with_states;
+        p.count_only = pl->count_only;
         p.row_len = row_len_of(pl, s);
         for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
         p.epoch = epoch;

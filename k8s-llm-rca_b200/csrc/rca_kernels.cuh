@@ -103,6 +103,7 @@ struct LevelParams {
     int chain_flag;                   // chain plans: 1 = every candidate continues, 2 = every candidate is a row
     int need_inter;                   // emit only if an interior node so far is of an intermediate kind
     int with_states;
+    int count_only;                   // rows are counted, never written
     int row_len;                      // words per emitted row at this level
     int row_len_lv[RCA_MAX_HOPS + 1]; // ... and at every level (arena bases are sums over earlier levels)
     unsigned epoch;                   // fused path: tag of this call's tile-state words (never 0)
@@ -372,6 +373,7 @@ __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, c
 // answer by shuffle.
 __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, int n, unsigned long long ob_s,
                                            unsigned long long run_e) {
+    if (p.count_only) return;
     const int s = p.s, q = s - 1, rl = p.row_len;
     const WarpSm &W = *w.W;
     const bool active = w.lane < n;
@@ -586,7 +588,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
         ctl->N[s] = base_n + s_run[1];
         unsigned ov = 0;
         if (fb_s + base_f + s_run[0] > p.fcap) ov |= 1u;
-        if (ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
+        if (!p.count_only && ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (ov) ctl->overflow = ov;
     }
 }
@@ -700,7 +702,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
         tile_lookback(tstate, tile, p.epoch, (unsigned long long)cf, (unsigned long long)ce, run_f, run_e);
         if (run_f + cf > 0xffffffffull) ov |= 1u;     // the 32-bit count field of the state word
         if (c.fb_s + run_f + cf > p.fcap) ov |= 1u;
-        if (c.ob_s + (run_e + ce) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
+        if (!p.count_only && c.ob_s + (run_e + ce) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (tile == c.ntiles - 1 && lane == 0) {      // the last tile knows the level totals
             ctl->F[s] = run_f + cf;
             ctl->N[s] = run_e + ce;

@@ -53,7 +53,7 @@ class PlanDesc(C.Structure):
                 ("has_inter", C.c_int32), ("prune", C.c_int32),
                 ("pos_kind", C.c_int32 * (MAX_HOPS + 1)),
                 ("kind_excl", C.c_uint8 * MAX_KINDS), ("kind_inter", C.c_uint8 * MAX_KINDS),
-                ("with_states", C.c_int32)]
+                ("with_states", C.c_int32), ("count_only", C.c_int32)]
 
 
 class StatsDesc(C.Structure):
@@ -104,7 +104,7 @@ def load_library(path: str | None = None):
 
 
 def varlen_plan(direction, max_hops, min_hops=1, dest_kind=-1, excl_kinds=(), inter_kinds=(), entity_only=False,
-                node_simple=True, pos_kind=None, prune=True, with_states=False) -> PlanDesc:
+                node_simple=True, pos_kind=None, prune=True, with_states=False, count_only=False) -> PlanDesc:
     """Variable-length path plan - the reference's metapath statements,
     find_metapath/find_srckind_metapath_neo4j.py:95-129."""
     p = PlanDesc()
@@ -125,10 +125,11 @@ def varlen_plan(direction, max_hops, min_hops=1, dest_kind=-1, excl_kinds=(), in
     for k in inter_kinds:
         p.kind_inter[int(k)] = 1
     p.with_states = int(bool(with_states))
+    p.count_only = int(bool(count_only))
     return p
 
 
-def chain_plan(etypes, dirs, with_states=False) -> PlanDesc:
+def chain_plan(etypes, dirs, with_states=False, count_only=False) -> PlanDesc:
     """Typed chain plan - one step per MATCH clause of the instance query,
     generate_query/generate_query.py:241-248."""
     assert len(etypes) == len(dirs) and 1 <= len(etypes) <= MAX_HOPS
@@ -142,6 +143,7 @@ def chain_plan(etypes, dirs, with_states=False) -> PlanDesc:
         p.pos_kind[i] = -1
     p.dest_kind = -1
     p.with_states = int(bool(with_states))
+    p.count_only = int(bool(count_only))
     return p
 
 
@@ -175,12 +177,15 @@ class ExpandResult:
         self.launches = int(st.launches)
         self.retries = int(st.retries)
         self._gen = engine._gen
+        self.count_only = False
 
     def rows(self, level: int, out: np.ndarray | None = None) -> np.ndarray:
         """Copy the rows of one level to the host.  `out`: optional pre-allocated (ideally pinned)
         int32 buffer with room for n*row_len words; a view of it is returned."""
         assert self._gen == self.engine._gen, "result was overwritten by a later expand()"
         n, w = self.emitted[level], self.row_len[level]
+        if self.count_only and n:
+            raise ValueError("the plan ran with count_only: there are no rows to copy")
         if out is not None:
             flat = out.reshape(-1)
             assert flat.dtype == np.int32 and flat.size >= n * w and flat.flags.c_contiguous
@@ -279,7 +284,9 @@ class Engine:
         self._gen += 1
         self._ck(self.lib.rca_expand(self.h, C.byref(plan), sp, n, tp, on_dev, C.byref(st)))
         levels = plan.max_hops if plan.kind == PLAN_VARLEN else plan.n_steps
-        return ExpandResult(self, st, levels)
+        res = ExpandResult(self, st, levels)
+        res.count_only = bool(plan.count_only)
+        return res
 
     def expand_static(self, plan: PlanDesc, dev_seeds, dev_seed_ts, dev_rows):
         """rca_expand_static: expansion that allocates nothing (fixed scratch inside the library; see

@@ -278,3 +278,16 @@ def test_message_contains_scan(snap_10k):
     first2, hits2 = eng.contains(pats, pairs_cap=8)
     assert hits2 == hits and np.array_equal(first, first2)
     eng.close()
+
+
+def test_count_only_plans(eng_10k, snap_10k):
+    """count_only: same counters, nothing written (for enumerations too large to materialise)."""
+    from k8s_llm_rca_b200 import engine
+    pod, node, ev, ns = _kinds(snap_10k, "Pod", "Node", "Event", "Namespace")
+    seeds = snap_10k.nodes_of_kind(pod)
+    full = eng_10k.expand(engine.varlen_plan("und", 4, dest_kind=node, excl_kinds=[ev, ns], entity_only=True), seeds)
+    cnt = eng_10k.expand(engine.varlen_plan("und", 4, dest_kind=node, excl_kinds=[ev, ns], entity_only=True,
+                                            count_only=True), seeds)
+    assert cnt.emitted == full.emitted and cnt.frontier == full.frontier and cnt.scanned == full.scanned
+    with pytest.raises(ValueError):
+        cnt.rows(3)
