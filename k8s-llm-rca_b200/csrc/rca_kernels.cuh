@@ -49,7 +49,10 @@ constexpr int kGroup = 32;            // tiles per group (split path)
 constexpr int kLv = RCA_MAX_HOPS + 2;
 constexpr int kQueue = 64;            // emission queue entries per warp
 #ifndef RCA_MINB
-#define RCA_MINB 6
+#define RCA_MINB 6            // resident CTAs per SM the count / fused kernels are compiled for (40 registers)
+#endif
+#ifndef RCA_MINB_FILL
+#define RCA_MINB_FILL 5       // fill_level keeps several state-probe loads in flight: 48 registers, no spills
 #endif
 
 // plan table in device memory, staged into shared memory per CTA (all offsets multiples of 16 B)
@@ -371,6 +374,7 @@ __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, c
 // State probes are shared: rows written together are siblings (same seed, usually the same second
 // node), so per column the lanes that hold the same node id elect one lane to probe and take its
 // answer by shuffle.
+template <int S>        // S: path length of the rows when known at compile time (1..4), else -1
 __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, int n, unsigned long long ob_s,
                                            unsigned long long run_e) {
     if (p.count_only) return;
@@ -391,18 +395,51 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
     if (p.with_states) {
         const long long ts = active ? __ldg(p.seed_ts + W.root[o]) : 0;
         unsigned miss = 0;
-        for (int d = 0; d <= s; d++) {
-            const int nd = active ? ((d <= q) ? w.anc_n[d * kTile + o] : v) : -1;
-            // same node AND same timestamp -> same answer (rows of one seed share the timestamp)
-            const unsigned same = __match_any_sync(0xffffffffu, nd) & __match_any_sync(0xffffffffu, ts);
-            const int leader = __ffs(same) - 1;
-            int first = -1, cnt = 0;
-            if (w.lane == leader && nd >= 0) state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
-            first = __shfl_sync(0xffffffffu, first, leader);
-            cnt = __shfl_sync(0xffffffffu, cnt, leader);
-            if (active) {
-                row[2 * s + 1 + d] = first;
-                miss |= (cnt == 0 ? 1u : 0u) << d;
+        if constexpr (S >= 0) {
+            // the kernel is latency-bound here: issue every column's offset loads, then every column's
+            // record loads, back to back - two memory round trips per row instead of 2(S+1)
+            int sb[S + 1], se[S + 1];
+#pragma unroll
+            for (int d = 0; d <= S; d++) {
+                const int nd = active ? ((d <= q) ? w.anc_n[d * kTile + o] : v) : 0;
+                sb[d] = __ldg(p.st_off + nd);
+                se[d] = active ? __ldg(p.st_off + nd + 1) : sb[d];
+            }
+            longlong2 iv[S + 1];
+#pragma unroll
+            for (int d = 0; d <= S; d++) {
+                iv[d] = make_longlong2(1, 0);
+                if (sb[d] < se[d]) iv[d] = __ldg(reinterpret_cast<const longlong2 *>(p.st_rec + sb[d]));
+            }
+#pragma unroll
+            for (int d = 0; d <= S; d++) {
+                int first = -1, cnt = 0;
+                if (sb[d] < se[d]) {
+                    if (iv[d].x <= ts && iv[d].y > ts) { first = __ldg(&p.st_rec[sb[d]].node); cnt = 1; }
+                    for (int j = sb[d] + 1; j < se[d]; j++) {
+                        const longlong2 x = __ldg(reinterpret_cast<const longlong2 *>(p.st_rec + j));
+                        if (x.x <= ts && x.y > ts) { if (cnt == 0) first = __ldg(&p.st_rec[j].node); cnt++; }
+                    }
+                }
+                if (active) {
+                    row[2 * s + 1 + d] = first;
+                    miss |= (cnt == 0 ? 1u : 0u) << d;
+                }
+            }
+        } else {
+            for (int d = 0; d <= s; d++) {
+                const int nd = active ? ((d <= q) ? w.anc_n[d * kTile + o] : v) : -1;
+                // same node AND same timestamp -> same answer (rows of one seed share the timestamp)
+                const unsigned same = __match_any_sync(0xffffffffu, nd) & __match_any_sync(0xffffffffu, ts);
+                const int leader = __ffs(same) - 1;
+                int first = -1, cnt = 0;
+                if (w.lane == leader && nd >= 0) state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
+                first = __shfl_sync(0xffffffffu, first, leader);
+                cnt = __shfl_sync(0xffffffffu, cnt, leader);
+                if (active) {
+                    row[2 * s + 1 + d] = first;
+                    miss |= (cnt == 0 ? 1u : 0u) << d;
+                }
             }
         }
         if (active) row[3 * s + 2] = (int)miss;
@@ -440,7 +477,7 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
             qn += __popc(be);
             __syncwarp();
             if (qn >= 32) {
-                flush_rows(p, w, 32, ob_s, run_e);
+                flush_rows<(QT >= 0 && QT <= 3) ? QT + 1 : -1>(p, w, 32, ob_s, run_e);
                 run_e += 32;
                 __syncwarp();
                 const int rest = qn - 32;
@@ -453,7 +490,7 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
             }
         }
     }
-    if (qn) flush_rows(p, w, qn, ob_s, run_e);
+    if (qn) flush_rows<(QT >= 0 && QT <= 3) ? QT + 1 : -1>(p, w, qn, ob_s, run_e);
 }
 
 // Walk the tile's windows and count the survivors.
@@ -595,7 +632,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
 
 // split path, step 3: re-walk every tile and write its survivors at (group prefix + in-group prefix)
 template <bool ADJ2, int MODE, int QT>
-__global__ void __launch_bounds__(kThreads, RCA_MINB) fill_level(const __grid_constant__ LevelParams p) {
+__global__ void __launch_bounds__(kThreads, RCA_MINB_FILL) fill_level(const __grid_constant__ LevelParams p) {
     extern __shared__ int s_dyn[];
     __shared__ TablesSm tsm;
     __shared__ unsigned long long s_fb[kLv];
