@@ -136,6 +136,16 @@ int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words)
  * Results stay in the engine until the next rca_expand / rca_close on it. */
 int rca_expand(rca_engine_t *e, const rca_plan_t *plan, const int32_t *seeds, int64_t n_seeds,
                const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats);
+/* Several plans in one submission (no counterpart in the reference, which sends one statement at a
+ * time): the plans run back to back on the engine's stream with one upload, one download and ONE
+ * synchronisation for the whole set; plan k's rows follow plan k-1's in the output arena.
+ * seeds[k] / n_seeds[k] / seed_ts[k] (seed_ts, or its entries for plans without with_states, may be
+ * null) are all host or all device memory.  stats (nullable) receives n_plans entries; level_ms is
+ * not filled, kernel_ms is the plan's share of the stream time.  rca_result_select chooses the plan
+ * that rca_result_level / rca_result_copy address (plan 0 after the call). */
+int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t n_plans, const int32_t *const *seeds,
+                    const int64_t *n_seeds, const int64_t *const *seed_ts, int seeds_on_device, rca_stats_t *stats);
+int rca_result_select(rca_engine_t *e, int32_t plan_index);
 /* device pointer / shape of the rows of paths with `level` relationships.
  * Row = (level+1) node ids, level relationship ids [, (level+1) state ids, 1 missing-state mask] */
 int rca_result_level(const rca_engine_t *e, int level, const int32_t **dev_rows, int64_t *n_rows,

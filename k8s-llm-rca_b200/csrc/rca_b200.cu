@@ -21,6 +21,14 @@ using namespace rca;
 
 static thread_local std::string g_open_error;
 
+struct PlanResult {
+    bool valid = false;
+    int levels = 0;
+    int row_len[RCA_MAX_HOPS + 1] = {0};
+    long long rows[RCA_MAX_HOPS + 1] = {0};
+    unsigned long long base[RCA_MAX_HOPS + 1] = {0};
+};
+
 struct rca_engine {
     int device = 0;
     int sm_count = 148;
@@ -68,12 +76,14 @@ struct rca_engine {
     long long n_msgs = 0;
     void *io_buf = nullptr;               // staging for rca_state_lookup with host buffers
     size_t io_cap = 0;
-    // last result
-    bool have_result = false;
-    int res_levels = 0;
-    int res_row_len[RCA_MAX_HOPS + 1] = {0};
-    long long res_rows[RCA_MAX_HOPS + 1] = {0};
-    unsigned long long res_base[RCA_MAX_HOPS + 1] = {0};
+    // rca_expand_many: per-plan tables and control blocks
+    unsigned char *m_ptab = nullptr, *mh_ptab = nullptr;
+    Ctl *m_ctl = nullptr, *mh_ctl = nullptr;
+    size_t many_cap = 0;
+    std::vector<cudaEvent_t> ev_many;
+    // results of the last submission (one per plan) and the one the accessors address
+    std::vector<PlanResult> results;
+    int selected = 0;
 };
 
 static int fail(rca_engine *e, int code, const char *fmt, ...) {
@@ -199,10 +209,13 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
                    e->st_off, e->st_rec, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
-                   e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off};
+                   e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off, e->m_ptab, e->m_ctl};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
     if (e->h_ptab) cudaFreeHost(e->h_ptab);
+    if (e->mh_ptab) cudaFreeHost(e->mh_ptab);
+    if (e->mh_ctl) cudaFreeHost(e->mh_ctl);
+    for (auto ev : e->ev_many) cudaEventDestroy(ev);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     for (auto ev : e->ev_lv) if (ev) cudaEventDestroy(ev);
@@ -234,7 +247,7 @@ extern "C" int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t ou
     CK(cudaSetDevice(e->device));
     int rc = grow(e, &e->frontier, &e->fcap, (unsigned long long)frontier_entries);
     if (rc) return rc;
-    e->have_result = false;
+    e->results.clear();
     return grow(e, &e->out, &e->ocap, (unsigned long long)output_words);
 }
 
@@ -389,78 +402,55 @@ extern "C" int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds) {
     return RCA_OK;
 }
 
-extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *seeds, int64_t n_seeds,
-                          const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats) {
-    if (!e) return RCA_ERR_ARG;
-    if (!pl || n_seeds < 0 || (n_seeds > 0 && !seeds)) return fail(e, RCA_ERR_ARG, "rca_expand: null plan or seeds");
-    if (n_seeds > 0x7fffffffLL) return fail(e, RCA_ERR_ARG, "rca_expand: more than 2^31-1 seeds in one call");
-    if (pl->with_states && n_seeds > 0 && !seed_ts) return fail(e, RCA_ERR_ARG, "rca_expand: with_states needs seed_ts");
-    int rc = validate_plan(e, pl);
-    if (rc) return rc;
-    CK(cudaSetDevice(e->device));
-    e->have_result = false;
-    const bool varlen = pl->kind == RCA_PLAN_VARLEN;
-    const int L = varlen ? pl->max_hops : pl->n_steps;
-    const int mode = !varlen ? kModeChain : (pl->node_simple ? kModeSimple : kModeRelUnique);
-    const bool fused = n_seeds <= (varlen ? e->fused_max_seeds : e->chain_fused_max_seeds);
+// ------------------------------------------------------------------------------------------------
+// One plan, prepared on the host: its table (kind boundaries, one kind-action row per level,
+// node-block -> kind table, one arrival row per level) and, per level, how to launch it.
+struct Sub { int t, d; };
+struct PreparedPlan {
+    const rca_plan_t *pl = nullptr;
+    bool varlen = false, fused = false, arr_prune = false;
+    int L = 0, mode = kModeChain;
+    std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
+    std::vector<char> level_typed, level_dead;
+};
 
-    // ---- seeds (and their timestamps) on the device
-    const int *d_seeds = seeds;
-    const long long *d_ts = (const long long *)seed_ts;
-    if (!seeds_on_device && n_seeds) {
-        unsigned long long cap = (unsigned long long)e->seeds_cap;
-        rc = grow(e, &e->seeds_buf, &cap, (unsigned long long)n_seeds);
-        e->seeds_cap = (long long)cap;
-        if (rc) return rc;
-        CK(cudaMemcpyAsync(e->seeds_buf, seeds, (size_t)n_seeds * sizeof(int), cudaMemcpyHostToDevice, e->stream));
-        d_seeds = e->seeds_buf;
-        if (pl->with_states) {
-            cap = (unsigned long long)e->ts_cap;
-            rc = grow(e, &e->ts_buf, &cap, (unsigned long long)n_seeds);
-            e->ts_cap = (long long)cap;
-            if (rc) return rc;
-            CK(cudaMemcpyAsync(e->ts_buf, seed_ts, (size_t)n_seeds * sizeof(long long), cudaMemcpyHostToDevice, e->stream));
-            d_ts = e->ts_buf;
-        }
-    }
-
-    // ---- plan table: kind boundaries, one kind-action row per level, node-block -> kind table,
-    //      one arrival row per level
-    bool arr_prune = false;
-    {
-        unsigned char *t = e->h_ptab;
-        std::memset(t, 0, kPtBytes);
-        int *ks = reinterpret_cast<int *>(t + kPtKs);
-        for (int k = 0; k < kKindPad; k++) ks[k] = k <= e->n_kinds ? e->kind_start[k] : 0x7fffffff;
-        if (varlen) {
-            unsigned reach[RCA_MAX_KINDS];
-            reach_bits(e, pl, reach);
-            for (int s = 0; s <= L; s++) {
-                unsigned char *row = t + kPtAct + s * RCA_MAX_KINDS;
-                for (int k = 0; k < e->n_kinds; k++) {
-                    const bool dead = pl->kind_excl[k] || (pl->pos_kind[s] >= 0 && pl->pos_kind[s] != k);
-                    unsigned a = dead ? kActDead : 0u;
-                    if (!dead && s < L && ((reach[k] >> (L - s - 1)) & 1u)) a |= kActCont;
-                    if (!dead && s >= pl->min_hops && (pl->dest_kind < 0 || pl->dest_kind == k)) a |= kActEmit;
-                    if (pl->kind_inter[k]) a |= kActInter;
-                    row[k] = (unsigned char)a;
-                }
+static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, unsigned char *t, PreparedPlan &pp) {
+    pp.pl = pl;
+    pp.varlen = pl->kind == RCA_PLAN_VARLEN;
+    pp.L = pp.varlen ? pl->max_hops : pl->n_steps;
+    pp.mode = !pp.varlen ? kModeChain : (pl->node_simple ? kModeSimple : kModeRelUnique);
+    pp.fused = n_seeds <= (pp.varlen ? e->fused_max_seeds : e->chain_fused_max_seeds);
+    const int L = pp.L;
+    std::memset(t, 0, kPtBytes);
+    int *ks = reinterpret_cast<int *>(t + kPtKs);
+    for (int k = 0; k < kKindPad; k++) ks[k] = k <= e->n_kinds ? e->kind_start[k] : 0x7fffffff;
+    if (pp.varlen) {
+        unsigned reach[RCA_MAX_KINDS];
+        reach_bits(e, pl, reach);
+        for (int s = 0; s <= L; s++) {
+            unsigned char *row = t + kPtAct + s * RCA_MAX_KINDS;
+            for (int k = 0; k < e->n_kinds; k++) {
+                const bool dead = pl->kind_excl[k] || (pl->pos_kind[s] >= 0 && pl->pos_kind[s] != k);
+                unsigned a = dead ? kActDead : 0u;
+                if (!dead && s < L && ((reach[k] >> (L - s - 1)) & 1u)) a |= kActCont;
+                if (!dead && s >= pl->min_hops && (pl->dest_kind < 0 || pl->dest_kind == k)) a |= kActEmit;
+                if (pl->kind_inter[k]) a |= kActInter;
+                row[k] = (unsigned char)a;
             }
         }
-        std::memcpy(t + kPtLut, e->kind_lut.data(), kLutEntries);
-        arr_prune = varlen && arrival_reach(e, pl, L, t + kPtArr);
-        CK(cudaMemcpyAsync(e->ptab, t, kPtBytes, cudaMemcpyHostToDevice, e->stream));
     }
+    std::memcpy(t + kPtLut, e->kind_lut.data(), kLutEntries);
+    pp.arr_prune = pp.varlen && arrival_reach(e, pl, L, t + kPtArr);
 
-    // ---- levels that can run as typed sub-launches: when only one or two (edge type, direction)
-    //      pairs can emit or continue at a level (always the case at the last level of a query with
-    //      a destination kind), scanning full adjacency rows is wasted work - the typed-range tables
-    //      lead straight to the useful relationships.  Result-neutral; split path only.
-    struct Sub { int t, d; };
-    std::vector<std::vector<Sub>> subs(L + 1);
-    std::vector<char> level_typed(L + 1, 0), level_dead(L + 1, 0);
-    if (varlen && !fused && arr_prune && mode == kModeSimple) {
-        const unsigned char *arr = e->h_ptab + kPtArr, *act = e->h_ptab + kPtAct;
+    // Levels that can run as typed sub-launches: when only one or two (edge type, direction) pairs can
+    // emit or continue at a level (always the case at the last emitting level of a query with a
+    // destination kind), scanning full adjacency rows is wasted work - the typed-range tables lead
+    // straight to the useful relationships.  Result-neutral; split path only.
+    pp.subs.assign(L + 1, {});
+    pp.level_typed.assign(L + 1, 0);
+    pp.level_dead.assign(L + 1, 0);
+    if (pp.varlen && !pp.fused && pp.arr_prune && pp.mode == kModeSimple) {
+        const unsigned char *arr = t + kPtArr, *act = t + kPtAct;
         const ArrivalModel m{e, pl};
         const int A = 2 * e->n_etypes;
         // forward pass: which arrivals can occur at depth s at all.  Depth 1: any allowed hop leaving a
@@ -468,8 +458,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         std::vector<char> can(A, 0), nxt(A, 0);
         for (int a = 0; a < A; a++) {
             if (!m.allowed(a)) continue;
-            const int near = m.tail(a);
-            can[a] = !(act[0 * RCA_MAX_KINDS + near] & kActDead);          // row 0 holds the seed rules
+            can[a] = !(act[0 * RCA_MAX_KINDS + m.tail(a)] & kActDead);     // row 0 holds the seed rules
         }
         for (int s = 1; s <= L; s++) {
             std::fill(nxt.begin(), nxt.end(), 0);
@@ -479,130 +468,235 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
                 if (k & kActDead) continue;
                 const bool emit = (k & kActEmit) != 0;
                 const bool cont = (k & kActCont) && arr[(size_t)s * kArrBytes + a];
-                if (emit || cont) subs[s].push_back(Sub{a >> 1, a & 1});
+                if (emit || cont) pp.subs[s].push_back(Sub{a >> 1, a & 1});
                 if (cont)
                     for (int b = 0; b < A; b++) if (!nxt[b] && m.step_ok(a, b)) nxt[b] = 1;
             }
             can = nxt;
-            level_dead[s] = subs[s].empty();
-            level_typed[s] = !subs[s].empty() && subs[s].size() <= 2;
+            pp.level_dead[s] = pp.subs[s].empty();
+            pp.level_typed[s] = !pp.subs[s].empty() && pp.subs[s].size() <= 2;
         }
     }
+}
 
-    // ---- scratch arenas: keep what earlier calls grew to, else a guess from the seed count
+// Device buffers one plan runs in.
+struct RunBufs {
+    const int *seeds; const long long *ts; long long n_seeds;
+    Ctl *ctl; const unsigned char *ptab; unsigned epoch; unsigned long long groups;
+};
+
+// Enqueue every level of a prepared plan on the engine's stream.  ev_lv (nullable): one event per level.
+static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b, cudaEvent_t *ev_lv, int *launches) {
+    const rca_plan_t *pl = pp.pl;
+    const int L = pp.L;
+    for (int s = 1; s <= L; s++) {
+        LevelParams p;
+        std::memset(&p, 0, sizeof p);
+        int dir;
+        if (pp.varlen) {
+            dir = pl->direction;
+            p.rng = dir == RCA_DIR_OUT ? e->out_rng : dir == RCA_DIR_IN ? e->in_rng : e->und_rng;
+            p.entity_only = pl->entity_only;
+        } else {
+            const int t = pl->step_etype[s - 1];
+            dir = pl->step_dir[s - 1];
+            const int rowk = dir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
+            p.typed = 1;
+            p.rng = (dir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
+            p.row_lo = e->kind_start[rowk];
+            p.row_hi = e->kind_start[rowk + 1];
+        }
+        p.adj1 = e->out_dst;
+        p.adj2 = dir == RCA_DIR_IN ? e->in_adj : e->und_adj;
+        p.n_nodes = e->n_nodes;
+        p.s = s;
+        p.chain_flag = s < L ? 1 : 2;
+        p.need_inter = pp.varlen && pl->has_inter;
+        p.with_states = pl->with_states;
+        p.count_only = pl->count_only;
+        p.row_len = row_len_of(pl, s);
+        for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
+        p.epoch = b.epoch;
+        p.lut_shift = e->lut_shift;
+        p.seeds = b.seeds; p.seed_ts = b.ts;
+        p.frontier = e->frontier; p.fcap = e->fcap;
+        p.out = e->out; p.ocap = e->ocap;
+        p.ctl = b.ctl; p.tstate = e->tstate;
+        p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
+        p.ptab = b.ptab;
+        p.rel_et = e->rel_et; p.arr_prune = pp.arr_prune;
+        p.st_off = e->st_off; p.st_rec = e->st_rec;
+        const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
+        const long long first = std::max<long long>(1, (b.n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
+        if (pp.fused) {
+            const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
+            int grid = max_grid(e, ks.fused, dyn);
+            if (s == 1) grid = (int)std::min<long long>(grid, first);
+            ks.fused<<<grid, kThreads, dyn, e->stream>>>(p);
+            ++*launches;
+        } else if (pp.level_dead[s]) {
+            // no (edge type, direction) can emit or continue here: the level and all later ones are empty
+        } else {
+            const int n_sub = pp.level_typed[s] ? (int)pp.subs[s].size() : 1;
+            for (int j = 0; j < n_sub; j++) {
+                int sdir = dir;
+                if (pp.level_typed[s]) {              // one typed step: ranges of (type, direction) over its near kind
+                    const int t = pp.subs[s][j].t;
+                    sdir = pp.subs[s][j].d ? RCA_DIR_IN : RCA_DIR_OUT;
+                    const int rowk = sdir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
+                    p.typed = 1;
+                    p.rng = (sdir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
+                    p.row_lo = e->kind_start[rowk];
+                    p.row_hi = e->kind_start[rowk + 1];
+                    p.adj2 = e->in_adj;
+                }
+                p.sub = j;
+                const KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
+                if (j) CK(cudaMemsetAsync(e->gsum, 0, b.groups * sizeof(ulonglong2), e->stream));
+                int grid = max_grid(e, ks.count, dyn);
+                if (s == 1) grid = (int)std::min<long long>(grid, first);
+                ks.count<<<grid, kThreads, dyn, e->stream>>>(p);
+                scan_groups<<<1, 1024, 0, e->stream>>>(p);
+                grid = max_grid(e, ks.fill, dyn);
+                if (s == 1) grid = (int)std::min<long long>(grid, first);
+                ks.fill<<<grid, kThreads, dyn, e->stream>>>(p);
+                *launches += 3;
+            }
+        }
+        CK(cudaGetLastError());
+        if (ev_lv) CK(cudaEventRecord(ev_lv[s], e->stream));
+    }
+    return RCA_OK;
+}
+
+// Tile-slot arrays for a run whose largest seed set is n_seeds (sizes follow the frontier capacity).
+static int ensure_tile_arrays(rca_engine *e, long long n_seeds, bool any_fused, bool any_split, unsigned long long *groups_out) {
+    const unsigned long long slots = ((unsigned long long)n_seeds + e->fcap) / kTile + (unsigned long long)kGroup * (kLv + 2);
+    const unsigned long long groups = slots / kGroup + kLv + 2;
+    int rc;
+    if (any_fused && slots > e->tcap) {               // a fresh array starts from zeros and epoch 1
+        rc = grow(e, &e->tstate, &e->tcap, slots);
+        if (rc) return rc;
+        CK(cudaMemsetAsync(e->tstate, 0, e->tcap * sizeof(ulonglong2), e->stream));
+        e->epoch = 0;
+    }
+    if (any_split) {
+        rc = grow(e, &e->tcount, &e->ccap, slots);
+        if (rc) return rc;
+        if (groups > e->gcap) {
+            unsigned long long c1 = e->gcap, c2 = e->gcap;
+            rc = grow(e, &e->gsum, &c1, groups);
+            if (rc) return rc;
+            rc = grow(e, &e->gscan, &c2, groups);
+            if (rc) return rc;
+            e->gcap = groups;
+        }
+    }
+    *groups_out = groups;
+    return RCA_OK;
+}
+
+// next tile-state tag; when the 30-bit tag wraps, the array is cleared and the count restarts
+static int next_epoch(rca_engine *e, unsigned *out) {
+    if ((++e->epoch & 0x3fffffffu) == 0) {
+        if (e->tstate) CK(cudaMemsetAsync(e->tstate, 0, e->tcap * sizeof(ulonglong2), e->stream));
+        e->epoch = 1;
+    }
+    *out = e->epoch;
+    return RCA_OK;
+}
+
+static void fill_stats(rca_stats_t *stats, const rca_plan_t *pl, int L, long long n_seeds, const Ctl *c, float ms, int launches,
+                       int retries) {
+    std::memset(stats, 0, sizeof *stats);
+    stats->frontier[0] = n_seeds;
+    for (int s = 1; s <= L; s++) {
+        stats->frontier[s] = (int64_t)c->F[s];
+        stats->scanned[s] = (int64_t)c->E[s];
+        stats->emitted[s] = (int64_t)c->N[s];
+        stats->total += stats->emitted[s];
+    }
+    for (int s = 0; s <= L; s++) stats->row_len[s] = row_len_of(pl, s);
+    stats->kernel_ms = ms;
+    stats->launches = launches;
+    stats->retries = retries;
+}
+
+static void publish_result(rca_engine *e, PlanResult &r, const rca_plan_t *pl, int L, const Ctl *c) {
+    r.levels = L;
+    r.valid = !pl->count_only;
+    unsigned long long obase = c->out_base;
+    for (int s = 0; s <= RCA_MAX_HOPS; s++) { r.rows[s] = 0; r.row_len[s] = row_len_of(pl, s); r.base[s] = 0; }
+    for (int s = 1; s <= L; s++) {
+        r.rows[s] = (long long)c->N[s];
+        r.base[s] = obase;
+        obase += c->N[s] * (unsigned long long)row_len_of(pl, s);
+    }
+}
+
+static int stage_seeds(rca_engine *e, const int32_t *seeds, const int64_t *seed_ts, long long n, bool want_ts, long long at,
+                       long long total) {
+    unsigned long long cap = (unsigned long long)e->seeds_cap;
+    int rc = grow(e, &e->seeds_buf, &cap, (unsigned long long)total);
+    e->seeds_cap = (long long)cap;
+    if (rc) return rc;
+    if (n) CK(cudaMemcpyAsync(e->seeds_buf + at, seeds, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    if (want_ts) {
+        cap = (unsigned long long)e->ts_cap;
+        rc = grow(e, &e->ts_buf, &cap, (unsigned long long)total);
+        e->ts_cap = (long long)cap;
+        if (rc) return rc;
+        if (n) CK(cudaMemcpyAsync(e->ts_buf + at, seed_ts, (size_t)n * sizeof(long long), cudaMemcpyHostToDevice, e->stream));
+    }
+    return RCA_OK;
+}
+
+extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *seeds, int64_t n_seeds,
+                          const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats) {
+    if (!e) return RCA_ERR_ARG;
+    if (!pl || n_seeds < 0 || (n_seeds > 0 && !seeds)) return fail(e, RCA_ERR_ARG, "rca_expand: null plan or seeds");
+    if (n_seeds > 0x7fffffffLL) return fail(e, RCA_ERR_ARG, "rca_expand: more than 2^31-1 seeds in one call");
+    if (pl->with_states && n_seeds > 0 && !seed_ts) return fail(e, RCA_ERR_ARG, "rca_expand: with_states needs seed_ts");
+    int rc = validate_plan(e, pl);
+    if (rc) return rc;
+    CK(cudaSetDevice(e->device));
+    e->results.assign(1, PlanResult());
+    e->selected = 0;
+    PreparedPlan pp;
+    prepare_plan(e, pl, n_seeds, e->h_ptab, pp);
+    const int L = pp.L;
+
+    const int *d_seeds = seeds;
+    const long long *d_ts = (const long long *)seed_ts;
+    if (!seeds_on_device && n_seeds) {
+        rc = stage_seeds(e, seeds, seed_ts, n_seeds, pl->with_states != 0, 0, n_seeds);
+        if (rc) return rc;
+        d_seeds = e->seeds_buf;
+        if (pl->with_states) d_ts = e->ts_buf;
+    }
+    CK(cudaMemcpyAsync(e->ptab, e->h_ptab, kPtBytes, cudaMemcpyHostToDevice, e->stream));
+
+    // scratch arenas: keep what earlier calls grew to, else a guess from the seed count
     if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * n_seeds, 1ull << 20)); if (rc) return rc; }
     if (!e->out) { rc = grow(e, &e->out, &e->ocap, std::max<unsigned long long>(64ull * n_seeds, 1ull << 22)); if (rc) return rc; }
 
     int retries = 0, launches = 0;
     float ms = 0.f;
     while (true) {
-        // tile slots: one per 32 frontier entries, levels group-aligned with a group of slack each
-        const unsigned long long slots = ((unsigned long long)n_seeds + e->fcap) / kTile + (unsigned long long)kGroup * (kLv + 2);
-        const unsigned long long groups = slots / kGroup + kLv + 2;
-        if (fused) {
-            if (slots > e->tcap || (++e->epoch & 0x3fffffffu) == 0) {     // new array or epoch wrapped: start from zeros
-                rc = grow(e, &e->tstate, &e->tcap, std::max(slots, e->tcap));
-                if (rc) return rc;
-                CK(cudaMemsetAsync(e->tstate, 0, e->tcap * sizeof(ulonglong2), e->stream));
-                e->epoch = 1;
-            }
-        } else {
-            rc = grow(e, &e->tcount, &e->ccap, slots);
-            if (rc) return rc;
-            if (groups > e->gcap) {
-                unsigned long long c1 = e->gcap, c2 = e->gcap;
-                rc = grow(e, &e->gsum, &c1, groups);
-                if (rc) return rc;
-                rc = grow(e, &e->gscan, &c2, groups);
-                if (rc) return rc;
-                e->gcap = groups;
-            }
-        }
+        RunBufs b;
+        b.seeds = d_seeds; b.ts = d_ts; b.n_seeds = n_seeds; b.ctl = e->ctl; b.ptab = e->ptab; b.epoch = 0;
+        rc = ensure_tile_arrays(e, n_seeds, pp.fused, !pp.fused, &b.groups);
+        if (rc) return rc;
+        if (pp.fused) { rc = next_epoch(e, &b.epoch); if (rc) return rc; }
         launches = 0;
         std::memset(e->h_ctl, 0, sizeof(Ctl));
         e->h_ctl->F[0] = (unsigned long long)n_seeds;
         CK(cudaEventRecord(e->ev0, e->stream));
         CK(cudaMemcpyAsync(e->ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
-        if (!fused) CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
+        if (!pp.fused) CK(cudaMemsetAsync(e->gsum, 0, b.groups * sizeof(ulonglong2), e->stream));
         CK(cudaEventRecord(e->ev_lv[0], e->stream));
-        for (int s = 1; s <= L; s++) {
-            LevelParams p;
-            std::memset(&p, 0, sizeof p);
-            int dir;
-            if (varlen) {
-                dir = pl->direction;
-                p.typed = 0;
-                p.rng = dir == RCA_DIR_OUT ? e->out_rng : dir == RCA_DIR_IN ? e->in_rng : e->und_rng;
-                p.entity_only = pl->entity_only;
-            } else {
-                const int t = pl->step_etype[s - 1];
-                dir = pl->step_dir[s - 1];
-                const int rowk = dir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
-                p.typed = 1;
-                p.rng = (dir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
-                p.row_lo = e->kind_start[rowk];
-                p.row_hi = e->kind_start[rowk + 1];
-            }
-            p.adj1 = e->out_dst;
-            p.adj2 = dir == RCA_DIR_IN ? e->in_adj : e->und_adj;
-            p.n_nodes = e->n_nodes;
-            p.s = s;
-            p.chain_flag = s < L ? 1 : 2;
-            p.need_inter = varlen && pl->has_inter;
-            p.with_states = pl->with_states;
-            p.count_only = pl->count_only;
-            p.row_len = row_len_of(pl, s);
-            for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
-            p.epoch = e->epoch;
-            p.lut_shift = e->lut_shift;
-            p.seeds = d_seeds; p.seed_ts = d_ts;
-            p.frontier = e->frontier; p.fcap = e->fcap;
-            p.out = e->out; p.ocap = e->ocap;
-            p.ctl = e->ctl; p.tstate = e->tstate;
-            p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
-            p.ptab = e->ptab;
-            p.rel_et = e->rel_et; p.arr_prune = arr_prune;
-            p.st_off = e->st_off; p.st_rec = e->st_rec;
-            const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
-            const long long first = std::max<long long>(1, (n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
-            if (fused) {
-                const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
-                int grid = max_grid(e, ks.fused, dyn);
-                if (s == 1) grid = (int)std::min<long long>(grid, first);
-                ks.fused<<<grid, kThreads, dyn, e->stream>>>(p);
-                launches++;
-            } else if (level_dead[s]) {
-                // no (edge type, direction) can emit or continue here: the level and all later ones are empty
-            } else {
-                const int n_sub = level_typed[s] ? (int)subs[s].size() : 1;
-                for (int j = 0; j < n_sub; j++) {
-                    int sdir = dir;
-                    if (level_typed[s]) {             // one typed step: ranges of (type, direction) over its near kind
-                        const int t = subs[s][j].t;
-                        sdir = subs[s][j].d ? RCA_DIR_IN : RCA_DIR_OUT;
-                        const int rowk = sdir == RCA_DIR_OUT ? e->et_src[t] : e->et_dst[t];
-                        p.typed = 1;
-                        p.rng = (sdir == RCA_DIR_OUT ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t]);
-                        p.row_lo = e->kind_start[rowk];
-                        p.row_hi = e->kind_start[rowk + 1];
-                        p.adj2 = e->in_adj;
-                    }
-                    p.sub = j;
-                    const KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
-                    if (j) CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
-                    int grid = max_grid(e, ks.count, dyn);
-                    if (s == 1) grid = (int)std::min<long long>(grid, first);
-                    ks.count<<<grid, kThreads, dyn, e->stream>>>(p);
-                    scan_groups<<<1, 1024, 0, e->stream>>>(p);
-                    grid = max_grid(e, ks.fill, dyn);
-                    if (s == 1) grid = (int)std::min<long long>(grid, first);
-                    ks.fill<<<grid, kThreads, dyn, e->stream>>>(p);
-                    launches += 3;
-                }
-            }
-            CK(cudaGetLastError());
-            CK(cudaEventRecord(e->ev_lv[s], e->stream));
-        }
+        rc = launch_levels(e, pp, b, e->ev_lv, &launches);
+        if (rc) return rc;
         CK(cudaEventRecord(e->ev1, e->stream));
         CK(cudaMemcpyAsync(e->h_ctl, e->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
@@ -616,56 +710,176 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         if (ov & 1u) { rc = grow(e, &e->frontier, &e->fcap, std::max(e->fcap * 2, fneed + fneed / 4)); if (rc) return rc; }
         if (ov & 2u) { rc = grow(e, &e->out, &e->ocap, std::max(e->ocap * 2, oneed + oneed / 4)); if (rc) return rc; }
     }
-
-    // ---- publish the result and the counters
-    e->res_levels = L;
-    long long total = 0;
-    for (int s = 0; s <= RCA_MAX_HOPS; s++) { e->res_rows[s] = 0; e->res_row_len[s] = row_len_of(pl, s); e->res_base[s] = 0; }
-    unsigned long long obase = 0;
-    for (int s = 1; s <= L; s++) {
-        e->res_rows[s] = (long long)e->h_ctl->N[s];
-        e->res_base[s] = obase;
-        obase += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s);
-        total += e->res_rows[s];
-    }
-    e->have_result = !pl->count_only;
+    publish_result(e, e->results[0], pl, L, e->h_ctl);
     if (stats) {
-        std::memset(stats, 0, sizeof *stats);
-        stats->frontier[0] = n_seeds;
-        for (int s = 1; s <= L; s++) {
-            stats->frontier[s] = (int64_t)e->h_ctl->F[s];
-            stats->scanned[s] = (int64_t)e->h_ctl->E[s];
-        }
-        for (int s = 0; s <= L; s++) { stats->emitted[s] = e->res_rows[s]; stats->row_len[s] = e->res_row_len[s]; }
-        stats->total = total;
-        stats->kernel_ms = ms;
+        fill_stats(stats, pl, L, n_seeds, e->h_ctl, ms, launches, retries);
         for (int s = 1; s <= L; s++) {
             float t = 0.f;
             if (cudaEventElapsedTime(&t, e->ev_lv[s - 1], e->ev_lv[s]) == cudaSuccess) stats->level_ms[s] = t;
         }
-        stats->launches = launches;
-        stats->retries = retries;
     }
     return RCA_OK;
 }
 
+// Several plans in one submission: everything is enqueued back to back on the stream - one table
+// upload, one control-block upload, one download, ONE synchronisation for the whole set.  Each
+// plan's rows follow the previous plan's in the output arena (the base travels on the device).
+extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t n_plans, const int32_t *const *seeds,
+                               const int64_t *n_seeds, const int64_t *const *seed_ts, int seeds_on_device,
+                               rca_stats_t *stats) {
+    if (!e) return RCA_ERR_ARG;
+    if (n_plans < 0 || (n_plans > 0 && (!plans || !seeds || !n_seeds))) return fail(e, RCA_ERR_ARG, "rca_expand_many: null argument");
+    e->results.clear();
+    e->selected = 0;
+    if (n_plans == 0) return RCA_OK;
+    long long total_seeds = 0, max_seeds = 0;
+    bool any_ts = false;
+    for (int k = 0; k < n_plans; k++) {
+        if (n_seeds[k] < 0 || n_seeds[k] > 0x7fffffffLL || (n_seeds[k] > 0 && !seeds[k]))
+            return fail(e, RCA_ERR_ARG, "rca_expand_many: plan %d: bad seeds", k);
+        if (plans[k].with_states && n_seeds[k] > 0 && (!seed_ts || !seed_ts[k]))
+            return fail(e, RCA_ERR_ARG, "rca_expand_many: plan %d: with_states needs seed_ts", k);
+        int rc = validate_plan(e, &plans[k]);
+        if (rc) return rc;
+        total_seeds += n_seeds[k];
+        max_seeds = std::max<long long>(max_seeds, n_seeds[k]);
+        any_ts |= plans[k].with_states != 0;
+    }
+    CK(cudaSetDevice(e->device));
+    int rc;
+    // per-plan tables and control blocks, host (pinned) and device
+    const size_t pt_stride = ((size_t)kPtBytes + 255) & ~(size_t)255;
+    if ((size_t)n_plans > e->many_cap) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->m_ptab) CK(cudaFree(e->m_ptab));
+        if (e->m_ctl) CK(cudaFree(e->m_ctl));
+        if (e->mh_ptab) CK(cudaFreeHost(e->mh_ptab));
+        if (e->mh_ctl) CK(cudaFreeHost(e->mh_ctl));
+        e->m_ptab = nullptr; e->m_ctl = nullptr; e->mh_ptab = nullptr; e->mh_ctl = nullptr; e->many_cap = 0;
+        const size_t cap = (size_t)n_plans + 8;
+        CK(cudaMalloc((void **)&e->m_ptab, cap * pt_stride));
+        CK(cudaMalloc((void **)&e->m_ctl, cap * sizeof(Ctl)));
+        CK(cudaMallocHost((void **)&e->mh_ptab, cap * pt_stride));
+        CK(cudaMallocHost((void **)&e->mh_ctl, cap * sizeof(Ctl)));
+        e->many_cap = cap;
+    }
+    while (e->ev_many.size() < (size_t)n_plans + 1) {
+        cudaEvent_t ev;
+        CK(cudaEventCreate(&ev));
+        e->ev_many.push_back(ev);
+    }
+    std::vector<PreparedPlan> pps((size_t)n_plans);
+    bool any_fused = false, any_split = false;
+    for (int k = 0; k < n_plans; k++) {
+        prepare_plan(e, &plans[k], n_seeds[k], e->mh_ptab + (size_t)k * pt_stride, pps[k]);
+        any_fused |= pps[k].fused;
+        any_split |= !pps[k].fused;
+    }
+    CK(cudaMemcpyAsync(e->m_ptab, e->mh_ptab, (size_t)n_plans * pt_stride, cudaMemcpyHostToDevice, e->stream));
+    // seeds: one staging buffer holds every plan's seeds back to back
+    std::vector<long long> at((size_t)n_plans, 0);
+    if (!seeds_on_device) {
+        long long off = 0;
+        for (int k = 0; k < n_plans; k++) {
+            at[k] = off;
+            rc = stage_seeds(e, seeds[k], seed_ts ? seed_ts[k] : nullptr, n_seeds[k], plans[k].with_states != 0, off, total_seeds);
+            if (rc) return rc;
+            off += n_seeds[k];
+        }
+        (void)any_ts;
+    }
+    if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * max_seeds, 1ull << 20)); if (rc) return rc; }
+    if (!e->out) { rc = grow(e, &e->out, &e->ocap, std::max<unsigned long long>(64ull * total_seeds, 1ull << 22)); if (rc) return rc; }
+
+    int retries = 0;
+    std::vector<int> launches((size_t)n_plans, 0);
+    while (true) {
+        unsigned long long groups = 0;
+        rc = ensure_tile_arrays(e, max_seeds, any_fused, any_split, &groups);
+        if (rc) return rc;
+        for (int k = 0; k < n_plans; k++) {
+            std::memset(&e->mh_ctl[k], 0, sizeof(Ctl));
+            e->mh_ctl[k].F[0] = (unsigned long long)n_seeds[k];
+            launches[k] = 0;
+        }
+        CK(cudaMemcpyAsync(e->m_ctl, e->mh_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+        CK(cudaEventRecord(e->ev_many[0], e->stream));
+        for (int k = 0; k < n_plans; k++) {
+            RunBufs b;
+            b.seeds = seeds_on_device ? seeds[k] : e->seeds_buf + at[k];
+            b.ts = plans[k].with_states ? (seeds_on_device ? (const long long *)seed_ts[k] : e->ts_buf + at[k]) : nullptr;
+            b.n_seeds = n_seeds[k]; b.ctl = e->m_ctl + k; b.ptab = e->m_ptab + (size_t)k * pt_stride; b.epoch = 0; b.groups = groups;
+            if (pps[k].fused) { rc = next_epoch(e, &b.epoch); if (rc) return rc; }
+            else CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
+            rc = launch_levels(e, pps[k], b, nullptr, &launches[k]);
+            if (rc) return rc;
+            if (k + 1 < n_plans) {                    // the next plan's rows start where this plan's end
+                RowLens rl;
+                for (int j = 0; j <= RCA_MAX_HOPS; j++) rl.v[j] = plans[k].count_only ? 0 : row_len_of(&plans[k], j);
+                chain_plans<<<1, 32, 0, e->stream>>>(e->m_ctl + k, e->m_ctl + k + 1, rl);
+                CK(cudaGetLastError());
+            }
+            CK(cudaEventRecord(e->ev_many[k + 1], e->stream));
+        }
+        CK(cudaMemcpyAsync(e->mh_ctl, e->m_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        unsigned ov = 0;
+        for (int k = 0; k < n_plans; k++) ov |= e->mh_ctl[k].overflow;
+        if (!ov) break;
+        if (++retries > 12) return fail(e, RCA_ERR_NOMEM, "rca_expand_many: scratch arenas still too small after %d retries", retries);
+        unsigned long long fneed = 0, oneed = 0;
+        for (int k = 0; k < n_plans; k++) {
+            unsigned long long f = 0;
+            const int L = pps[k].L;
+            for (int s = 1; s <= L; s++) { f += e->mh_ctl[k].F[s]; oneed += e->mh_ctl[k].N[s] * (unsigned long long)row_len_of(&plans[k], s); }
+            fneed = std::max(fneed, f);
+        }
+        if (ov & 1u) { rc = grow(e, &e->frontier, &e->fcap, std::max(e->fcap * 2, fneed + fneed / 4)); if (rc) return rc; }
+        if (ov & 2u) { rc = grow(e, &e->out, &e->ocap, std::max(e->ocap * 2, oneed + oneed / 4)); if (rc) return rc; }
+    }
+    e->results.assign((size_t)n_plans, PlanResult());
+    for (int k = 0; k < n_plans; k++) {
+        publish_result(e, e->results[k], &plans[k], pps[k].L, &e->mh_ctl[k]);
+        if (stats) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e->ev_many[k], e->ev_many[k + 1]);
+            fill_stats(&stats[k], &plans[k], pps[k].L, n_seeds[k], &e->mh_ctl[k], ms, launches[k], retries);
+        }
+    }
+    return RCA_OK;
+}
+
+extern "C" int rca_result_select(rca_engine_t *e, int32_t plan_index) {
+    if (!e) return RCA_ERR_ARG;
+    if (plan_index < 0 || (size_t)plan_index >= e->results.size()) return fail(e, RCA_ERR_ARG, "rca_result_select: no plan %d in the last submission", plan_index);
+    e->selected = plan_index;
+    return RCA_OK;
+}
+
+static const PlanResult *current_result(const rca_engine *e) {
+    if (e->selected < 0 || (size_t)e->selected >= e->results.size() || !e->results[e->selected].valid) return nullptr;
+    return &e->results[e->selected];
+}
+
 extern "C" int rca_result_level(const rca_engine_t *e, int level, const int32_t **dev_rows, int64_t *n_rows, int32_t *row_len) {
     if (!e || level < 0 || level > RCA_MAX_HOPS) return RCA_ERR_ARG;
-    if (!e->have_result) return fail(const_cast<rca_engine *>(e), RCA_ERR_ARG, "rca_result_level: no result held (call rca_expand first)");
-    if (dev_rows) *dev_rows = e->res_rows[level] ? e->out + e->res_base[level] : nullptr;
-    if (n_rows) *n_rows = e->res_rows[level];
-    if (row_len) *row_len = e->res_row_len[level];
+    const PlanResult *r = current_result(e);
+    if (!r) return fail(const_cast<rca_engine *>(e), RCA_ERR_ARG, "rca_result_level: no result held (call rca_expand first)");
+    if (dev_rows) *dev_rows = r->rows[level] ? e->out + r->base[level] : nullptr;
+    if (n_rows) *n_rows = r->rows[level];
+    if (row_len) *row_len = r->row_len[level];
     return RCA_OK;
 }
 
 extern "C" int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows) {
     if (!e || level < 0 || level > RCA_MAX_HOPS) return RCA_ERR_ARG;
-    if (!e->have_result) return fail(e, RCA_ERR_ARG, "rca_result_copy: no result held (call rca_expand first)");
-    const size_t words = (size_t)e->res_rows[level] * (size_t)e->res_row_len[level];
+    const PlanResult *r = current_result(e);
+    if (!r) return fail(e, RCA_ERR_ARG, "rca_result_copy: no result held (call rca_expand first)");
+    const size_t words = (size_t)r->rows[level] * (size_t)r->row_len[level];
     if (!words) return RCA_OK;
     if (!host_rows) return fail(e, RCA_ERR_ARG, "rca_result_copy: null buffer");
     CK(cudaSetDevice(e->device));
-    CK(cudaMemcpyAsync(host_rows, e->out + e->res_base[level], words * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(host_rows, e->out + r->base[level], words * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return RCA_OK;
 }

@@ -86,6 +86,7 @@ struct Ctl {                          // device control block, one per engine
     unsigned long long N[kLv];        // rows emitted per level  (level s occupies output words sum N[j]*row_len[j] ..)
     unsigned long long E[kLv];        // candidates scanned per level
     unsigned long long subF, subN;    // split path: entries / rows written by earlier sub-launches of the level
+    unsigned long long out_base;      // first output word of this plan (plans of one submission share the arena)
     unsigned int ticket[kLv];         // fused path: tile tickets
     unsigned int overflow;            // bit0 frontier arena, bit1 output arena
     unsigned int pad;
@@ -543,7 +544,7 @@ __device__ __forceinline__ LevelCtx level_setup(const LevelParams &p, TablesSm &
     c.w.anc_n = reinterpret_cast<int *>(c.w.W + 1);
     c.w.anc_r = c.w.anc_n + s * kTile;
     c.w.stage = c.w.anc_r + s * kTile;
-    unsigned long long fb_s = 0, ob_s = 0;
+    unsigned long long fb_s = 0, ob_s = ctl->out_base;
     for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
     c.fb_s = fb_s; c.ob_s = ob_s;
     c.Fq = ctl->F[q];
@@ -588,7 +589,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
     Ctl *ctl = p.ctl;
     if (ctl->overflow) return;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, s = p.s, q = s - 1;
-    unsigned long long fb_s = 0, ob_s = 0;
+    unsigned long long fb_s = 0, ob_s = ctl->out_base;
     for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
     const unsigned long long Fq = ctl->F[q];
     const unsigned long long ntiles = (Fq + kTile - 1) / kTile;
@@ -750,6 +751,17 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
     if (lane == 0) {
         if (scanned) atomicAdd(&ctl->E[s], scanned);
         if (ov) atomicOr(&ctl->overflow, ov);
+    }
+}
+
+// rca_expand_many: the next plan's rows start where this plan's end (row_len 0 for count-only plans)
+struct RowLens { int v[RCA_MAX_HOPS + 1]; };
+__global__ void chain_plans(const Ctl *prev, Ctl *next, RowLens rl) {
+    if (threadIdx.x == 0) {
+        unsigned long long end = prev->out_base;
+        for (int j = 1; j <= RCA_MAX_HOPS; j++) end += prev->N[j] * (unsigned long long)rl.v[j];
+        next->out_base = end;
+        if (prev->overflow) next->overflow = prev->overflow;      // a void run voids what follows it
     }
 }
 

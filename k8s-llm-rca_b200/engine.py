@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold", "rca_reserve",
-           "rca_expand", "rca_expand_static",
+           "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_text_load",
            "rca_text_contains", "rca_version")
 
@@ -88,6 +88,9 @@ def load_library(path: str | None = None):
                                C.POINTER(StatsDesc)]
     lib.rca_expand_static.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.c_int64, C.POINTER(StatsDesc)]
+    lib.rca_expand_many.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
+                                    C.POINTER(C.c_void_p), C.c_int, C.POINTER(StatsDesc)]
+    lib.rca_result_select.argtypes = [C.c_void_p, C.c_int32]
     lib.rca_result_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
                                      C.POINTER(C.c_int32)]
     lib.rca_result_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -178,6 +181,7 @@ class ExpandResult:
         self.retries = int(st.retries)
         self._gen = engine._gen
         self.count_only = False
+        self.index = 0                 # position in the submission (expand_many)
 
     def rows(self, level: int, out: np.ndarray | None = None) -> np.ndarray:
         """Copy the rows of one level to the host.  `out`: optional pre-allocated (ideally pinned)
@@ -186,6 +190,7 @@ class ExpandResult:
         n, w = self.emitted[level], self.row_len[level]
         if self.count_only and n:
             raise ValueError("the plan ran with count_only: there are no rows to copy")
+        self.engine._ck(self.engine.lib.rca_result_select(self.engine.h, self.index))
         if out is not None:
             flat = out.reshape(-1)
             assert flat.dtype == np.int32 and flat.size >= n * w and flat.flags.c_contiguous
@@ -203,6 +208,7 @@ class ExpandResult:
         """(device pointer, n_rows, row_len) - for consumers that stay on the GPU (NCCL gather)."""
         assert self._gen == self.engine._gen, "result was overwritten by a later expand()"
         p, n, w = C.c_void_p(), C.c_int64(), C.c_int32()
+        self.engine._ck(self.engine.lib.rca_result_select(self.engine.h, self.index))
         self.engine._ck(self.engine.lib.rca_result_level(self.engine.h, level, C.byref(p), C.byref(n), C.byref(w)))
         return (p.value or 0), int(n.value), int(w.value)
 
@@ -287,6 +293,42 @@ class Engine:
         res = ExpandResult(self, st, levels)
         res.count_only = bool(plan.count_only)
         return res
+
+    def expand_many(self, plans, seeds_list, ts_list=None):
+        """Several plans in one submission (rca_expand_many): one synchronisation for the whole set.
+        seeds_list[k] / ts_list[k]: numpy arrays, or CUDA tensors for all plans.  -> [ExpandResult]."""
+        n = len(plans)
+        arr = (PlanDesc * n)(*plans)
+        keep, sp, tp, ns, devs = [], (C.c_void_p * n)(), (C.c_void_p * n)(), (C.c_int64 * n)(), set()
+        for k in range(n):
+            s = seeds_list[k]
+            if isinstance(s, (list, tuple)) or (isinstance(s, np.ndarray) and s.dtype != np.int32):
+                s = np.ascontiguousarray(s, dtype=np.int32)
+            ptr, dev, ka = _dev_ptr(s)
+            keep.append(ka)
+            sp[k], ns[k] = ptr, int(ka.shape[0])
+            devs.add(dev)
+            t = ts_list[k] if ts_list is not None else None
+            if t is not None:
+                if not hasattr(t, "data_ptr"):
+                    t = np.ascontiguousarray(t, dtype=np.int64)
+                tptr, tdev, kt = _dev_ptr(t)
+                keep.append(kt)
+                tp[k] = tptr
+                devs.add(tdev)
+        if len(devs) > 1:
+            raise ValueError("all seed / timestamp buffers must be host arrays or all device tensors")
+        st = (StatsDesc * n)()
+        self._gen += 1
+        self._ck(self.lib.rca_expand_many(self.h, arr, n, sp, ns, tp, devs.pop() if devs else 0, st))
+        out = []
+        for k in range(n):
+            levels = plans[k].max_hops if plans[k].kind == PLAN_VARLEN else plans[k].n_steps
+            r = ExpandResult(self, st[k], levels)
+            r.count_only = bool(plans[k].count_only)
+            r.index = k
+            out.append(r)
+        return out
 
     def expand_static(self, plan: PlanDesc, dev_seeds, dev_seed_ts, dev_rows):
         """rca_expand_static: expansion that allocates nothing (fixed scratch inside the library; see

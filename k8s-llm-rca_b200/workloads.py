@@ -78,9 +78,19 @@ class Config3:
             ts = ts + rank * 3_600_000
         return pods.astype(np.int32), ev, ts
 
-    def run(self, eng: E.Engine, pods, ev, ts, fetch=None):
-        """One step.  `fetch(result)` is called after each expansion while its rows are still
-        resident (e2e runs copy them out there).  Returns (instances, [ExpandResult...])."""
+    def run(self, eng: E.Engine, pods, ev, ts, fetch=None, batched=True):
+        """One step.  `fetch(result)` is called for each expansion while its rows are still resident
+        (e2e runs copy them out there).  Returns (instances, [(name, ExpandResult)...]).
+        batched: the six plans go to the engine as ONE submission (rca_expand_many); otherwise six calls."""
+        if batched:
+            t = ts if self.with_states else None
+            names = ["varlen"] + list(self.chains)
+            plans = [self.varlen] + [c[2] for c in self.chains.values()]
+            res = eng.expand_many(plans, [pods] + [ev] * len(self.chains), [t] * len(plans) if t is not None else None)
+            if fetch:
+                for r in res:
+                    fetch(r)
+            return sum(r.total for r in res), list(zip(names, res))
         results = []
         total = 0
         r = eng.expand(self.varlen, pods, ts if self.with_states else None)

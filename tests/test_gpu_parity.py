@@ -291,3 +291,45 @@ def test_count_only_plans(eng_10k, snap_10k):
     assert cnt.emitted == full.emitted and cnt.frontier == full.frontier and cnt.scanned == full.scanned
     with pytest.raises(ValueError):
         cnt.rows(3)
+
+
+def test_expand_many_equals_separate_calls(snap_10k):
+    """One submission of several plans == the same plans one call at a time (rows, order, counters)."""
+    from k8s_llm_rca_b200 import engine, workloads
+    for threshold in (None, 0, 1 << 40):
+        w = workloads.Config3(snap=snap_10k)
+        eng = engine.Engine(snap_10k)
+        if threshold is not None:
+            eng.set_fused_threshold(threshold)
+        pods, ev, ts = w.batch(0)
+        names = ["varlen"] + list(w.chains)
+        plans = [w.varlen] + [c[2] for c in w.chains.values()]
+        seeds = [pods] + [ev] * len(w.chains)
+        single = []
+        for p, s in zip(plans, seeds):
+            r = eng.expand(p, s, ts)
+            single.append((r.emitted, r.frontier, r.scanned, r.all_rows()))
+        many = eng.expand_many(plans, seeds, [ts] * len(plans))
+        for (em, fr, sc, rows), r, name in zip(single, many, names):
+            assert r.emitted == em and r.frontier == fr and r.scanned == sc, name
+            got = r.all_rows()
+            assert got.keys() == rows.keys()
+            for lvl in rows:
+                assert np.array_equal(got[lvl], rows[lvl]), (name, lvl)
+        # a tiny arena: the whole submission is re-run after growing
+        eng2 = engine.Engine(snap_10k)
+        if threshold is not None:
+            eng2.set_fused_threshold(threshold)
+        eng2.reserve(64, 256)
+        again = eng2.expand_many(plans, seeds, [ts] * len(plans))
+        assert again[0].retries >= 1
+        for (em, _, _, rows), r in zip(single, again):
+            assert r.emitted == em and all(np.array_equal(r.rows(lvl), rows[lvl]) for lvl in rows)
+        # mixed with a count-only plan and an empty seed list
+        cnt = engine.varlen_plan("und", 3, dest_kind=snap_10k.kind_index("Node"), excl_kinds=w.excl, entity_only=True,
+                                 count_only=True)
+        mix = eng.expand_many([cnt, plans[1], plans[2]], [pods, ev, np.zeros(0, np.int32)], [None, ts, ts[:0]])
+        assert mix[0].total > 0 and mix[2].total == 0
+        assert np.array_equal(mix[1].rows(3), single[1][3][3])
+        eng.close()
+        eng2.close()
