@@ -140,8 +140,8 @@ int rca_expand(rca_engine_t *e, const rca_plan_t *plan, const int32_t *seeds, in
  * time): the plans run back to back on the engine's stream with one upload, one download and ONE
  * synchronisation for the whole set; plan k's rows follow plan k-1's in the output arena.
  * seeds[k] / n_seeds[k] / seed_ts[k] (seed_ts, or its entries for plans without with_states, may be
- * null) are all host or all device memory.  stats (nullable) receives n_plans entries; level_ms is
- * not filled, kernel_ms is the plan's share of the stream time.  rca_result_select chooses the plan
+ * null) are all host or all device memory.  stats (nullable) receives n_plans entries (kernel_ms = the
+ * plan's own launches).  rca_result_select chooses the plan
  * that rca_result_level / rca_result_copy address (plan 0 after the call). */
 int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t n_plans, const int32_t *const *seeds,
                     const int64_t *n_seeds, const int64_t *const *seed_ts, int seeds_on_device, rca_stats_t *stats);

@@ -763,7 +763,8 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
         CK(cudaMallocHost((void **)&e->mh_ctl, cap * sizeof(Ctl)));
         e->many_cap = cap;
     }
-    while (e->ev_many.size() < (size_t)n_plans + 1) {
+    const size_t ev_stride = RCA_MAX_HOPS + 2;        // per plan: start, then one event per level
+    while (e->ev_many.size() < (size_t)n_plans * ev_stride) {
         cudaEvent_t ev;
         CK(cudaEventCreate(&ev));
         e->ev_many.push_back(ev);
@@ -803,15 +804,16 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
             launches[k] = 0;
         }
         CK(cudaMemcpyAsync(e->m_ctl, e->mh_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
-        CK(cudaEventRecord(e->ev_many[0], e->stream));
         for (int k = 0; k < n_plans; k++) {
+            cudaEvent_t *evk = e->ev_many.data() + (size_t)k * ev_stride;
             RunBufs b;
             b.seeds = seeds_on_device ? seeds[k] : e->seeds_buf + at[k];
             b.ts = plans[k].with_states ? (seeds_on_device ? (const long long *)seed_ts[k] : e->ts_buf + at[k]) : nullptr;
             b.n_seeds = n_seeds[k]; b.ctl = e->m_ctl + k; b.ptab = e->m_ptab + (size_t)k * pt_stride; b.epoch = 0; b.groups = groups;
             if (pps[k].fused) { rc = next_epoch(e, &b.epoch); if (rc) return rc; }
             else CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
-            rc = launch_levels(e, pps[k], b, nullptr, &launches[k]);
+            CK(cudaEventRecord(evk[0], e->stream));
+            rc = launch_levels(e, pps[k], b, evk, &launches[k]);
             if (rc) return rc;
             if (k + 1 < n_plans) {                    // the next plan's rows start where this plan's end
                 RowLens rl;
@@ -819,7 +821,6 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
                 chain_plans<<<1, 32, 0, e->stream>>>(e->m_ctl + k, e->m_ctl + k + 1, rl);
                 CK(cudaGetLastError());
             }
-            CK(cudaEventRecord(e->ev_many[k + 1], e->stream));
         }
         CK(cudaMemcpyAsync(e->mh_ctl, e->m_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
@@ -841,9 +842,14 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
     for (int k = 0; k < n_plans; k++) {
         publish_result(e, e->results[k], &plans[k], pps[k].L, &e->mh_ctl[k]);
         if (stats) {
+            cudaEvent_t *evk = e->ev_many.data() + (size_t)k * ev_stride;
             float ms = 0.f;
-            cudaEventElapsedTime(&ms, e->ev_many[k], e->ev_many[k + 1]);
+            cudaEventElapsedTime(&ms, evk[0], evk[pps[k].L]);
             fill_stats(&stats[k], &plans[k], pps[k].L, n_seeds[k], &e->mh_ctl[k], ms, launches[k], retries);
+            for (int s = 1; s <= pps[k].L; s++) {
+                float t = 0.f;
+                if (cudaEventElapsedTime(&t, evk[s - 1], evk[s]) == cudaSuccess) stats[k].level_ms[s] = t;
+            }
         }
     }
     return RCA_OK;
