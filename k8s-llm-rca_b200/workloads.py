@@ -122,7 +122,7 @@ class Config3:
             cols = [rows]
             miss = np.zeros(len(rows), np.int64)
             for d in range(length + 1):
-                first, cnt, _ = orc.states(rows[:, d], t, limit=1)
+                first, cnt, _ = orc.states(rows[:, d], t, limit=1, threads=threads)
                 cols.append(first[:, None])
                 miss |= (cnt == 0).astype(np.int64) << d
             cols.append(miss.astype(np.int32)[:, None])

@@ -104,7 +104,7 @@ class CsrOracle:
             raise ValueError("bad arguments")
         return self._take(out.value, n, 2 * L + 1), int(sc.value)
 
-    def states(self, nodes, ts, limit=10, ts_hi=None):
+    def states(self, nodes, ts, limit=10, ts_hi=None, threads=0):
         nodes = np.ascontiguousarray(np.asarray(nodes, np.int32))
         ts = np.ascontiguousarray(np.asarray(ts, np.int64))
         hi = ts if ts_hi is None else np.ascontiguousarray(np.asarray(ts_hi, np.int64))
@@ -113,5 +113,5 @@ class CsrOracle:
         cnt = np.empty(n, np.int32)
         ids = np.empty((n, limit), np.int32)
         self.lib.orc_states(C.byref(self.g), _ptr(nodes), _ptr(ts), _ptr(hi), C.c_int64(n), limit, _ptr(first), _ptr(cnt),
-                            _ptr(ids))
+                            _ptr(ids), int(threads))
         return first, cnt, ids

@@ -239,8 +239,13 @@ int64_t orc_chain(const orc_graph_t *g, const int32_t *et, const int32_t *dir, i
  * with tmin <= ts[i] and tmax > ts_hi[i] (ts_hi == ts: the strict form; :51-60 is the loose form).  first[i] = lowest matching STATE node id or -1, cnt[i] = number
  * of matches; ids (may be NULL) receives up to `limit` ids per query, -1 padded. */
 void orc_states(const orc_graph_t *g, const int32_t *nodes, const int64_t *ts, const int64_t *ts_hi, int64_t n, int limit,
-                int32_t *first, int32_t *cnt, int32_t *ids) {
-#pragma omp parallel for schedule(static)
+                int32_t *first, int32_t *cnt, int32_t *ids, int threads) {
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+#else
+    threads = 1;
+#endif
+#pragma omp parallel for schedule(static) num_threads(threads)
     for (int64_t i = 0; i < n; i++) {
         int32_t v = nodes[i], c = 0, f = -1;
         for (int32_t j = g->st_off[v]; j < g->st_off[v + 1]; j++) {
