@@ -127,6 +127,10 @@ int rca_set_stream(rca_engine_t *e, uint64_t cuda_stream);
  * suits them much longer); this call sets both.
  * No counterpart in the reference: it is a tuning knob of this engine. */
 int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds);
+/* Typed chains whose steps fan out little - product of the steps' largest adjacency-row lengths at
+ * most `max_rows_per_seed` (default 64; 0 switches this off) - run as ONE depth-first launch instead
+ * of one launch per step.  Same rows, same order, same counters.  No counterpart in the reference. */
+int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_seed);
 /* pre-size the scratch arenas: frontier entries (16 B each) and output words (4 B each) */
 int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words);
 

@@ -62,6 +62,7 @@ struct rca_engine {
     ulonglong2 *gsum = nullptr, *gscan = nullptr;   // split path: group sums (zeroed per call) and their scan
     unsigned long long gcap = 0;
     long long fused_max_seeds = 16384;    // up to this many seeds a variable-length plan runs one fused launch per level
+    long long chain_walk_fanout = 64;     // typed chains whose per-seed fan-out is at most this run as one depth-first launch
     long long chain_fused_max_seeds = 1 << 20;   // typed chains have uniform tiles: the fused launch suits them far longer
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
@@ -402,6 +403,12 @@ extern "C" int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds) {
     return RCA_OK;
 }
 
+extern "C" int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_seed) {
+    if (!e || max_rows_per_seed < 0) return RCA_ERR_ARG;
+    e->chain_walk_fanout = max_rows_per_seed;
+    return RCA_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // One plan, prepared on the host: its table (kind boundaries, one kind-action row per level,
 // node-block -> kind table, one arrival row per level) and, per level, how to launch it.
@@ -409,6 +416,7 @@ struct Sub { int t, d; };
 struct PreparedPlan {
     const rca_plan_t *pl = nullptr;
     bool varlen = false, fused = false, arr_prune = false;
+    bool walk = false;                           // typed chain with little fan-out: one chain_walk launch
     int L = 0, mode = kModeChain;
     std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
     std::vector<char> level_typed, level_dead;
@@ -420,6 +428,13 @@ static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, u
     pp.L = pp.varlen ? pl->max_hops : pl->n_steps;
     pp.mode = !pp.varlen ? kModeChain : (pl->node_simple ? kModeSimple : kModeRelUnique);
     pp.fused = n_seeds <= (pp.varlen ? e->fused_max_seeds : e->chain_fused_max_seeds);
+    if (!pp.varlen && pp.fused && e->chain_walk_fanout > 0) {
+        // product of the steps' largest row lengths bounds the rows (and the work) of one seed
+        long long fan = 1;
+        for (int i = 0; i < pl->n_steps && fan <= e->chain_walk_fanout; i++)
+            fan *= std::max(1, pl->step_dir[i] == RCA_DIR_OUT ? e->et_max_out[pl->step_etype[i]] : e->et_max_in[pl->step_etype[i]]);
+        pp.walk = fan <= e->chain_walk_fanout;
+    }
     const int L = pp.L;
     std::memset(t, 0, kPtBytes);
     int *ks = reinterpret_cast<int *>(t + kPtKs);
@@ -489,6 +504,31 @@ struct RunBufs {
 static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b, cudaEvent_t *ev_lv, int *launches) {
     const rca_plan_t *pl = pp.pl;
     const int L = pp.L;
+    if (pp.walk) {                                    // the whole chain in one launch
+        ChainParams c;
+        std::memset(&c, 0, sizeof c);
+        c.L = L;
+        for (int i = 0; i < L; i++) {
+            const int t = pl->step_etype[i];
+            const bool out = pl->step_dir[i] == RCA_DIR_OUT;
+            const int rowk = out ? e->et_src[t] : e->et_dst[t];
+            c.rng[i] = out ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t];
+            c.row_lo[i] = e->kind_start[rowk];
+            c.row_hi[i] = e->kind_start[rowk + 1];
+            c.against[i] = out ? 0 : 1;
+        }
+        c.adj1 = e->out_dst; c.adj2 = e->in_adj; c.n_nodes = e->n_nodes;
+        c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
+        c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
+        c.out = e->out; c.ocap = e->ocap; c.ctl = b.ctl; c.tstate = e->tstate;
+        c.st_off = e->st_off; c.st_rec = e->st_rec;
+        const long long blocks = std::max<long long>(1, (b.n_seeds + kThreads - 1) / kThreads);
+        chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
+        ++*launches;
+        CK(cudaGetLastError());
+        if (ev_lv) for (int s = 1; s <= L; s++) CK(cudaEventRecord(ev_lv[s], e->stream));
+        return RCA_OK;
+    }
     for (int s = 1; s <= L; s++) {
         LevelParams p;
         std::memset(&p, 0, sizeof p);

@@ -754,6 +754,142 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// chain_walk: a whole typed chain (generate_query/generate_query.py:241-260) in ONE launch, for chains
+// whose steps fan out little (the engine checks the per-edge-type maximum degrees).  One thread per
+// seed walks the steps depth-first twice: once to count its rows, once - after a warp scan and the
+// same decoupled look-back the fused kernel uses - to write them.  Rows come out ordered by seed and
+// then by adjacency slot at each step, which is exactly the order of the level-wise kernels.
+struct ChainParams {
+    int L;
+    const int2 *rng[RCA_MAX_HOPS];    // typed (begin, end) table of step i, indexed by node - row_lo[i]
+    int row_lo[RCA_MAX_HOPS], row_hi[RCA_MAX_HOPS];
+    int against[RCA_MAX_HOPS];        // step walks in_adj (neighbour, rel) instead of out_dst
+    const int *adj1;
+    const int2 *adj2;
+    int n_nodes;
+    int with_states, count_only, row_len;
+    unsigned epoch;
+    const int *seeds;
+    const long long *seed_ts;
+    long long n_seeds;
+    int *out;
+    unsigned long long ocap;
+    Ctl *ctl;
+    ulonglong2 *tstate;
+    const int *st_off;
+    const StRec *st_rec;
+};
+
+template <bool FILL>
+__device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, int seed, long long ts, int *dst,
+                                                        unsigned long long *scanned, unsigned long long *alive) {
+    int node[RCA_MAX_HOPS + 1], rel[RCA_MAX_HOPS], cur[RCA_MAX_HOPS], end[RCA_MAX_HOPS];
+    unsigned long long rows = 0;
+    const int L = p.L;
+    node[0] = seed;
+    if (seed < p.row_lo[0] || seed >= p.row_hi[0]) return 0;
+    {
+        const int2 r = __ldg(p.rng[0] + (seed - p.row_lo[0]));
+        cur[0] = r.x; end[0] = r.y;
+        if (!FILL) scanned[1] += (unsigned long long)(r.y - r.x);
+    }
+    int d = 0;
+    while (d >= 0) {
+        if (cur[d] >= end[d]) { d--; continue; }
+        const int slot = cur[d]++;
+        int v, r;
+        if (p.against[d]) {
+            const int2 a = __ldg(p.adj2 + slot);
+            v = a.x; r = a.y & kRelMask;
+        } else {
+            v = __ldg(p.adj1 + slot);
+            r = slot;
+        }
+        node[d + 1] = v; rel[d] = r;
+        if (!FILL) alive[d + 1]++;
+        if (d + 1 == L) {
+            if (FILL) {
+                int *row = dst + rows * (unsigned long long)p.row_len;
+                for (int k = 0; k <= L; k++) row[k] = node[k];
+                for (int k = 0; k < L; k++) row[L + 1 + k] = rel[k];
+                if (p.with_states) {
+                    unsigned miss = 0;
+                    for (int k = 0; k <= L; k++) {
+                        int first, cnt;
+                        state_probe(p.st_off, p.st_rec, node[k], ts, first, cnt);
+                        row[2 * L + 1 + k] = first;
+                        miss |= (cnt == 0 ? 1u : 0u) << k;
+                    }
+                    row[3 * L + 2] = (int)miss;
+                }
+            }
+            rows++;
+            continue;
+        }
+        d++;
+        if (v >= p.row_lo[d] && v < p.row_hi[d]) {
+            const int2 rg = __ldg(p.rng[d] + (v - p.row_lo[d]));
+            cur[d] = rg.x; end[d] = rg.y;
+            if (!FILL) scanned[d + 1] += (unsigned long long)(rg.y - rg.x);
+        } else {
+            cur[d] = end[d] = 0;
+        }
+    }
+    return rows;
+}
+
+__global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ ChainParams p) {
+    const int lane = threadIdx.x & 31;
+    Ctl *ctl = p.ctl;
+    const unsigned ntiles = (unsigned)((p.n_seeds + 31) / 32);
+    const int L = p.L;
+    unsigned long long sc[RCA_MAX_HOPS + 1], al[RCA_MAX_HOPS + 1];
+    for (int k = 0; k <= RCA_MAX_HOPS; k++) { sc[k] = 0; al[k] = 0; }
+    unsigned long long total_rows = 0;
+    bool ov = false;
+    while (true) {
+        unsigned tile = 0;
+        if (lane == 0) tile = atomicAdd(&ctl->ticket[L], 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= ntiles) break;
+        const long long i = (long long)tile * 32 + lane;
+        int seed = -1;
+        long long ts = 0;
+        if (i < p.n_seeds) {
+            seed = __ldg(p.seeds + i);
+            if (p.with_states) ts = __ldg(p.seed_ts + i);
+        }
+        unsigned long long mine = 0;
+        if (seed >= 0 && seed < p.n_nodes) mine = chain_dfs<false>(p, seed, ts, nullptr, sc, al);
+        unsigned long long incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        const unsigned long long tile_rows = __shfl_sync(0xffffffffu, incl, 31);
+        unsigned long long pre_f, pre_e;
+        tile_lookback(p.tstate, tile, p.epoch, 0ull, tile_rows, pre_f, pre_e);
+        if (tile == ntiles - 1 && lane == 0) ctl->N[L] = pre_e + tile_rows;
+        total_rows += 0;
+        const unsigned long long base = ctl->out_base + (pre_e + incl - mine) * (unsigned long long)p.row_len;
+        if (!p.count_only && ctl->out_base + (pre_e + tile_rows) * (unsigned long long)p.row_len > p.ocap) ov = true;
+        else if (!p.count_only && mine) chain_dfs<true>(p, seed, ts, p.out + base, nullptr, nullptr);
+    }
+    // counters: partial paths alive after each step and entries scanned at each step
+    for (int k = 1; k <= L; k++) {
+        unsigned long long a = al[k], b = sc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+        if (lane == 0) {
+            if (a && k < L) atomicAdd(&ctl->F[k], a);
+            if (b) atomicAdd(&ctl->E[k], b);
+        }
+    }
+    if (ov && lane == 0) atomicOr(&ctl->overflow, 2u);
+}
+
 // rca_expand_many: the next plan's rows start where this plan's end (row_len 0 for count-only plans)
 struct RowLens { int v[RCA_MAX_HOPS + 1]; };
 __global__ void chain_plans(const Ctl *prev, Ctl *next, RowLens rl) {
