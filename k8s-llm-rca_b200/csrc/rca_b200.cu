@@ -392,6 +392,11 @@ static KernelSet pick_kernels(int mode, int q) {
 }
 
 static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
+    // levels 6 to 8 need more than the 48 KB of shared memory (static tables included) a kernel gets without asking
+    if (dyn_smem + 8192u > 48u * 1024u) {
+        const cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem);
+        if (rc != cudaSuccess) std::fprintf(stderr, "rca_b200: cudaFuncSetAttribute(%zu) failed: %s\n", dyn_smem, cudaGetErrorString(rc));
+    }
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem) != cudaSuccess || per_sm < 1) per_sm = 1;
     return e->sm_count * per_sm;

@@ -333,3 +333,12 @@ def test_expand_many_equals_separate_calls(snap_10k):
         assert np.array_equal(mix[1].rows(3), single[1][3][3])
         eng.close()
         eng2.close()
+
+
+def test_eight_hops(eng_small, snap_small, csr_oracle_lib):
+    """RCA_MAX_HOPS deep: levels 6 to 8 need more shared memory than a kernel gets by default."""
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    dep, nfs, ev, ns, node = _kinds(snap_small, "Deployment", "nfs", "Event", "Namespace", "Node")
+    seeds = snap_small.nodes_of_kind(dep)[:4]
+    res = check_varlen(eng_small, orc, seeds, "und", 8, dest_kind=nfs, excl_kinds=[ev, ns, node], entity_only=True)
+    assert res.levels == 8
