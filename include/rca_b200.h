@@ -131,6 +131,12 @@ int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds);
  * most `max_rows_per_seed` (default 64; 0 switches this off) - run as ONE depth-first launch instead
  * of one launch per step.  Same rows, same order, same counters.  No counterpart in the reference. */
 int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_seed);
+/* A level of a large variable-length plan that comes down to a typed step over an edge type no node
+ * has two of on the near side (Pod -spec_nodeName-> Node, ownerReferences, claimRef ...) runs through
+ * kernels made for that case: one lane per partial path, no row-length scan, no emission queue, every
+ * load of the lane in flight as early as its address is known.  Same rows, same order, same counters.
+ * on = 0 sends such levels through the general kernels (default on).  No counterpart in the reference. */
+int rca_set_unit_steps(rca_engine_t *e, int on);
 /* pre-size the scratch arenas: frontier entries (16 B each) and output words (4 B each) */
 int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words);
 

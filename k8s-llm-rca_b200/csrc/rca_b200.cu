@@ -47,6 +47,8 @@ struct rca_engine {
     int2 *typed_out = nullptr, *typed_in = nullptr;
     int *out_dst = nullptr, *st_off = nullptr;
     StRec *st_rec = nullptr;              // HasState intervals, one 32 B record each
+    StHead *st_head = nullptr;            // first interval + count + offset per node that can have one (rca_kernels.cuh)
+    int n_head = 0;
     unsigned char *rel_et = nullptr;      // edge type per relationship (only when there are <= 256 edge types)
     std::vector<int> et_max_out, et_max_in;   // largest number of relationships of the type at one start / end node
     // scratch
@@ -63,6 +65,7 @@ struct rca_engine {
     unsigned long long gcap = 0;
     long long fused_max_seeds = 16384;    // up to this many seeds a variable-length plan runs one fused launch per level
     long long chain_walk_fanout = 64;     // typed chains whose per-seed fan-out is at most this run as one depth-first launch
+    bool unit_steps = true;               // typed steps with at most one candidate per path use count_unit / fill_unit
     long long chain_fused_max_seeds = 1 << 20;   // typed chains have uniform tiles: the fused launch suits them far longer
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
@@ -181,6 +184,15 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         std::vector<StRec> rec((size_t)s->n_states);
         for (size_t j = 0; j < rec.size(); j++) rec[j] = StRec{s->st_tmin[j], s->st_tmax[j], s->st_node[j], {0, 0, 0}};
         OCK(upload(&g->st_rec, rec.data(), rec.size()));
+        int last = -1;                                 // entity kinds come first: the table stops at the last node with an interval
+        for (int v = 0; v < s->n_nodes; v++) if (s->st_off[v + 1] > s->st_off[v]) last = v;
+        g->n_head = last + 1;
+        std::vector<StHead> head((size_t)g->n_head);
+        for (int v = 0; v < g->n_head; v++) {
+            const int b = s->st_off[v], c = s->st_off[v + 1] - b;
+            head[v] = c ? StHead{s->st_tmin[b], s->st_tmax[b], s->st_node[b], c, b, 0} : StHead{1, 0, -1, 0, 0, 0};
+        }
+        OCK(upload(&g->st_head, head.data(), head.size()));
     }
     if (s->n_etypes <= 256 && s->rel_et) {
         std::vector<unsigned char> et((size_t)s->n_rels);
@@ -209,7 +221,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_rec, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
+                   e->st_off, e->st_rec, e->st_head, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off, e->m_ptab, e->m_ctl};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
@@ -240,6 +252,12 @@ static int grow(rca_engine *e, T **buf, unsigned long long *cap, unsigned long l
     *cap = 0;
     CK(cudaMalloc((void **)buf, std::max<unsigned long long>(want, 1) * sizeof(T)));
     *cap = want;
+    return RCA_OK;
+}
+
+extern "C" int rca_set_unit_steps(rca_engine_t *e, int on) {
+    if (!e) return RCA_ERR_ARG;
+    e->unit_steps = on != 0;
     return RCA_OK;
 }
 
@@ -391,6 +409,16 @@ static KernelSet pick_kernels(int mode, int q) {
     }
 }
 
+// unit steps (rca_kernels.cuh): typed step, at most one candidate per path, path so far of 2..4 nodes
+template <bool ADJ2>
+static KernelSet pick_unit_kernels(int q) {
+    switch (q) {
+        case 1: return KernelSet{count_unit<ADJ2, 1>, fill_unit<ADJ2, 1>, nullptr};
+        case 2: return KernelSet{count_unit<ADJ2, 2>, fill_unit<ADJ2, 2>, nullptr};
+        default: return KernelSet{count_unit<ADJ2, 3>, fill_unit<ADJ2, 3>, nullptr};
+    }
+}
+
 static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
     // levels 6 to 8 need more than the 48 KB of shared memory (static tables included) a kernel gets without asking
     if (dyn_smem + 8192u > 48u * 1024u) {
@@ -417,7 +445,7 @@ extern "C" int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_s
 // ------------------------------------------------------------------------------------------------
 // One plan, prepared on the host: its table (kind boundaries, one kind-action row per level,
 // node-block -> kind table, one arrival row per level) and, per level, how to launch it.
-struct Sub { int t, d; };
+struct Sub { int t, d, fl, aux; };    // fl / aux: what LevelParams::unit_fl / unit_aux say about the step's far kind
 struct PreparedPlan {
     const rca_plan_t *pl = nullptr;
     bool varlen = false, fused = false, arr_prune = false;
@@ -488,7 +516,8 @@ static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, u
                 if (k & kActDead) continue;
                 const bool emit = (k & kActEmit) != 0;
                 const bool cont = (k & kActCont) && arr[(size_t)s * kArrBytes + a];
-                if (emit || cont) pp.subs[s].push_back(Sub{a >> 1, a & 1});
+                if (emit || cont)
+                    pp.subs[s].push_back(Sub{a >> 1, a & 1, (cont ? 1 : 0) | (emit ? 2 : 0), m.head(a) | ((k & kActInter) ? 1 << 16 : 0)});
                 if (cont)
                     for (int b = 0; b < A; b++) if (!nxt[b] && m.step_ok(a, b)) nxt[b] = 1;
             }
@@ -526,7 +555,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
         c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
         c.out = e->out; c.ocap = e->ocap; c.ctl = b.ctl; c.tstate = e->tstate;
-        c.st_off = e->st_off; c.st_rec = e->st_rec;
+        c.st_head = e->st_head; c.n_head = e->n_head; c.st_rec = e->st_rec;
         const long long blocks = std::max<long long>(1, (b.n_seeds + kThreads - 1) / kThreads);
         chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
         ++*launches;
@@ -570,7 +599,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
         p.ptab = b.ptab;
         p.rel_et = e->rel_et; p.arr_prune = pp.arr_prune;
-        p.st_off = e->st_off; p.st_rec = e->st_rec;
+        p.st_head = e->st_head; p.n_head = e->n_head; p.st_rec = e->st_rec;
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         const long long first = std::max<long long>(1, (b.n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
         if (pp.fused) {
@@ -596,15 +625,24 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                     p.adj2 = e->in_adj;
                 }
                 p.sub = j;
-                const KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
+                KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
+                size_t dyn_c = dyn, dyn_f = dyn;
+                if (pp.level_typed[s] && e->unit_steps && pp.mode == kModeSimple && s >= 2 && s <= 4 &&
+                    (sdir == RCA_DIR_OUT ? e->et_max_out : e->et_max_in)[pp.subs[s][j].t] <= 1) {
+                    ks = sdir == RCA_DIR_OUT ? pick_unit_kernels<false>(s - 1) : pick_unit_kernels<true>(s - 1);
+                    p.unit_fl = pp.subs[s][j].fl;
+                    p.unit_aux = pp.subs[s][j].aux;
+                    dyn_c = 0;
+                    dyn_f = (size_t)kWarps * kTile * p.row_len * sizeof(int);
+                }
                 if (j) CK(cudaMemsetAsync(e->gsum, 0, b.groups * sizeof(ulonglong2), e->stream));
-                int grid = max_grid(e, ks.count, dyn);
+                int grid = max_grid(e, ks.count, dyn_c);
                 if (s == 1) grid = (int)std::min<long long>(grid, first);
-                ks.count<<<grid, kThreads, dyn, e->stream>>>(p);
+                ks.count<<<grid, kThreads, dyn_c, e->stream>>>(p);
                 scan_groups<<<1, 1024, 0, e->stream>>>(p);
-                grid = max_grid(e, ks.fill, dyn);
+                grid = max_grid(e, ks.fill, dyn_f);
                 if (s == 1) grid = (int)std::min<long long>(grid, first);
-                ks.fill<<<grid, kThreads, dyn, e->stream>>>(p);
+                ks.fill<<<grid, kThreads, dyn_f, e->stream>>>(p);
                 *launches += 3;
             }
         }
@@ -1253,7 +1291,7 @@ extern "C" int rca_expand_static(rca_engine_t *e, const rca_plan_t *pl, const in
         p.tstate = reinterpret_cast<ulonglong2 *>(ss + kSsTstate);
         p.ptab = ss + kSsPtab;
         p.rel_et = e->rel_et; p.arr_prune = arr_prune;
-        p.st_off = e->st_off; p.st_rec = e->st_rec;
+        p.st_head = e->st_head; p.n_head = e->n_head; p.st_rec = e->st_rec;
         const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         int grid = max_grid(e, ks.fused, dyn);

@@ -54,6 +54,9 @@ constexpr int kQueue = 64;            // emission queue entries per warp
 #ifndef RCA_MINB_FILL
 #define RCA_MINB_FILL 5       // fill_level keeps several state-probe loads in flight: 48 registers, no spills
 #endif
+#ifndef RCA_MINB_UNIT
+#define RCA_MINB_UNIT 4       // fill_unit: 64 registers, every probe load of a row in flight
+#endif
 
 // plan table in device memory, staged into shared memory per CTA (all offsets multiples of 16 B)
 constexpr int kKindPad = RCA_MAX_KINDS + 4;                                   // kind_start ints, INT_MAX padded
@@ -79,6 +82,14 @@ struct StRec {                        // one HasState interval: exactly one 32 B
     long long tmin, tmax;
     int node;
     int pad[3];
+};
+
+// Per entity node: its first interval inline, the number of intervals, and where the others are
+// (st_rec[off + 1 .. off + cnt)).  One 32 B sector answers the HasState predicate for every node with a
+// single interval, without the offsets -> records round trip.
+struct StHead {
+    long long tmin, tmax;             // (1, 0) when the node has no interval: matches no timestamp
+    int node, cnt, off, pad;
 };
 
 struct Ctl {                          // device control block, one per engine
@@ -127,8 +138,12 @@ struct LevelParams {
     const unsigned char *ptab;        // plan table (layout above)
     const unsigned char *rel_et;      // edge type of every relationship (null: more than 256 edge types)
     int arr_prune;                    // refine 'continue' by the arrival table (edge type, direction)
+    // unit steps (count_unit / fill_unit): the far kind of the typed step is fixed, so its tests are per launch
+    int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row
+    int unit_aux;                     // kind | intermediate-kind flag << 16 of the far kind
     // HasState intervals
-    const int *st_off;
+    const StHead *st_head;            // [n_head]: nodes at or above n_head have no intervals
+    int n_head;
     const StRec *st_rec;
 };
 
@@ -215,19 +230,39 @@ __device__ __forceinline__ int kind_lut(const Tables &T, int v) {
 }
 
 // HasState predicate for one (node, timestamp): lowest matching STATE node id (or -1) and count.
-// One interval = one 32 B record, read with two 16 B loads of the same sector.
-__device__ __forceinline__ void state_probe(const int *st_off, const StRec *rec, int v, long long ts, int &first,
-                                            int &cnt) {
-    const int b = __ldg(st_off + v), e = __ldg(st_off + v + 1);
+// ld_head issues the two 16 B loads of the node's sector; head_finish consumes them (and walks the
+// node's other intervals, if any) - callers put other loads between the two.
+struct HeadRegs {
+    longlong2 iv;
+    int4 m;                           // node, cnt, off
+};
+__device__ __forceinline__ HeadRegs ld_head(const StHead *head, int n_head, int v, bool on) {
+    HeadRegs h;
+    h.iv = make_longlong2(1, 0);
+    h.m = make_int4(-1, 0, 0, 0);
+    if (on && (unsigned)v < (unsigned)n_head) {
+        const longlong2 *q = reinterpret_cast<const longlong2 *>(head + v);
+        h.iv = __ldg(q);
+        h.m = __ldg(reinterpret_cast<const int4 *>(q + 1));
+    }
+    return h;
+}
+__device__ __forceinline__ void head_finish(const HeadRegs &h, const StRec *rec, long long ts, int &first, int &cnt) {
     first = -1;
     cnt = 0;
-    for (int j = b; j < e; j++) {
-        const longlong2 iv = __ldg(reinterpret_cast<const longlong2 *>(rec + j));
-        if (iv.x <= ts && iv.y > ts) {
-            if (cnt == 0) first = __ldg(&rec[j].node);
+    if (h.iv.x <= ts && h.iv.y > ts) { first = h.m.x; cnt = 1; }
+    for (int j = 1; j < h.m.y; j++) {
+        const longlong2 x = __ldg(reinterpret_cast<const longlong2 *>(rec + h.m.z + j));
+        if (x.x <= ts && x.y > ts) {
+            if (cnt == 0) first = __ldg(&rec[h.m.z + j].node);
             cnt++;
         }
     }
+}
+__device__ __forceinline__ void state_probe(const StHead *head, int n_head, const StRec *rec, int v, long long ts, int &first,
+                                            int &cnt) {
+    const HeadRegs h = ld_head(head, n_head, v, true);
+    head_finish(h, rec, ts, first, cnt);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -399,29 +434,16 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
         if constexpr (S >= 0) {
             // the kernel is latency-bound here: issue every column's offset loads, then every column's
             // record loads, back to back - two memory round trips per row instead of 2(S+1)
-            int sb[S + 1], se[S + 1];
+            HeadRegs h[S + 1];
 #pragma unroll
             for (int d = 0; d <= S; d++) {
-                const int nd = active ? ((d <= q) ? w.anc_n[d * kTile + o] : v) : 0;
-                sb[d] = __ldg(p.st_off + nd);
-                se[d] = active ? __ldg(p.st_off + nd + 1) : sb[d];
-            }
-            longlong2 iv[S + 1];
-#pragma unroll
-            for (int d = 0; d <= S; d++) {
-                iv[d] = make_longlong2(1, 0);
-                if (sb[d] < se[d]) iv[d] = __ldg(reinterpret_cast<const longlong2 *>(p.st_rec + sb[d]));
+                const int nd = (d <= q) ? w.anc_n[d * kTile + o] : v;
+                h[d] = ld_head(p.st_head, p.n_head, nd, active);
             }
 #pragma unroll
             for (int d = 0; d <= S; d++) {
-                int first = -1, cnt = 0;
-                if (sb[d] < se[d]) {
-                    if (iv[d].x <= ts && iv[d].y > ts) { first = __ldg(&p.st_rec[sb[d]].node); cnt = 1; }
-                    for (int j = sb[d] + 1; j < se[d]; j++) {
-                        const longlong2 x = __ldg(reinterpret_cast<const longlong2 *>(p.st_rec + j));
-                        if (x.x <= ts && x.y > ts) { if (cnt == 0) first = __ldg(&p.st_rec[j].node); cnt++; }
-                    }
-                }
+                int first, cnt;
+                head_finish(h[d], p.st_rec, ts, first, cnt);
                 if (active) {
                     row[2 * s + 1 + d] = first;
                     miss |= (cnt == 0 ? 1u : 0u) << d;
@@ -434,7 +456,7 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
                 const unsigned same = __match_any_sync(0xffffffffu, nd) & __match_any_sync(0xffffffffu, ts);
                 const int leader = __ffs(same) - 1;
                 int first = -1, cnt = 0;
-                if (w.lane == leader && nd >= 0) state_probe(p.st_off, p.st_rec, nd, ts, first, cnt);
+                if (w.lane == leader && nd >= 0) state_probe(p.st_head, p.n_head, p.st_rec, nd, ts, first, cnt);
                 first = __shfl_sync(0xffffffffu, first, leader);
                 cnt = __shfl_sync(0xffffffffu, cnt, leader);
                 if (active) {
@@ -657,6 +679,177 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_FILL) fill_level(const __gr
 }
 
 // ------------------------------------------------------------------------------------------------
+// Unit steps.  A typed step over an edge type no node has two of on the near side (Pod -spec_nodeName->
+// Node, ownerReferences, claimRef ...: the engine knows from the typed-range tables) gives every
+// partial path at most ONE candidate.  Then a tile needs no scan of row lengths, no compaction, no
+// windows and no emission queue - one lane, one path, from its frontier entry to its finished row -
+// and, since nothing waits on a neighbour lane, every load of that lane can be in flight as early as
+// its address is known: the parent walk and the state probes of the nodes already on the path run
+// beside the range -> adjacency chain instead of after it (5 dependent round trips per row, not 8).
+// The kind tests are per launch, not per candidate: the far kind of the step is fixed (p.unit_fl).
+// Same tile slots, same counts, same scan as count_level / fill_level; split path, levels >= 2.
+
+struct UnitCtx {
+    unsigned long long Fq, fb_s, ob_s, slot0;
+    unsigned ntiles;
+};
+__device__ __forceinline__ UnitCtx unit_setup(const LevelParams &p, unsigned long long *s_fb) {
+    UnitCtx c;
+    const int tid = threadIdx.x, s = p.s, q = s - 1;
+    Ctl *ctl = p.ctl;
+    if (tid < kLv) {
+        unsigned long long fb = 0;
+        for (int j = 1; j < tid && j < s; j++) fb += ctl->F[j];
+        s_fb[tid] = fb;
+    }
+    __syncthreads();
+    unsigned long long fb_s = 0, ob_s = ctl->out_base;
+    for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
+    c.fb_s = fb_s; c.ob_s = ob_s;
+    c.Fq = ctl->F[q];
+    c.ntiles = (unsigned)((c.Fq + kTile - 1) / kTile);
+    const unsigned long long vpos = ctl->F[0] + (fb_s - ctl->F[q]);
+    c.slot0 = ((vpos / kTile + kGroup - 1) / kGroup + (unsigned long long)q) * kGroup;
+    return c;
+}
+
+// One lane's path: its nodes a[0..Q] and relationships rel[1..Q] (walked up the parent entries), the
+// candidate (v, r) and what becomes of it (bit0 continue, bit1 emit).
+template <bool ADJ2, int Q>
+struct UnitLane {
+    int a[Q + 1], rel[Q + 1];
+    int v, r, root, inter, fl;
+    bool has;
+    __device__ __forceinline__ void load(const LevelParams &p, const unsigned long long *fb, unsigned long long i, bool valid) {
+        int4 e = make_int4(0, 0, 0, 0);
+        if (valid) e = p.frontier[fb[Q] + i];
+        a[Q] = e.x; rel[Q] = e.z; inter = e.w >> 16;
+        int2 rg = make_int2(0, 0);
+        if (valid && e.x >= p.row_lo && e.x < p.row_hi) rg = __ldg(p.rng + (e.x - p.row_lo));
+        int par = e.y;
+#pragma unroll
+        for (int d = Q - 1; d >= 1; d--) {
+            int4 pe = make_int4(0, 0, 0, 0);
+            if (valid) pe = p.frontier[fb[d] + (unsigned)par];
+            a[d] = pe.x; rel[d] = pe.z; par = pe.y;
+        }
+        root = par;
+        a[0] = valid ? __ldg(p.seeds + par) : 0;
+        rel[0] = 0;
+        has = rg.y > rg.x;
+        v = 0; r = 0;
+        if (has) {
+            if (ADJ2) {
+                const int2 x = __ldg(p.adj2 + rg.x);
+                v = x.x; r = x.y & kRelMask;
+            } else {
+                v = __ldg(p.adj1 + rg.x);
+                r = rg.x;
+            }
+        }
+        bool dead = !has;
+#pragma unroll
+        for (int d = 0; d <= Q; d++) dead |= (a[d] == v);
+        fl = dead ? 0 : ((p.unit_fl & 1) | (((p.unit_fl & 2) && (!p.need_inter || inter)) ? 2 : 0));
+    }
+};
+
+template <bool ADJ2, int Q>
+__global__ void __launch_bounds__(kThreads, 6) count_unit(const __grid_constant__ LevelParams p) {
+    __shared__ unsigned long long s_fb[kLv];
+    if (overflow_seen(p.ctl)) return;
+    const UnitCtx c = unit_setup(p, s_fb);
+    const int lane = threadIdx.x & 31;
+    unsigned long long scanned = 0;
+    const unsigned nwarps = gridDim.x * kWarps;
+    for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
+        const unsigned long long i = (unsigned long long)tile * kTile + lane;
+        UnitLane<ADJ2, Q> u;
+        u.load(p, s_fb, i, i < c.Fq);
+        const int cf = __popc(__ballot_sync(0xffffffffu, u.fl & 1)), ce = __popc(__ballot_sync(0xffffffffu, u.fl & 2));
+        scanned += (unsigned long long)__popc(__ballot_sync(0xffffffffu, u.has));
+        if (lane == 0) {
+            const unsigned long long slot = c.slot0 + tile;
+            p.tcount[slot] = make_uint2((unsigned)cf, (unsigned)ce);
+            if (cf) atomicAdd(&p.gsum[slot / kGroup].x, (unsigned long long)cf);
+            if (ce) atomicAdd(&p.gsum[slot / kGroup].y, (unsigned long long)ce);
+        }
+    }
+    if (lane == 0 && scanned) atomicAdd(&p.ctl->E[p.s], scanned);
+}
+
+template <bool ADJ2, int Q>
+__global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __grid_constant__ LevelParams p) {
+    extern __shared__ int s_dyn[];                    // per warp: 32 finished rows
+    __shared__ unsigned long long s_fb[kLv];
+    if (overflow_seen(p.ctl)) return;
+    UnitCtx c = unit_setup(p, s_fb);
+    c.fb_s += p.ctl->subF;
+    c.ob_s += p.ctl->subN * (unsigned long long)p.row_len;
+    constexpr int S = Q + 1;                          // hops of the rows
+    const int lane = threadIdx.x & 31, rl = p.row_len;
+    const unsigned lt = (1u << lane) - 1u;
+    int *stage = s_dyn + (threadIdx.x >> 5) * (kTile * rl);
+    const bool want_rows = !p.count_only && (p.unit_fl & 2);
+    const unsigned nwarps = gridDim.x * kWarps;
+    for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
+        const unsigned long long slot = c.slot0 + tile, g = slot / kGroup;
+        const unsigned in_g = (unsigned)(slot % kGroup);
+        uint2 mine = make_uint2(0, 0);
+        if ((unsigned)lane < in_g) mine = p.tcount[g * kGroup + lane];
+        const ulonglong2 gp = p.gscan[g];
+        const unsigned long long i = (unsigned long long)tile * kTile + lane;
+        const bool valid = i < c.Fq;
+        UnitLane<ADJ2, Q> u;
+        u.load(p, s_fb, i, valid);
+        // state probes: the header sector of every node of the row, all in flight together
+        const bool probe = want_rows && p.with_states && u.has && (!p.need_inter || u.inter);
+        long long ts = 0;
+        HeadRegs h[S + 1];
+        if (p.with_states) {
+            if (probe) ts = __ldg(p.seed_ts + u.root);
+#pragma unroll
+            for (int d = 0; d <= S; d++) h[d] = ld_head(p.st_head, p.n_head, (d <= Q) ? u.a[d] : u.v, probe);
+        }
+        const unsigned long long run_f = gp.x + __reduce_add_sync(0xffffffffu, mine.x);
+        const unsigned long long run_e = gp.y + __reduce_add_sync(0xffffffffu, mine.y);
+        const unsigned bf = __ballot_sync(0xffffffffu, u.fl & 1), be = __ballot_sync(0xffffffffu, u.fl & 2);
+        if (u.fl & 1) {
+            const unsigned long long pos = c.fb_s + run_f + __popc(bf & lt);
+            if (pos < p.fcap) p.frontier[pos] = make_int4(u.v, (int)i, u.r, p.unit_aux | (u.inter << 16));
+        }
+        if (!be || p.count_only) continue;
+        const int n = __popc(be);
+        const unsigned long long w0 = c.ob_s + run_e * (unsigned long long)rl;
+        if (w0 + (unsigned long long)n * rl > p.ocap) continue;      // flagged with the counts: the run is void
+        if (u.fl & 2) {
+            int *row = stage + __popc(be & lt) * rl;
+#pragma unroll
+            for (int d = 0; d <= Q; d++) row[d] = u.a[d];
+            row[S] = u.v;
+#pragma unroll
+            for (int d = 1; d <= Q; d++) row[S + d] = u.rel[d];
+            row[2 * S] = u.r;
+            if (p.with_states) {
+                unsigned miss = 0;
+#pragma unroll
+                for (int d = 0; d <= S; d++) {
+                    int first, cnt;
+                    head_finish(h[d], p.st_rec, ts, first, cnt);
+                    row[2 * S + 1 + d] = first;
+                    miss |= (cnt == 0 ? 1u : 0u) << d;
+                }
+                row[3 * S + 2] = (int)miss;
+            }
+        }
+        __syncwarp();
+        int *dst = p.out + w0;
+        for (int k = lane; k < n * rl; k += 32) dst[k] = stage[k];
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // fused path: count, decoupled look-back, fill in one launch (small seed sets)
 
 // tile-state word: x = status:2 | epoch:30 | f:32 (continuing entries), y = e (emitted rows)
@@ -777,7 +970,8 @@ struct ChainParams {
     unsigned long long ocap;
     Ctl *ctl;
     ulonglong2 *tstate;
-    const int *st_off;
+    const StHead *st_head;
+    int n_head;
     const StRec *st_rec;
 };
 
@@ -817,7 +1011,7 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
                     unsigned miss = 0;
                     for (int k = 0; k <= L; k++) {
                         int first, cnt;
-                        state_probe(p.st_off, p.st_rec, node[k], ts, first, cnt);
+                        state_probe(p.st_head, p.n_head, p.st_rec, node[k], ts, first, cnt);
                         row[2 * L + 1 + k] = first;
                         miss |= (cnt == 0 ? 1u : 0u) << k;
                     }
