@@ -51,6 +51,10 @@ struct rca_engine {
     int n_head = 0;
     unsigned char *rel_et = nullptr;      // edge type per relationship (only when there are <= 256 edge types)
     std::vector<int> et_max_out, et_max_in;   // largest number of relationships of the type at one start / end node
+    // edge types no node has two of (on that side): per node of the near kind, its (neighbour, relationship) or
+    // (-1, -1), instead of a range into an adjacency array; base -1 = the type is not like that
+    int2 *unit_next = nullptr;
+    std::vector<long long> unit_out_base, unit_in_base;
     // scratch
     int4 *frontier = nullptr;
     unsigned long long fcap = 0;
@@ -188,9 +192,12 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         for (int v = 0; v < s->n_nodes; v++) if (s->st_off[v + 1] > s->st_off[v]) last = v;
         g->n_head = last + 1;
         std::vector<StHead> head((size_t)g->n_head);
+        auto t44 = [](long long t) { return (unsigned long long)std::min<long long>(std::max<long long>(t, 0), (long long)kT44); };
         for (int v = 0; v < g->n_head; v++) {
             const int b = s->st_off[v], c = s->st_off[v + 1] - b;
-            head[v] = c ? StHead{s->st_tmin[b], s->st_tmax[b], s->st_node[b], c, b, 0} : StHead{1, 0, -1, 0, 0, 0};
+            if (!c) { head[v] = StHead{1ull, 0ull}; continue; }
+            const unsigned long long node = (unsigned)s->st_node[b], more = (unsigned long long)std::min(c - 1, 255);
+            head[v] = StHead{t44(s->st_tmin[b]) | (node & 0xfffffull) << 44, t44(s->st_tmax[b]) | (node >> 20) << 44 | more << 56};
         }
         OCK(upload(&g->st_head, head.data(), head.size()));
     }
@@ -207,6 +214,29 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         for (long long j = s->typed_in_base[t]; j < s->typed_in_base[t + 1]; j++)
             g->et_max_in[t] = std::max(g->et_max_in[t], s->typed_in[2 * j + 1] - s->typed_in[2 * j]);
     }
+    {
+        std::vector<int2> nx;
+        g->unit_out_base.assign(s->n_etypes, -1);
+        g->unit_in_base.assign(s->n_etypes, -1);
+        for (int t = 0; t < s->n_etypes; t++) {
+            if (g->et_max_out[t] <= 1) {
+                g->unit_out_base[t] = (long long)nx.size();
+                for (long long j = s->typed_out_base[t]; j < s->typed_out_base[t + 1]; j++) {
+                    const int b = s->typed_out[2 * j];
+                    nx.push_back(s->typed_out[2 * j + 1] > b ? make_int2(s->out_dst[b], b) : make_int2(-1, -1));
+                }
+            }
+            if (g->et_max_in[t] <= 1) {
+                g->unit_in_base[t] = (long long)nx.size();
+                for (long long j = s->typed_in_base[t]; j < s->typed_in_base[t + 1]; j++) {
+                    const int b = s->typed_in[2 * j];
+                    nx.push_back(s->typed_in[2 * j + 1] > b ? make_int2(s->in_adj[2 * (size_t)b], s->in_adj[2 * (size_t)b + 1] & kRelMask)
+                                                            : make_int2(-1, -1));
+                }
+            }
+        }
+        OCK(upload(&g->unit_next, nx.data(), nx.size()));
+    }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
     OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
     OCK(cudaMalloc((void **)&g->ptab, kPtBytes));
@@ -221,7 +251,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_rec, e->st_head, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
+                   e->st_off, e->st_rec, e->st_head, e->unit_next, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off, e->m_ptab, e->m_ctl};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
@@ -410,12 +440,11 @@ static KernelSet pick_kernels(int mode, int q) {
 }
 
 // unit steps (rca_kernels.cuh): typed step, at most one candidate per path, path so far of 2..4 nodes
-template <bool ADJ2>
 static KernelSet pick_unit_kernels(int q) {
     switch (q) {
-        case 1: return KernelSet{count_unit<ADJ2, 1>, fill_unit<ADJ2, 1>, nullptr};
-        case 2: return KernelSet{count_unit<ADJ2, 2>, fill_unit<ADJ2, 2>, nullptr};
-        default: return KernelSet{count_unit<ADJ2, 3>, fill_unit<ADJ2, 3>, nullptr};
+        case 1: return KernelSet{count_unit<1>, fill_unit<1>, nullptr};
+        case 2: return KernelSet{count_unit<2>, fill_unit<2>, nullptr};
+        default: return KernelSet{count_unit<3>, fill_unit<3>, nullptr};
     }
 }
 
@@ -555,7 +584,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
         c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
         c.out = e->out; c.ocap = e->ocap; c.ctl = b.ctl; c.tstate = e->tstate;
-        c.st_head = e->st_head; c.n_head = e->n_head; c.st_rec = e->st_rec;
+        c.st_head = e->st_head; c.n_head = e->n_head; c.st_off = e->st_off; c.st_rec = e->st_rec;
         const long long blocks = std::max<long long>(1, (b.n_seeds + kThreads - 1) / kThreads);
         chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
         ++*launches;
@@ -599,7 +628,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
         p.ptab = b.ptab;
         p.rel_et = e->rel_et; p.arr_prune = pp.arr_prune;
-        p.st_head = e->st_head; p.n_head = e->n_head; p.st_rec = e->st_rec;
+        p.st_head = e->st_head; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         const long long first = std::max<long long>(1, (b.n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
         if (pp.fused) {
@@ -628,8 +657,9 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
                 size_t dyn_c = dyn, dyn_f = dyn;
                 if (pp.level_typed[s] && e->unit_steps && pp.mode == kModeSimple && s >= 2 && s <= 4 &&
-                    (sdir == RCA_DIR_OUT ? e->et_max_out : e->et_max_in)[pp.subs[s][j].t] <= 1) {
-                    ks = sdir == RCA_DIR_OUT ? pick_unit_kernels<false>(s - 1) : pick_unit_kernels<true>(s - 1);
+                    (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t] >= 0) {
+                    ks = pick_unit_kernels(s - 1);
+                    p.unit_next = e->unit_next + (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t];
                     p.unit_fl = pp.subs[s][j].fl;
                     p.unit_aux = pp.subs[s][j].aux;
                     dyn_c = 0;
@@ -1291,7 +1321,7 @@ extern "C" int rca_expand_static(rca_engine_t *e, const rca_plan_t *pl, const in
         p.tstate = reinterpret_cast<ulonglong2 *>(ss + kSsTstate);
         p.ptab = ss + kSsPtab;
         p.rel_et = e->rel_et; p.arr_prune = arr_prune;
-        p.st_head = e->st_head; p.n_head = e->n_head; p.st_rec = e->st_rec;
+        p.st_head = e->st_head; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
         const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         int grid = max_grid(e, ks.fused, dyn);

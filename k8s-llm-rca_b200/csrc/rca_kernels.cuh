@@ -54,6 +54,9 @@ constexpr int kQueue = 64;            // emission queue entries per warp
 #ifndef RCA_MINB_FILL
 #define RCA_MINB_FILL 5       // fill_level keeps several state-probe loads in flight: 48 registers, no spills
 #endif
+#ifndef RCA_MINB_UNITC
+#define RCA_MINB_UNITC 6      // count_unit
+#endif
 #ifndef RCA_MINB_UNIT
 #define RCA_MINB_UNIT 4       // fill_unit: 64 registers, every probe load of a row in flight
 #endif
@@ -84,13 +87,18 @@ struct StRec {                        // one HasState interval: exactly one 32 B
     int pad[3];
 };
 
-// Per entity node: its first interval inline, the number of intervals, and where the others are
-// (st_rec[off + 1 .. off + cnt)).  One 32 B sector answers the HasState predicate for every node with a
-// single interval, without the offsets -> records round trip.
+// Per entity node, 16 bytes: its first interval, the STATE node of that interval and how many more
+// intervals the node has, packed so that ONE 16-byte load answers the HasState predicate for every
+// node with a single interval.  (A row's probes are lane-divergent loads, and the L1 data pipe - the
+// unit that limits fill_unit - spends one pass per lane and load whatever the load's width.)
+//   a = tmin (44 bits) | node bits 0..19 << 44
+//   b = tmax (44 bits) | node bits 20..31 << 44 | min(255, number of further intervals) << 56
+// Times are milliseconds clamped to [0, 2^44-1] (1970 .. 2527); a timestamp outside [0, 2^44-2] is
+// answered from the full records instead (state_probe_full), so every answer is exact.
 struct StHead {
-    long long tmin, tmax;             // (1, 0) when the node has no interval: matches no timestamp
-    int node, cnt, off, pad;
+    unsigned long long a, b;          // no interval: tmin 1, tmax 0 - matches no timestamp
 };
+constexpr unsigned long long kT44 = (1ull << 44) - 1;
 
 struct Ctl {                          // device control block, one per engine
     unsigned long long F[kLv];        // frontier size per level (level s occupies arena entries sum F[1..s-1] ..)
@@ -141,9 +149,11 @@ struct LevelParams {
     // unit steps (count_unit / fill_unit): the far kind of the typed step is fixed, so its tests are per launch
     int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row
     int unit_aux;                     // kind | intermediate-kind flag << 16 of the far kind
+    const int2 *unit_next;            // per node of the near kind: its one (neighbour, relationship), or (-1, -1)
     // HasState intervals
     const StHead *st_head;            // [n_head]: nodes at or above n_head have no intervals
     int n_head;
+    const int *st_off;                // [V+1]: a node's records are st_rec[st_off[v] .. st_off[v+1])
     const StRec *st_rec;
 };
 
@@ -230,39 +240,46 @@ __device__ __forceinline__ int kind_lut(const Tables &T, int v) {
 }
 
 // HasState predicate for one (node, timestamp): lowest matching STATE node id (or -1) and count.
-// ld_head issues the two 16 B loads of the node's sector; head_finish consumes them (and walks the
-// node's other intervals, if any) - callers put other loads between the two.
-struct HeadRegs {
-    longlong2 iv;
-    int4 m;                           // node, cnt, off
-};
-__device__ __forceinline__ HeadRegs ld_head(const StHead *head, int n_head, int v, bool on) {
-    HeadRegs h;
-    h.iv = make_longlong2(1, 0);
-    h.m = make_int4(-1, 0, 0, 0);
-    if (on && (unsigned)v < (unsigned)n_head) {
-        const longlong2 *q = reinterpret_cast<const longlong2 *>(head + v);
-        h.iv = __ldg(q);
-        h.m = __ldg(reinterpret_cast<const int4 *>(q + 1));
-    }
-    return h;
-}
-__device__ __forceinline__ void head_finish(const HeadRegs &h, const StRec *rec, long long ts, int &first, int &cnt) {
-    first = -1;
-    cnt = 0;
-    if (h.iv.x <= ts && h.iv.y > ts) { first = h.m.x; cnt = 1; }
-    for (int j = 1; j < h.m.y; j++) {
-        const longlong2 x = __ldg(reinterpret_cast<const longlong2 *>(rec + h.m.z + j));
+// From the full records (every node, every timestamp):
+__device__ __forceinline__ void state_probe_full(const int *st_off, const StRec *rec, int v, long long ts, int from, int &first,
+                                                 int &cnt) {
+    const int b = __ldg(st_off + v) + from, e = __ldg(st_off + v + 1);
+    for (int j = b; j < e; j++) {
+        const longlong2 x = __ldg(reinterpret_cast<const longlong2 *>(rec + j));
         if (x.x <= ts && x.y > ts) {
-            if (cnt == 0) first = __ldg(&rec[h.m.z + j].node);
+            if (cnt == 0) first = __ldg(&rec[j].node);
             cnt++;
         }
     }
 }
-__device__ __forceinline__ void state_probe(const StHead *head, int n_head, const StRec *rec, int v, long long ts, int &first,
-                                            int &cnt) {
-    const HeadRegs h = ld_head(head, n_head, v, true);
-    head_finish(h, rec, ts, first, cnt);
+// Through the packed header: ld_head issues the node's one 16 B load, head_finish consumes it (and
+// walks the node's other intervals, if it has any) - callers put other loads between the two.
+struct States {
+    const StHead *head;
+    int n_head;
+    const int *off;
+    const StRec *rec;
+};
+__device__ __forceinline__ ulonglong2 ld_head(const States &st, int v, bool on) {
+    ulonglong2 h = make_ulonglong2(1ull, 0ull);
+    if (on && (unsigned)v < (unsigned)st.n_head) h = __ldg(reinterpret_cast<const ulonglong2 *>(st.head + v));
+    return h;
+}
+__device__ __forceinline__ void head_finish(const States &st, const ulonglong2 h, int v, long long ts, int &first, int &cnt) {
+    first = -1;
+    cnt = 0;
+    if ((unsigned long long)ts >= kT44) {             // outside the packed range: exact answer from the records
+        if ((unsigned)v < (unsigned)st.n_head) state_probe_full(st.off, st.rec, v, ts, 0, first, cnt);
+        return;
+    }
+    if ((long long)(h.x & kT44) <= ts && (long long)(h.y & kT44) > ts) {
+        first = (int)((h.x >> 44) | (((h.y >> 44) & 0xfffull) << 20));
+        cnt = 1;
+    }
+    if (h.y >> 56) state_probe_full(st.off, st.rec, v, ts, 1, first, cnt);
+}
+__device__ __forceinline__ void state_probe(const States &st, int v, long long ts, int &first, int &cnt) {
+    head_finish(st, ld_head(st, v, true), v, ts, first, cnt);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -434,16 +451,14 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
         if constexpr (S >= 0) {
             // the kernel is latency-bound here: issue every column's offset loads, then every column's
             // record loads, back to back - two memory round trips per row instead of 2(S+1)
-            HeadRegs h[S + 1];
+            const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+            ulonglong2 h[S + 1];
 #pragma unroll
-            for (int d = 0; d <= S; d++) {
-                const int nd = (d <= q) ? w.anc_n[d * kTile + o] : v;
-                h[d] = ld_head(p.st_head, p.n_head, nd, active);
-            }
+            for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= q) ? w.anc_n[d * kTile + o] : v, active);
 #pragma unroll
             for (int d = 0; d <= S; d++) {
                 int first, cnt;
-                head_finish(h[d], p.st_rec, ts, first, cnt);
+                head_finish(st, h[d], (d <= q) ? w.anc_n[d * kTile + o] : v, ts, first, cnt);
                 if (active) {
                     row[2 * s + 1 + d] = first;
                     miss |= (cnt == 0 ? 1u : 0u) << d;
@@ -456,7 +471,7 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
                 const unsigned same = __match_any_sync(0xffffffffu, nd) & __match_any_sync(0xffffffffu, ts);
                 const int leader = __ffs(same) - 1;
                 int first = -1, cnt = 0;
-                if (w.lane == leader && nd >= 0) state_probe(p.st_head, p.n_head, p.st_rec, nd, ts, first, cnt);
+                if (w.lane == leader && nd >= 0) state_probe(States{p.st_head, p.n_head, p.st_off, p.st_rec}, nd, ts, first, cnt);
                 first = __shfl_sync(0xffffffffu, first, leader);
                 cnt = __shfl_sync(0xffffffffu, cnt, leader);
                 if (active) {
@@ -618,27 +633,34 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
     const unsigned long long vpos = (q == 0) ? 0ull : ctl->F[0] + (fb_s - ctl->F[q]);
     const unsigned long long g0 = (vpos / kTile + kGroup - 1) / kGroup + (unsigned long long)q;
     const unsigned long long ng = (ntiles + kGroup - 1) / kGroup;
-    if (tid == 0) { s_run[0] = 0; s_run[1] = 0; }
-    __syncthreads();
-    for (unsigned long long base = 0; base < ng; base += 1024) {
-        const unsigned long long g = base + tid;
-        ulonglong2 v = make_ulonglong2(0, 0);
-        if (g < ng) v = p.gsum[g0 + g];
-        unsigned long long a = v.x, b = v.y;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned long long na = __shfl_up_sync(0xffffffffu, a, o), nb = __shfl_up_sync(0xffffffffu, b, o);
-            if (lane >= o) { a += na; b += nb; }
-        }
-        if (lane == 31) { s_w[0][wid] = a; s_w[1][wid] = b; }
-        __syncthreads();
-        unsigned long long wa = s_run[0], wb = s_run[1];
-        for (int k = 0; k < wid; k++) { wa += s_w[0][k]; wb += s_w[1][k]; }
-        if (g < ng) p.gscan[g0 + g] = make_ulonglong2(wa + a - v.x, wb + b - v.y);
-        __syncthreads();
-        if (tid == 1023) { s_run[0] = wa + a; s_run[1] = wb + b; }
-        __syncthreads();
+    // every thread owns a contiguous run of groups: its loads are all in flight at once, then one
+    // block-wide scan of the 1024 partial sums, then the thread's own prefixes
+    const unsigned long long chunk = (ng + 1023) / 1024;
+    const unsigned long long lo = min((unsigned long long)tid * chunk, ng), hi = min(lo + chunk, ng);
+    unsigned long long a = 0, b = 0;
+#pragma unroll 4
+    for (unsigned long long g = lo; g < hi; g++) {
+        const ulonglong2 v = p.gsum[g0 + g];
+        a += v.x; b += v.y;
     }
+    const unsigned long long ta = a, tb = b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long na = __shfl_up_sync(0xffffffffu, a, o), nb = __shfl_up_sync(0xffffffffu, b, o);
+        if (lane >= o) { a += na; b += nb; }
+    }
+    if (lane == 31) { s_w[0][wid] = a; s_w[1][wid] = b; }
+    __syncthreads();
+    unsigned long long wa = 0, wb = 0;
+    for (int k = 0; k < wid; k++) { wa += s_w[0][k]; wb += s_w[1][k]; }
+    unsigned long long ea = wa + a - ta, eb = wb + b - tb;             // exclusive prefix of this thread's run
+    for (unsigned long long g = lo; g < hi; g++) {
+        const ulonglong2 v = p.gsum[g0 + g];
+        p.gscan[g0 + g] = make_ulonglong2(ea, eb);
+        ea += v.x; eb += v.y;
+    }
+    if (tid == 1023) { s_run[0] = ea; s_run[1] = eb; }
+    __syncthreads();
     if (tid == 0) {
         // sub-launch 0 starts the level; later ones append after what the earlier ones wrote
         const unsigned long long base_f = p.sub ? ctl->F[s] : 0ull, base_n = p.sub ? ctl->N[s] : 0ull;
@@ -685,7 +707,9 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_FILL) fill_level(const __gr
 // windows and no emission queue - one lane, one path, from its frontier entry to its finished row -
 // and, since nothing waits on a neighbour lane, every load of that lane can be in flight as early as
 // its address is known: the parent walk and the state probes of the nodes already on the path run
-// beside the range -> adjacency chain instead of after it (5 dependent round trips per row, not 8).
+// beside the step itself instead of after it, and the step is ONE load - for such edge types the engine
+// keeps, per node of the near kind, the neighbour and the relationship themselves (LevelParams::unit_next)
+// rather than a range into an adjacency array (4 dependent round trips per row, not 8).
 // The kind tests are per launch, not per candidate: the far kind of the step is fixed (p.unit_fl).
 // Same tile slots, same counts, same scan as count_level / fill_level; split path, levels >= 2.
 
@@ -715,17 +739,16 @@ __device__ __forceinline__ UnitCtx unit_setup(const LevelParams &p, unsigned lon
 
 // One lane's path: its nodes a[0..Q] and relationships rel[1..Q] (walked up the parent entries), the
 // candidate (v, r) and what becomes of it (bit0 continue, bit1 emit).
-template <bool ADJ2, int Q>
+template <int Q>
 struct UnitLane {
     int a[Q + 1], rel[Q + 1];
     int v, r, root, inter, fl;
     bool has;
-    __device__ __forceinline__ void load(const LevelParams &p, const unsigned long long *fb, unsigned long long i, bool valid) {
-        int4 e = make_int4(0, 0, 0, 0);
-        if (valid) e = p.frontier[fb[Q] + i];
+    // e: the lane's frontier entry (fetched one tile ahead by the callers)
+    __device__ __forceinline__ void load(const LevelParams &p, const unsigned long long *fb, const int4 e, bool valid) {
         a[Q] = e.x; rel[Q] = e.z; inter = e.w >> 16;
-        int2 rg = make_int2(0, 0);
-        if (valid && e.x >= p.row_lo && e.x < p.row_hi) rg = __ldg(p.rng + (e.x - p.row_lo));
+        int2 nx = make_int2(-1, -1);
+        if (valid && e.x >= p.row_lo && e.x < p.row_hi) nx = __ldg(p.unit_next + (e.x - p.row_lo));
         int par = e.y;
 #pragma unroll
         for (int d = Q - 1; d >= 1; d--) {
@@ -736,17 +759,8 @@ struct UnitLane {
         root = par;
         a[0] = valid ? __ldg(p.seeds + par) : 0;
         rel[0] = 0;
-        has = rg.y > rg.x;
-        v = 0; r = 0;
-        if (has) {
-            if (ADJ2) {
-                const int2 x = __ldg(p.adj2 + rg.x);
-                v = x.x; r = x.y & kRelMask;
-            } else {
-                v = __ldg(p.adj1 + rg.x);
-                r = rg.x;
-            }
-        }
+        has = nx.x >= 0;
+        v = nx.x; r = nx.y;
         bool dead = !has;
 #pragma unroll
         for (int d = 0; d <= Q; d++) dead |= (a[d] == v);
@@ -754,18 +768,24 @@ struct UnitLane {
     }
 };
 
-template <bool ADJ2, int Q>
-__global__ void __launch_bounds__(kThreads, 6) count_unit(const __grid_constant__ LevelParams p) {
+template <int Q>
+__global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __grid_constant__ LevelParams p) {
     __shared__ unsigned long long s_fb[kLv];
     if (overflow_seen(p.ctl)) return;
     const UnitCtx c = unit_setup(p, s_fb);
     const int lane = threadIdx.x & 31;
     unsigned long long scanned = 0;
     const unsigned nwarps = gridDim.x * kWarps;
-    for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
-        const unsigned long long i = (unsigned long long)tile * kTile + lane;
-        UnitLane<ADJ2, Q> u;
-        u.load(p, s_fb, i, i < c.Fq);
+    const int4 *fq = p.frontier + s_fb[Q];
+    const int4 none = make_int4(0, 0, 0, 0);
+    unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    int4 e_next = ((unsigned long long)tile * kTile + lane < c.Fq) ? fq[(unsigned long long)tile * kTile + lane] : none;
+    for (; tile < c.ntiles; tile += nwarps) {
+        const unsigned long long i = (unsigned long long)tile * kTile + lane, i2 = i + (unsigned long long)nwarps * kTile;
+        const int4 e = e_next;
+        e_next = i2 < c.Fq ? fq[i2] : none;           // the next tile's entries travel while this tile is worked on
+        UnitLane<Q> u;
+        u.load(p, s_fb, e, i < c.Fq);
         const int cf = __popc(__ballot_sync(0xffffffffu, u.fl & 1)), ce = __popc(__ballot_sync(0xffffffffu, u.fl & 2));
         scanned += (unsigned long long)__popc(__ballot_sync(0xffffffffu, u.has));
         if (lane == 0) {
@@ -778,7 +798,7 @@ __global__ void __launch_bounds__(kThreads, 6) count_unit(const __grid_constant_
     if (lane == 0 && scanned) atomicAdd(&p.ctl->E[p.s], scanned);
 }
 
-template <bool ADJ2, int Q>
+template <int Q>
 __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __grid_constant__ LevelParams p) {
     extern __shared__ int s_dyn[];                    // per warp: 32 finished rows
     __shared__ unsigned long long s_fb[kLv];
@@ -792,24 +812,31 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
     int *stage = s_dyn + (threadIdx.x >> 5) * (kTile * rl);
     const bool want_rows = !p.count_only && (p.unit_fl & 2);
     const unsigned nwarps = gridDim.x * kWarps;
-    for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
+    const int4 *fq = p.frontier + s_fb[Q];
+    const int4 none = make_int4(0, 0, 0, 0);
+    unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    int4 e_next = ((unsigned long long)tile * kTile + lane < c.Fq) ? fq[(unsigned long long)tile * kTile + lane] : none;
+    for (; tile < c.ntiles; tile += nwarps) {
         const unsigned long long slot = c.slot0 + tile, g = slot / kGroup;
         const unsigned in_g = (unsigned)(slot % kGroup);
         uint2 mine = make_uint2(0, 0);
         if ((unsigned)lane < in_g) mine = p.tcount[g * kGroup + lane];
         const ulonglong2 gp = p.gscan[g];
-        const unsigned long long i = (unsigned long long)tile * kTile + lane;
+        const unsigned long long i = (unsigned long long)tile * kTile + lane, i2 = i + (unsigned long long)nwarps * kTile;
         const bool valid = i < c.Fq;
-        UnitLane<ADJ2, Q> u;
-        u.load(p, s_fb, i, valid);
+        const int4 e = e_next;
+        e_next = i2 < c.Fq ? fq[i2] : none;           // the next tile's entries travel while this tile is worked on
+        UnitLane<Q> u;
+        u.load(p, s_fb, e, valid);
         // state probes: the header sector of every node of the row, all in flight together
         const bool probe = want_rows && p.with_states && u.has && (!p.need_inter || u.inter);
         long long ts = 0;
-        HeadRegs h[S + 1];
+        const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+        ulonglong2 h[S + 1];
         if (p.with_states) {
             if (probe) ts = __ldg(p.seed_ts + u.root);
 #pragma unroll
-            for (int d = 0; d <= S; d++) h[d] = ld_head(p.st_head, p.n_head, (d <= Q) ? u.a[d] : u.v, probe);
+            for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= Q) ? u.a[d] : u.v, probe);
         }
         const unsigned long long run_f = gp.x + __reduce_add_sync(0xffffffffu, mine.x);
         const unsigned long long run_e = gp.y + __reduce_add_sync(0xffffffffu, mine.y);
@@ -835,7 +862,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
 #pragma unroll
                 for (int d = 0; d <= S; d++) {
                     int first, cnt;
-                    head_finish(h[d], p.st_rec, ts, first, cnt);
+                    head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, first, cnt);
                     row[2 * S + 1 + d] = first;
                     miss |= (cnt == 0 ? 1u : 0u) << d;
                 }
@@ -972,6 +999,7 @@ struct ChainParams {
     ulonglong2 *tstate;
     const StHead *st_head;
     int n_head;
+    const int *st_off;
     const StRec *st_rec;
 };
 
@@ -1011,7 +1039,7 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
                     unsigned miss = 0;
                     for (int k = 0; k <= L; k++) {
                         int first, cnt;
-                        state_probe(p.st_head, p.n_head, p.st_rec, node[k], ts, first, cnt);
+                        state_probe(States{p.st_head, p.n_head, p.st_off, p.st_rec}, node[k], ts, first, cnt);
                         row[2 * L + 1 + k] = first;
                         miss |= (cnt == 0 ? 1u : 0u) << k;
                     }

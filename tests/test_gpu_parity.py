@@ -342,3 +342,36 @@ def test_eight_hops(eng_small, snap_small, csr_oracle_lib):
     seeds = snap_small.nodes_of_kind(dep)[:4]
     res = check_varlen(eng_small, orc, seeds, "und", 8, dest_kind=nfs, excl_kinds=[ev, ns, node], entity_only=True)
     assert res.levels == 8
+
+
+def test_fused_state_filter_extreme_timestamps(eng_small, snap_small, csr_oracle_lib):
+    """Seed timestamps outside the range the packed state headers hold (before 1970, after 2527) and at
+    interval boundaries are answered exactly (the kernels then read the full records)."""
+    from k8s_llm_rca_b200 import engine
+    from k8s_llm_rca_b200.synth import DAY, T_BASE
+    orc = csr_oracle_lib.CsrOracle(snap_small)
+    pod, node, ev, ns = _kinds(snap_small, "Pod", "Node", "Event", "Namespace")
+    seeds = snap_small.nodes_of_kind(pod)
+    edge = np.concatenate([snap_small.st_tmin, snap_small.st_tmax, snap_small.st_tmin - 1, snap_small.st_tmax - 1])
+    special = np.array([-1, -5, 0, 1, (1 << 44) - 2, (1 << 44) - 1, 1 << 44, 1 << 50, (1 << 62), -(1 << 40),
+                        T_BASE, T_BASE + 3 * DAY], dtype=np.int64)
+    pool = np.concatenate([special, edge.astype(np.int64)])
+    ts = pool[np.random.default_rng(3).integers(0, len(pool), size=len(seeds))]
+    ts[:len(special)] = special[:len(seeds)][:len(special)]
+    plan = engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True, with_states=True)
+    res = eng_small.expand(plan, seeds, ts)
+    ts_of_seed = dict(zip(seeds.tolist(), ts.tolist()))
+    total = 0
+    for s in (1, 2, 3):
+        got = res.rows(s)
+        if len(got) == 0:
+            continue
+        total += len(got)
+        t = np.array([ts_of_seed[v] for v in got[:, 0].tolist()], dtype=np.int64)
+        miss = np.zeros(len(got), np.int64)
+        for d in range(s + 1):
+            f, c, _ = orc.states(got[:, d], t)
+            assert np.array_equal(got[:, 2 * s + 1 + d], f)
+            miss |= (c == 0).astype(np.int64) << d
+        assert np.array_equal(got[:, 3 * s + 2].astype(np.int64), miss)
+    assert total > 0
