@@ -89,6 +89,10 @@ struct rca_engine {
     Ctl *m_ctl = nullptr, *mh_ctl = nullptr;
     size_t many_cap = 0;
     std::vector<cudaEvent_t> ev_many;
+    // rca_expand_many: plans whose output is bounded on the host run beside the others on these streams
+    std::vector<cudaStream_t> side;
+    std::vector<cudaEvent_t> ev_side;
+    cudaEvent_t ev_fork = nullptr;
     // results of the last submission (one per plan) and the one the accessors address
     std::vector<PlanResult> results;
     int selected = 0;
@@ -259,6 +263,9 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->mh_ptab) cudaFreeHost(e->mh_ptab);
     if (e->mh_ctl) cudaFreeHost(e->mh_ctl);
     for (auto ev : e->ev_many) cudaEventDestroy(ev);
+    for (auto ev : e->ev_side) cudaEventDestroy(ev);
+    for (auto st : e->side) cudaStreamDestroy(st);
+    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     for (auto ev : e->ev_lv) if (ev) cudaEventDestroy(ev);
@@ -479,6 +486,7 @@ struct PreparedPlan {
     const rca_plan_t *pl = nullptr;
     bool varlen = false, fused = false, arr_prune = false;
     bool walk = false;                           // typed chain with little fan-out: one chain_walk launch
+    long long fan = 0;                           // ... and the most rows one seed can have
     int L = 0, mode = kModeChain;
     std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
     std::vector<char> level_typed, level_dead;
@@ -496,6 +504,7 @@ static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, u
         for (int i = 0; i < pl->n_steps && fan <= e->chain_walk_fanout; i++)
             fan *= std::max(1, pl->step_dir[i] == RCA_DIR_OUT ? e->et_max_out[pl->step_etype[i]] : e->et_max_in[pl->step_etype[i]]);
         pp.walk = fan <= e->chain_walk_fanout;
+        pp.fan = fan;
     }
     const int L = pp.L;
     std::memset(t, 0, kPtBytes);
@@ -561,6 +570,8 @@ static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, u
 struct RunBufs {
     const int *seeds; const long long *ts; long long n_seeds;
     Ctl *ctl; const unsigned char *ptab; unsigned epoch; unsigned long long groups;
+    unsigned long long tstate_at = 0;            // chain_walk / chain_line: first tile-state word of this plan
+    unsigned long long ocap = 0;                 // output words this plan may use (0: the whole arena)
 };
 
 // Enqueue every level of a prepared plan on the engine's stream.  ev_lv (nullable): one event per level.
@@ -576,6 +587,8 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
             const bool out = pl->step_dir[i] == RCA_DIR_OUT;
             const int rowk = out ? e->et_src[t] : e->et_dst[t];
             c.rng[i] = out ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t];
+            const long long ub = e->unit_steps ? (out ? e->unit_out_base : e->unit_in_base)[t] : -1;
+            c.unit[i] = ub >= 0 ? e->unit_next + ub : nullptr;
             c.row_lo[i] = e->kind_start[rowk];
             c.row_hi[i] = e->kind_start[rowk + 1];
             c.against[i] = out ? 0 : 1;
@@ -583,10 +596,13 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         c.adj1 = e->out_dst; c.adj2 = e->in_adj; c.n_nodes = e->n_nodes;
         c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
         c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
-        c.out = e->out; c.ocap = e->ocap; c.ctl = b.ctl; c.tstate = e->tstate;
+        c.out = e->out; c.ocap = b.ocap ? b.ocap : e->ocap; c.ctl = b.ctl; c.tstate = e->tstate + b.tstate_at;
         c.st_head = e->st_head; c.n_head = e->n_head; c.st_off = e->st_off; c.st_rec = e->st_rec;
         const long long blocks = std::max<long long>(1, (b.n_seeds + kThreads - 1) / kThreads);
-        chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
+        bool line = true;                             // all steps before the last are unit steps: no search needed
+        for (int i = 0; i + 1 < L; i++) line &= c.unit[i] != nullptr;
+        if (line) chain_line<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
+        else chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
         ++*launches;
         CK(cudaGetLastError());
         if (ev_lv) for (int s = 1; s <= L; s++) CK(cudaEventRecord(ev_lv[s], e->stream));
@@ -623,7 +639,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.lut_shift = e->lut_shift;
         p.seeds = b.seeds; p.seed_ts = b.ts;
         p.frontier = e->frontier; p.fcap = e->fcap;
-        p.out = e->out; p.ocap = e->ocap;
+        p.out = e->out; p.ocap = b.ocap ? b.ocap : e->ocap;
         p.ctl = b.ctl; p.tstate = e->tstate;
         p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
         p.ptab = b.ptab;
@@ -683,8 +699,9 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
 }
 
 // Tile-slot arrays for a run whose largest seed set is n_seeds (sizes follow the frontier capacity).
-static int ensure_tile_arrays(rca_engine *e, long long n_seeds, bool any_fused, bool any_split, unsigned long long *groups_out) {
-    const unsigned long long slots = ((unsigned long long)n_seeds + e->fcap) / kTile + (unsigned long long)kGroup * (kLv + 2);
+static int ensure_tile_arrays(rca_engine *e, long long n_seeds, bool any_fused, bool any_split, unsigned long long *groups_out,
+                              unsigned long long extra_slots = 0) {
+    const unsigned long long slots = ((unsigned long long)n_seeds + e->fcap) / kTile + (unsigned long long)kGroup * (kLv + 2) + extra_slots;
     const unsigned long long groups = slots / kGroup + kLv + 2;
     int rc;
     if (any_fused && slots > e->tcap) {               // a fresh array starts from zeros and epoch 1
@@ -905,18 +922,62 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
     if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * max_seeds, 1ull << 20)); if (rc) return rc; }
     if (!e->out) { rc = grow(e, &e->out, &e->ocap, std::max<unsigned long long>(64ull * total_seeds, 1ull << 22)); if (rc) return rc; }
 
+    // Plans that run as one chain_walk / chain_line launch have at most (seeds x fan-out) rows: their rows
+    // get fixed places at the top of the output arena, nothing of theirs depends on the plans before
+    // them, and they run on side streams beside the other plans (a 100 k-seed chain fills a third of the
+    // GPU and is latency-bound).  The other plans follow one another from the bottom of the arena as
+    // before, the base travelling on the device.
+    std::vector<char> aside((size_t)n_plans, 0);
+    std::vector<unsigned long long> top_base((size_t)n_plans, 0), tile_at((size_t)n_plans, 0);
+    unsigned long long top_words = 0, side_tiles = 0;
+    int n_aside = 0;
+    for (int k = 0; k < n_plans; k++) {
+        if (!pps[k].walk || n_plans < 2) continue;
+        aside[k] = 1;
+        n_aside++;
+        tile_at[k] = side_tiles;
+        side_tiles += (unsigned long long)n_seeds[k] / kThreads + 2;
+        if (!plans[k].count_only) top_words += (unsigned long long)n_seeds[k] * (unsigned long long)pps[k].fan * row_len_of(&plans[k], pps[k].L);
+    }
+    if (n_aside) {
+        if (e->ocap < top_words + (1ull << 22)) { rc = grow(e, &e->out, &e->ocap, top_words + std::max<unsigned long long>(64ull * total_seeds, 1ull << 22)); if (rc) return rc; }
+        const size_t want = std::min<size_t>((size_t)n_aside, 4);
+        while (e->side.size() < want) {
+            cudaStream_t st;
+            CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            e->side.push_back(st);
+            cudaEvent_t ev;
+            CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            e->ev_side.push_back(ev);
+        }
+        if (!e->ev_fork) CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+    }
+
     int retries = 0;
     std::vector<int> launches((size_t)n_plans, 0);
     while (true) {
         unsigned long long groups = 0;
-        rc = ensure_tile_arrays(e, max_seeds, any_fused, any_split, &groups);
+        rc = ensure_tile_arrays(e, max_seeds, any_fused, any_split, &groups, side_tiles);
         if (rc) return rc;
+        const unsigned long long side_tstate = e->tcap - side_tiles;       // the side plans' tile states sit at the end
+        {
+            unsigned long long at = e->ocap;                                // ... and their rows at the top, plan by plan
+            for (int k = 0; k < n_plans; k++) {
+                if (!aside[k] || plans[k].count_only) continue;
+                at -= (unsigned long long)n_seeds[k] * (unsigned long long)pps[k].fan * row_len_of(&plans[k], pps[k].L);
+                top_base[k] = at;
+            }
+        }
         for (int k = 0; k < n_plans; k++) {
             std::memset(&e->mh_ctl[k], 0, sizeof(Ctl));
             e->mh_ctl[k].F[0] = (unsigned long long)n_seeds[k];
+            if (aside[k]) e->mh_ctl[k].out_base = top_base[k];
             launches[k] = 0;
         }
         CK(cudaMemcpyAsync(e->m_ctl, e->mh_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+        cudaStream_t main_stream = e->stream;
+        if (n_aside) CK(cudaEventRecord(e->ev_fork, main_stream));          // uploads are done before any side plan starts
+        int prev = -1, n_side_used = 0;                                     // prev: the last plan that runs in the main stream
         for (int k = 0; k < n_plans; k++) {
             cudaEvent_t *evk = e->ev_many.data() + (size_t)k * ev_stride;
             RunBufs b;
@@ -924,16 +985,34 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
             b.ts = plans[k].with_states ? (seeds_on_device ? (const long long *)seed_ts[k] : e->ts_buf + at[k]) : nullptr;
             b.n_seeds = n_seeds[k]; b.ctl = e->m_ctl + k; b.ptab = e->m_ptab + (size_t)k * pt_stride; b.epoch = 0; b.groups = groups;
             if (pps[k].fused) { rc = next_epoch(e, &b.epoch); if (rc) return rc; }
-            else CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
+            if (aside[k]) {
+                cudaStream_t st = e->side[(size_t)n_side_used % e->side.size()];
+                if ((size_t)n_side_used < e->side.size()) CK(cudaStreamWaitEvent(st, e->ev_fork, 0));
+                n_side_used++;
+                b.tstate_at = side_tstate + tile_at[k];
+                e->stream = st;
+                CK(cudaEventRecord(evk[0], st));
+                rc = launch_levels(e, pps[k], b, evk, &launches[k]);
+                e->stream = main_stream;
+                if (rc) return rc;
+                continue;
+            }
+            b.ocap = e->ocap - top_words;
+            if (!pps[k].fused) CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
+            if (prev >= 0) {                          // this plan's rows start where the previous main-stream plan's end
+                RowLens rl;
+                for (int j = 0; j <= RCA_MAX_HOPS; j++) rl.v[j] = plans[prev].count_only ? 0 : row_len_of(&plans[prev], j);
+                chain_plans<<<1, 32, 0, e->stream>>>(e->m_ctl + prev, e->m_ctl + k, rl);
+                CK(cudaGetLastError());
+            }
             CK(cudaEventRecord(evk[0], e->stream));
             rc = launch_levels(e, pps[k], b, evk, &launches[k]);
             if (rc) return rc;
-            if (k + 1 < n_plans) {                    // the next plan's rows start where this plan's end
-                RowLens rl;
-                for (int j = 0; j <= RCA_MAX_HOPS; j++) rl.v[j] = plans[k].count_only ? 0 : row_len_of(&plans[k], j);
-                chain_plans<<<1, 32, 0, e->stream>>>(e->m_ctl + k, e->m_ctl + k + 1, rl);
-                CK(cudaGetLastError());
-            }
+            prev = k;
+        }
+        for (size_t j = 0; j < std::min<size_t>((size_t)n_side_used, e->side.size()); j++) {   // join
+            CK(cudaEventRecord(e->ev_side[j], e->side[j]));
+            CK(cudaStreamWaitEvent(main_stream, e->ev_side[j], 0));
         }
         CK(cudaMemcpyAsync(e->mh_ctl, e->m_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
@@ -941,11 +1020,14 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
         for (int k = 0; k < n_plans; k++) ov |= e->mh_ctl[k].overflow;
         if (!ov) break;
         if (++retries > 12) return fail(e, RCA_ERR_NOMEM, "rca_expand_many: scratch arenas still too small after %d retries", retries);
-        unsigned long long fneed = 0, oneed = 0;
+        unsigned long long fneed = 0, oneed = top_words;
         for (int k = 0; k < n_plans; k++) {
             unsigned long long f = 0;
             const int L = pps[k].L;
-            for (int s = 1; s <= L; s++) { f += e->mh_ctl[k].F[s]; oneed += e->mh_ctl[k].N[s] * (unsigned long long)row_len_of(&plans[k], s); }
+            for (int s = 1; s <= L; s++) {
+                f += e->mh_ctl[k].F[s];
+                if (!aside[k]) oneed += e->mh_ctl[k].N[s] * (unsigned long long)row_len_of(&plans[k], s);
+            }
             fneed = std::max(fneed, f);
         }
         if (ov & 1u) { rc = grow(e, &e->frontier, &e->fcap, std::max(e->fcap * 2, fneed + fneed / 4)); if (rc) return rc; }

@@ -983,6 +983,8 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
 struct ChainParams {
     int L;
     const int2 *rng[RCA_MAX_HOPS];    // typed (begin, end) table of step i, indexed by node - row_lo[i]
+    const int2 *unit[RCA_MAX_HOPS];   // non-null: no node has two relationships of step i's type on the near side;
+                                      // the table holds the (neighbour, relationship) itself, or (-1, -1)
     int row_lo[RCA_MAX_HOPS], row_hi[RCA_MAX_HOPS];
     int against[RCA_MAX_HOPS];        // step walks in_adj (neighbour, rel) instead of out_dst
     const int *adj1;
@@ -1007,21 +1009,33 @@ template <bool FILL>
 __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, int seed, long long ts, int *dst,
                                                         unsigned long long *scanned, unsigned long long *alive) {
     int node[RCA_MAX_HOPS + 1], rel[RCA_MAX_HOPS], cur[RCA_MAX_HOPS], end[RCA_MAX_HOPS];
+    int uv[RCA_MAX_HOPS], ur[RCA_MAX_HOPS];           // unit steps: the one candidate itself
     unsigned long long rows = 0;
     const int L = p.L;
     node[0] = seed;
-    if (seed < p.row_lo[0] || seed >= p.row_hi[0]) return 0;
-    {
-        const int2 r = __ldg(p.rng[0] + (seed - p.row_lo[0]));
-        cur[0] = r.x; end[0] = r.y;
-        if (!FILL) scanned[1] += (unsigned long long)(r.y - r.x);
-    }
+    // candidates of step d for a path whose tail is v
+    auto enter = [&](int d, int v) {
+        cur[d] = end[d] = 0;
+        if (v < p.row_lo[d] || v >= p.row_hi[d]) return;
+        if (p.unit[d]) {
+            const int2 nx = __ldg(p.unit[d] + (v - p.row_lo[d]));
+            uv[d] = nx.x; ur[d] = nx.y;
+            end[d] = nx.x >= 0 ? 1 : 0;
+        } else {
+            const int2 rg = __ldg(p.rng[d] + (v - p.row_lo[d]));
+            cur[d] = rg.x; end[d] = rg.y;
+        }
+        if (!FILL) scanned[d + 1] += (unsigned long long)(end[d] - cur[d]);
+    };
+    enter(0, seed);
     int d = 0;
     while (d >= 0) {
         if (cur[d] >= end[d]) { d--; continue; }
         const int slot = cur[d]++;
         int v, r;
-        if (p.against[d]) {
+        if (p.unit[d]) {
+            v = uv[d]; r = ur[d];
+        } else if (p.against[d]) {
             const int2 a = __ldg(p.adj2 + slot);
             v = a.x; r = a.y & kRelMask;
         } else {
@@ -1036,10 +1050,17 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
                 for (int k = 0; k <= L; k++) row[k] = node[k];
                 for (int k = 0; k < L; k++) row[L + 1 + k] = rel[k];
                 if (p.with_states) {
+                    // every node's header load goes out before the first one is looked at
+                    const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+                    ulonglong2 h[RCA_MAX_HOPS + 1];
+#pragma unroll
+                    for (int k = 0; k <= RCA_MAX_HOPS; k++) h[k] = ld_head(st, k <= L ? node[k] : 0, k <= L);
                     unsigned miss = 0;
-                    for (int k = 0; k <= L; k++) {
+#pragma unroll
+                    for (int k = 0; k <= RCA_MAX_HOPS; k++) {
+                        if (k > L) continue;
                         int first, cnt;
-                        state_probe(States{p.st_head, p.n_head, p.st_off, p.st_rec}, node[k], ts, first, cnt);
+                        head_finish(st, h[k], node[k], ts, first, cnt);
                         row[2 * L + 1 + k] = first;
                         miss |= (cnt == 0 ? 1u : 0u) << k;
                     }
@@ -1050,32 +1071,31 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
             continue;
         }
         d++;
-        if (v >= p.row_lo[d] && v < p.row_hi[d]) {
-            const int2 rg = __ldg(p.rng[d] + (v - p.row_lo[d]));
-            cur[d] = rg.x; end[d] = rg.y;
-            if (!FILL) scanned[d + 1] += (unsigned long long)(rg.y - rg.x);
-        } else {
-            cur[d] = end[d] = 0;
-        }
+        enter(d, v);
     }
     return rows;
 }
 
 __global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ ChainParams p) {
-    const int lane = threadIdx.x & 31;
+    // One ticket = 256 seeds (one per thread).  Row counts are scanned inside the CTA first and only the
+    // CTA totals go through the look-back: every tile of a call is in flight at once (100 k seeds fill a
+    // third of the GPU), so a tile waits for (tiles before it) / 32 look-back steps - 8 x fewer this way.
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_wsum[kWarps], s_pre;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     Ctl *ctl = p.ctl;
-    const unsigned ntiles = (unsigned)((p.n_seeds + 31) / 32);
+    const unsigned ntiles = (unsigned)((p.n_seeds + kThreads - 1) / kThreads);
     const int L = p.L;
     unsigned long long sc[RCA_MAX_HOPS + 1], al[RCA_MAX_HOPS + 1];
     for (int k = 0; k <= RCA_MAX_HOPS; k++) { sc[k] = 0; al[k] = 0; }
-    unsigned long long total_rows = 0;
     bool ov = false;
     while (true) {
-        unsigned tile = 0;
-        if (lane == 0) tile = atomicAdd(&ctl->ticket[L], 1u);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
+        __syncthreads();                              // the previous tile's readers of s_* are done
+        if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->ticket[L], 1u);
+        __syncthreads();
+        const unsigned tile = s_tile;
         if (tile >= ntiles) break;
-        const long long i = (long long)tile * 32 + lane;
+        const long long i = (long long)tile * kThreads + threadIdx.x;
         int seed = -1;
         long long ts = 0;
         if (i < p.n_seeds) {
@@ -1090,13 +1110,27 @@ __global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ C
             const unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += n;
         }
-        const unsigned long long tile_rows = __shfl_sync(0xffffffffu, incl, 31);
-        unsigned long long pre_f, pre_e;
-        tile_lookback(p.tstate, tile, p.epoch, 0ull, tile_rows, pre_f, pre_e);
-        if (tile == ntiles - 1 && lane == 0) ctl->N[L] = pre_e + tile_rows;
-        total_rows += 0;
-        const unsigned long long base = ctl->out_base + (pre_e + incl - mine) * (unsigned long long)p.row_len;
-        if (!p.count_only && ctl->out_base + (pre_e + tile_rows) * (unsigned long long)p.row_len > p.ocap) ov = true;
+        if (lane == 31) s_wsum[wid] = incl;
+        __syncthreads();
+        unsigned long long tile_rows = 0, before = 0;     // rows of the whole tile / of the warps before this one
+#pragma unroll
+        for (int k = 0; k < kWarps; k++) {
+            const unsigned long long x = s_wsum[k];
+            tile_rows += x;
+            if (k < wid) before += x;
+        }
+        if (wid == 0) {
+            unsigned long long pre_f, pre_e;
+            tile_lookback(p.tstate, tile, p.epoch, 0ull, tile_rows, pre_f, pre_e);
+            if (lane == 0) {
+                s_pre = pre_e;
+                if (tile == ntiles - 1) ctl->N[L] = pre_e + tile_rows;
+            }
+        }
+        __syncthreads();
+        const unsigned long long pre = s_pre;
+        const unsigned long long base = ctl->out_base + (pre + before + incl - mine) * (unsigned long long)p.row_len;
+        if (!p.count_only && ctl->out_base + (pre + tile_rows) * (unsigned long long)p.row_len > p.ocap) ov = true;
         else if (!p.count_only && mine) chain_dfs<true>(p, seed, ts, p.out + base, nullptr, nullptr);
     }
     // counters: partial paths alive after each step and entries scanned at each step
@@ -1107,6 +1141,152 @@ __global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ C
         if (lane == 0) {
             if (a && k < L) atomicAdd(&ctl->F[k], a);
             if (b) atomicAdd(&ctl->E[k], b);
+        }
+    }
+    if (ov && lane == 0) atomicOr(&ctl->overflow, 2u);
+}
+
+// chain_line: the same job as chain_walk for chains whose steps before the last are all unit steps (the
+// usual case: EVENT <-HasEvent- Event -involvedObject-> Pod -spec_nodeName-> Node).  A seed then has ONE
+// partial path, so there is nothing to search: the walk is a straight line of single loads, nodes and
+// relationships stay in registers across the look-back (no second walk, no local-memory stacks), the
+// state headers of the nodes are requested as the walk passes them, and only the last step may fan out
+// into several rows.  Same rows, same order, same counters as chain_walk.
+__global__ void __launch_bounds__(kThreads) chain_line(const __grid_constant__ ChainParams p) {
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_wsum[kWarps], s_pre;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    Ctl *ctl = p.ctl;
+    const unsigned ntiles = (unsigned)((p.n_seeds + kThreads - 1) / kThreads);
+    const int L = p.L;
+    const bool probe = p.with_states && !p.count_only;
+    const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+    unsigned sc[RCA_MAX_HOPS + 1], al[RCA_MAX_HOPS + 1];
+#pragma unroll
+    for (int k = 0; k <= RCA_MAX_HOPS; k++) { sc[k] = 0; al[k] = 0; }
+    bool ov = false;
+    while (true) {
+        __syncthreads();                              // the previous tile's readers of s_* are done
+        if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->ticket[L], 1u);
+        __syncthreads();
+        const unsigned tile = s_tile;
+        if (tile >= ntiles) break;
+        const long long i = (long long)tile * kThreads + threadIdx.x;
+        int seed = -1;
+        long long ts = 0;
+        if (i < p.n_seeds) {
+            seed = __ldg(p.seeds + i);
+            if (p.with_states) ts = __ldg(p.seed_ts + i);
+        }
+        int node[RCA_MAX_HOPS + 1], rel[RCA_MAX_HOPS];
+        ulonglong2 h[RCA_MAX_HOPS];
+        bool alive = seed >= 0 && seed < p.n_nodes;
+        node[0] = seed;
+        int lb = 0, le = 0;                           // candidates of the last step
+        int2 last = make_int2(-1, -1);                // ... or the one candidate itself, if that step is a unit step too
+#pragma unroll
+        for (int k = 0; k < RCA_MAX_HOPS; k++) {
+            h[k] = make_ulonglong2(1ull, 0ull);
+            if (k >= L) continue;
+            if (probe) h[k] = ld_head(st, node[k], alive);
+            const bool in = alive && node[k] >= p.row_lo[k] && node[k] < p.row_hi[k];
+            if (k < L - 1 || p.unit[k]) {
+                int2 nx = make_int2(-1, -1);
+                if (in) nx = __ldg(p.unit[k] + (node[k] - p.row_lo[k]));
+                const bool ok = nx.x >= 0;
+                sc[k + 1] += ok ? 1u : 0u;
+                if (k < L - 1) {
+                    alive = ok;
+                    node[k + 1] = nx.x; rel[k] = nx.y;
+                    al[k + 1] += ok ? 1u : 0u;
+                } else {
+                    last = nx;
+                    le = ok ? 1 : 0;
+                }
+            } else if (in) {
+                const int2 rg = __ldg(p.rng[k] + (node[k] - p.row_lo[k]));
+                lb = rg.x; le = rg.y;
+                sc[k + 1] += (unsigned)(rg.y - rg.x);
+            }
+        }
+        const unsigned long long mine = (unsigned long long)(le - lb);
+        unsigned long long incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (lane == 31) s_wsum[wid] = incl;
+        __syncthreads();
+        unsigned long long tile_rows = 0, before = 0;
+#pragma unroll
+        for (int k = 0; k < kWarps; k++) {
+            const unsigned long long x = s_wsum[k];
+            tile_rows += x;
+            if (k < wid) before += x;
+        }
+        if (wid == 0) {
+            unsigned long long pre_f, pre_e;
+            tile_lookback(p.tstate, tile, p.epoch, 0ull, tile_rows, pre_f, pre_e);
+            if (lane == 0) {
+                s_pre = pre_e;
+                if (tile == ntiles - 1) ctl->N[L] = pre_e + tile_rows;
+            }
+        }
+        __syncthreads();
+        const unsigned long long pre = s_pre;
+        if (p.count_only) continue;
+        if (ctl->out_base + (pre + tile_rows) * (unsigned long long)p.row_len > p.ocap) { ov = true; continue; }
+        if (!mine) continue;
+        // the states of the nodes every row of this seed shares
+        int first[RCA_MAX_HOPS];
+        unsigned miss0 = 0;
+        if (probe) {
+#pragma unroll
+            for (int k = 0; k < RCA_MAX_HOPS; k++) {
+                first[k] = -1;
+                if (k >= L) continue;
+                int cnt;
+                head_finish(st, h[k], node[k], ts, first[k], cnt);
+                miss0 |= (cnt == 0 ? 1u : 0u) << k;
+            }
+        }
+        int *row = p.out + ctl->out_base + (pre + before + incl - mine) * (unsigned long long)p.row_len;
+        for (int j = lb; j < le; j++, row += p.row_len) {
+            int v, r;
+            if (p.unit[L - 1]) {
+                v = last.x; r = last.y;
+            } else if (p.against[L - 1]) {
+                const int2 a = __ldg(p.adj2 + j);
+                v = a.x; r = a.y & kRelMask;
+            } else {
+                v = __ldg(p.adj1 + j);
+                r = j;
+            }
+#pragma unroll
+            for (int k = 0; k < RCA_MAX_HOPS; k++) {
+                if (k >= L) continue;
+                row[k] = node[k];
+                if (k < L - 1) row[L + 1 + k] = rel[k];
+                if (probe) row[2 * L + 1 + k] = first[k];
+            }
+            row[L] = v;
+            row[2 * L] = r;
+            if (probe) {
+                int fv, cnt;
+                state_probe(st, v, ts, fv, cnt);
+                row[3 * L + 1] = fv;
+                row[3 * L + 2] = (int)(miss0 | ((cnt == 0 ? 1u : 0u) << L));
+            }
+        }
+    }
+    for (int k = 1; k <= L; k++) {
+        unsigned a = al[k], b = sc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+        if (lane == 0) {
+            if (a && k < L) atomicAdd(&ctl->F[k], (unsigned long long)a);
+            if (b) atomicAdd(&ctl->E[k], (unsigned long long)b);
         }
     }
     if (ov && lane == 0) atomicOr(&ctl->overflow, 2u);

@@ -106,3 +106,32 @@ def test_unit_steps_survive_arena_growth(snap_small, csr_oracle_lib):
     ref, _ = orc.varlen(seeds, "und", 4, **kw)
     assert got == rows_to_set(ref)
     e.close()
+
+
+def test_chain_line_same_bytes_as_chain_walk(snap_10k, csr_oracle_lib):
+    """Typed chains whose steps before the last are unit steps run through chain_line; with the unit tables off
+    the same plans run through chain_walk.  Same rows, same order, same counters, states included."""
+    from k8s_llm_rca_b200 import engine, workloads
+    from k8s_llm_rca_b200.synth import DAY, T_BASE
+    w = workloads.Config3(snap=snap_10k)
+    orc = csr_oracle_lib.CsrOracle(snap_10k)
+    e = engine.Engine(snap_10k)
+    lo, hi = snap_10k.kind_range(snap_10k.label_index("EVENT"))
+    seeds = np.concatenate([np.arange(lo, hi, dtype=np.int32), [-3, snap_10k.n_nodes + 7, 0]]).astype(np.int32)
+    ts = (T_BASE + np.random.default_rng(4).integers(0, 30 * DAY, size=len(seeds))).astype(np.int64)
+    for name, (ets, dirs, plan) in w.chains.items():
+        got = []
+        for on in (True, False):
+            e.set_unit_steps(on)
+            r = e.expand(plan, seeds, ts)
+            got.append((r.rows(r.levels).copy(), r.frontier, r.scanned, r.emitted))
+        (a, fa, sa, na), (b, fb, sb, nb) = got
+        assert np.array_equal(a, b), name
+        assert fa == fb and sa == sb and na == nb, name
+        L = len(ets)
+        ok = seeds[(seeds >= 0) & (seeds < snap_10k.n_nodes)]
+        ref, _ = orc.chain(ok, ets, [1 if d == "in" else 0 for d in dirs])
+        assert rows_to_set({L: a[:, :2 * L + 1]}) == rows_to_set({L: ref}), name
+        cnt = e.expand(engine.chain_plan(ets, dirs, count_only=True), seeds)
+        assert cnt.emitted == na
+    e.close()
