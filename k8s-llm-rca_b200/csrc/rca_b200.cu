@@ -21,6 +21,20 @@ using namespace rca;
 
 static thread_local std::string g_open_error;
 
+// ------------------------------------------------------------------------------------------------
+// One plan, prepared on the host: its table (kind boundaries, one kind-action row per level,
+// node-block -> kind table, one arrival row per level) and, per level, how to launch it.
+struct Sub { int t, d, fl, aux; };    // fl / aux: what LevelParams::unit_fl / unit_aux say about the step's far kind
+struct PreparedPlan {
+    const rca_plan_t *pl = nullptr;
+    bool varlen = false, fused = false, arr_prune = false;
+    bool walk = false;                           // typed chain with little fan-out: one chain_walk launch
+    long long fan = 0;                           // ... and the most rows one seed can have
+    int L = 0, mode = kModeChain;
+    std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
+    std::vector<char> level_typed, level_dead;
+};
+
 struct PlanResult {
     bool valid = false;
     int levels = 0;
@@ -89,6 +103,16 @@ struct rca_engine {
     Ctl *m_ctl = nullptr, *mh_ctl = nullptr;
     size_t many_cap = 0;
     std::vector<cudaEvent_t> ev_many;
+    struct Occ { const void *kernel; size_t dyn; int grid; };
+    std::vector<Occ> occ_cache;           // launch grid per (kernel, dynamic shared memory)
+    struct CachedPlan {
+        rca_plan_t plan;
+        bool fused;
+        PreparedPlan pp;
+        std::vector<unsigned char> table;
+    };
+    std::vector<CachedPlan> plan_cache;   // prepared plans of earlier calls (prepare_plan): the schema analysis is done once
+    size_t plan_cache_next = 0;
     // rca_expand_many: plans whose output is bounded on the host run beside the others on these streams
     std::vector<cudaStream_t> side;
     std::vector<cudaEvent_t> ev_side;
@@ -456,6 +480,7 @@ static KernelSet pick_unit_kernels(int q) {
 }
 
 static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
+    for (const auto &c : e->occ_cache) if (c.kernel == (const void *)kernel && c.dyn == dyn_smem) return c.grid;
     // levels 6 to 8 need more than the 48 KB of shared memory (static tables included) a kernel gets without asking
     if (dyn_smem + 8192u > 48u * 1024u) {
         const cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem);
@@ -463,36 +488,25 @@ static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
     }
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    e->occ_cache.push_back({(const void *)kernel, dyn_smem, e->sm_count * per_sm});    // asked once per (kernel, shared memory)
     return e->sm_count * per_sm;
 }
 
 extern "C" int rca_set_fused_threshold(rca_engine_t *e, int64_t max_seeds) {
     if (!e || max_seeds < 0) return RCA_ERR_ARG;
     e->fused_max_seeds = e->chain_fused_max_seeds = max_seeds;
+    e->plan_cache.clear();
     return RCA_OK;
 }
 
 extern "C" int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_seed) {
     if (!e || max_rows_per_seed < 0) return RCA_ERR_ARG;
     e->chain_walk_fanout = max_rows_per_seed;
+    e->plan_cache.clear();
     return RCA_OK;
 }
 
-// ------------------------------------------------------------------------------------------------
-// One plan, prepared on the host: its table (kind boundaries, one kind-action row per level,
-// node-block -> kind table, one arrival row per level) and, per level, how to launch it.
-struct Sub { int t, d, fl, aux; };    // fl / aux: what LevelParams::unit_fl / unit_aux say about the step's far kind
-struct PreparedPlan {
-    const rca_plan_t *pl = nullptr;
-    bool varlen = false, fused = false, arr_prune = false;
-    bool walk = false;                           // typed chain with little fan-out: one chain_walk launch
-    long long fan = 0;                           // ... and the most rows one seed can have
-    int L = 0, mode = kModeChain;
-    std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
-    std::vector<char> level_typed, level_dead;
-};
-
-static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, unsigned char *t, PreparedPlan &pp) {
+static void prepare_plan_fresh(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, unsigned char *t, PreparedPlan &pp) {
     pp.pl = pl;
     pp.varlen = pl->kind == RCA_PLAN_VARLEN;
     pp.L = pp.varlen ? pl->max_hops : pl->n_steps;
@@ -566,6 +580,28 @@ static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, u
     }
 }
 
+// prepare_plan_fresh through a small cache keyed by the plan itself and the one thing the preparation takes
+// from the seed count (which family of kernels runs); the knobs that change a preparation clear the cache
+static void prepare_plan(rca_engine *e, const rca_plan_t *pl, int64_t n_seeds, unsigned char *t, PreparedPlan &pp) {
+    const bool varlen = pl->kind == RCA_PLAN_VARLEN;
+    const bool fused = n_seeds <= (varlen ? e->fused_max_seeds : e->chain_fused_max_seeds);
+    for (auto &c : e->plan_cache) {
+        if (c.fused != fused || std::memcmp(&c.plan, pl, sizeof *pl) != 0) continue;
+        pp = c.pp;
+        pp.pl = pl;
+        std::memcpy(t, c.table.data(), kPtBytes);
+        return;
+    }
+    prepare_plan_fresh(e, pl, n_seeds, t, pp);
+    rca_engine::CachedPlan c;
+    c.plan = *pl;
+    c.fused = fused;
+    c.pp = pp;
+    c.table.assign(t, t + kPtBytes);
+    if (e->plan_cache.size() < 32) e->plan_cache.push_back(std::move(c));
+    else e->plan_cache[e->plan_cache_next++ % 32] = std::move(c);
+}
+
 // Device buffers one plan runs in.
 struct RunBufs {
     const int *seeds; const long long *ts; long long n_seeds;
@@ -605,7 +641,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         else chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
         ++*launches;
         CK(cudaGetLastError());
-        if (ev_lv) for (int s = 1; s <= L; s++) CK(cudaEventRecord(ev_lv[s], e->stream));
+        if (ev_lv) CK(cudaEventRecord(ev_lv[L], e->stream));     // one launch: the earlier levels have no time of their own
         return RCA_OK;
     }
     for (int s = 1; s <= L; s++) {
@@ -843,9 +879,9 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     publish_result(e, e->results[0], pl, L, e->h_ctl);
     if (stats) {
         fill_stats(stats, pl, L, n_seeds, e->h_ctl, ms, launches, retries);
-        for (int s = 1; s <= L; s++) {
+        for (int s = pp.walk ? L : 1; s <= L; s++) {       // a one-launch chain has one time: the last level's
             float t = 0.f;
-            if (cudaEventElapsedTime(&t, e->ev_lv[s - 1], e->ev_lv[s]) == cudaSuccess) stats->level_ms[s] = t;
+            if (cudaEventElapsedTime(&t, e->ev_lv[pp.walk ? 0 : s - 1], e->ev_lv[s]) == cudaSuccess) stats->level_ms[s] = t;
         }
     }
     return RCA_OK;
@@ -1041,9 +1077,9 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
             float ms = 0.f;
             cudaEventElapsedTime(&ms, evk[0], evk[pps[k].L]);
             fill_stats(&stats[k], &plans[k], pps[k].L, n_seeds[k], &e->mh_ctl[k], ms, launches[k], retries);
-            for (int s = 1; s <= pps[k].L; s++) {
+            for (int s = pps[k].walk ? pps[k].L : 1; s <= pps[k].L; s++) {
                 float t = 0.f;
-                if (cudaEventElapsedTime(&t, evk[s - 1], evk[s]) == cudaSuccess) stats[k].level_ms[s] = t;
+                if (cudaEventElapsedTime(&t, evk[pps[k].walk ? 0 : s - 1], evk[s]) == cudaSuccess) stats[k].level_ms[s] = t;
             }
         }
     }

@@ -170,21 +170,26 @@ class ExpandResult:
     """Counters of one expansion plus access to its rows.  Rows live in the engine's output arena
     until the next expand() on the same engine; rows() copies them out."""
 
+    _ARRAYS = ("frontier", "scanned", "emitted", "row_len", "level_ms")
+
     def __init__(self, engine, st: StatsDesc, levels: int):
         self.engine = engine
         self.levels = levels
-        self.frontier = list(st.frontier)[:levels + 1]
-        self.scanned = list(st.scanned)[:levels + 1]
-        self.emitted = list(st.emitted)[:levels + 1]
-        self.row_len = list(st.row_len)[:levels + 1]
-        self.total = int(st.total)
-        self.kernel_ms = float(st.kernel_ms)
-        self.level_ms = list(st.level_ms)[:levels + 1]
-        self.launches = int(st.launches)
-        self.retries = int(st.retries)
+        self._st = st                  # the per-level arrays become lists when first asked for
+        self.total = st.total
+        self.kernel_ms = st.kernel_ms
+        self.launches = st.launches
+        self.retries = st.retries
         self._gen = engine._gen
         self.count_only = False
         self.index = 0                 # position in the submission (expand_many)
+
+    def __getattr__(self, name):
+        if name in ExpandResult._ARRAYS:
+            v = list(getattr(self._st, name))[:self.levels + 1]
+            setattr(self, name, v)
+            return v
+        raise AttributeError(name)
 
     def rows(self, level: int, out: np.ndarray | None = None) -> np.ndarray:
         """Copy the rows of one level to the host.  `out`: optional pre-allocated (ideally pinned)
