@@ -137,6 +137,9 @@ int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_seed);
  * load of the lane in flight as early as its address is known.  Same rows, same order, same counters.
  * on = 0 sends such levels through the general kernels (default on).  No counterpart in the reference. */
 int rca_set_unit_steps(rca_engine_t *e, int on);
+/* device memory the snapshot occupies on this engine's GPU (adjacency, typed tables, intervals and the
+ * tables rca_open derives from them), in bytes.  No counterpart in the reference. */
+int64_t rca_graph_bytes(const rca_engine_t *e);
 /* pre-size the scratch arenas: frontier entries (16 B each) and output words (4 B each) */
 int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words);
 

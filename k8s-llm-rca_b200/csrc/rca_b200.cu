@@ -68,6 +68,7 @@ struct rca_engine {
     // edge types no node has two of (on that side): per node of the near kind, its (neighbour, relationship) or
     // (-1, -1), instead of a range into an adjacency array; base -1 = the type is not like that
     int2 *unit_next = nullptr;
+    size_t graph_bytes = 0;               // device memory held by the snapshot (adjacency, typed tables, intervals, the tables above)
     std::vector<long long> unit_out_base, unit_in_base;
     // scratch
     int4 *frontier = nullptr;
@@ -264,6 +265,10 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
             }
         }
         OCK(upload(&g->unit_next, nx.data(), nx.size()));
+        g->graph_bytes = 3 * V1 * sizeof(int2) + (size_t)s->n_rels * (sizeof(int) + sizeof(int2)) + (size_t)s->n_und * sizeof(int2) +
+                         ((size_t)s->n_typed_out + (size_t)s->n_typed_in) * sizeof(int2) + V1 * sizeof(int) +
+                         (size_t)s->n_states * sizeof(StRec) + (g->rel_et ? (size_t)s->n_rels : 0) +
+                         (size_t)g->n_head * sizeof(StHead) + nx.size() * sizeof(int2);
     }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
     OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
@@ -315,6 +320,8 @@ static int grow(rca_engine *e, T **buf, unsigned long long *cap, unsigned long l
     *cap = want;
     return RCA_OK;
 }
+
+extern "C" int64_t rca_graph_bytes(const rca_engine_t *e) { return e ? (int64_t)e->graph_bytes : 0; }
 
 extern "C" int rca_set_unit_steps(rca_engine_t *e, int on) {
     if (!e) return RCA_ERR_ARG;

@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold",
-           "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_reserve",
+           "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_graph_bytes", "rca_reserve",
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_text_load",
            "rca_text_contains", "rca_version")
@@ -87,6 +87,8 @@ def load_library(path: str | None = None):
     lib.rca_set_fused_threshold.argtypes = [C.c_void_p, C.c_int64]
     lib.rca_set_chain_walk_fanout.argtypes = [C.c_void_p, C.c_int64]
     lib.rca_set_unit_steps.argtypes = [C.c_void_p, C.c_int]
+    lib.rca_graph_bytes.argtypes = [C.c_void_p]
+    lib.rca_graph_bytes.restype = C.c_int64
     lib.rca_expand.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
                                C.POINTER(StatsDesc)]
     lib.rca_expand_static.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
@@ -287,6 +289,10 @@ class Engine:
     def set_unit_steps(self, on: bool):
         """Typed steps with at most one candidate per path run through the one-lane-per-path kernels (default on)."""
         self._ck(self.lib.rca_set_unit_steps(self.h, 1 if on else 0))
+
+    def graph_bytes(self) -> int:
+        """Device memory the snapshot occupies on this engine's GPU."""
+        return int(self.lib.rca_graph_bytes(self.h))
 
     def reserve(self, frontier_entries: int, output_words: int):
         self._ck(self.lib.rca_reserve(self.h, int(frontier_entries), int(output_words)))
