@@ -63,7 +63,8 @@ struct rca_engine {
     StRec *st_rec = nullptr;              // HasState intervals, one 32 B record each
     StHead *st_head = nullptr;            // first interval + count + offset per node that can have one (rca_kernels.cuh)
     int n_head = 0;
-    unsigned char *rel_et = nullptr;      // edge type per relationship (only when there are <= 256 edge types)
+    unsigned char *rel_et = nullptr;      // edge type per relationship = per out_dst slot (only when there are <= 256 edge types)
+    unsigned char *in_et = nullptr, *und_et = nullptr;   // ... and per in_adj / und_adj slot
     std::vector<int> et_max_out, et_max_in;   // largest number of relationships of the type at one start / end node
     // edge types no node has two of (on that side): per node of the near kind, its (neighbour, relationship) or
     // (-1, -1), instead of a range into an adjacency array; base -1 = the type is not like that
@@ -234,6 +235,11 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         std::vector<unsigned char> et((size_t)s->n_rels);
         for (size_t j = 0; j < et.size(); j++) et[j] = (unsigned char)s->rel_et[j];
         OCK(upload(&g->rel_et, et.data(), et.size()));
+        std::vector<unsigned char> ie((size_t)s->n_rels), ue((size_t)s->n_und);
+        for (size_t j = 0; j < ie.size(); j++) ie[j] = et[(size_t)(s->in_adj[2 * j + 1] & kRelMask)];
+        for (size_t j = 0; j < ue.size(); j++) ue[j] = et[(size_t)(s->und_adj[2 * j + 1] & kRelMask)];
+        OCK(upload(&g->in_et, ie.data(), ie.size()));
+        OCK(upload(&g->und_et, ue.data(), ue.size()));
     }
     g->et_max_out.assign(s->n_etypes, 0);
     g->et_max_in.assign(s->n_etypes, 0);
@@ -267,7 +273,7 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         OCK(upload(&g->unit_next, nx.data(), nx.size()));
         g->graph_bytes = 3 * V1 * sizeof(int2) + (size_t)s->n_rels * (sizeof(int) + sizeof(int2)) + (size_t)s->n_und * sizeof(int2) +
                          ((size_t)s->n_typed_out + (size_t)s->n_typed_in) * sizeof(int2) + V1 * sizeof(int) +
-                         (size_t)s->n_states * sizeof(StRec) + (g->rel_et ? (size_t)s->n_rels : 0) +
+                         (size_t)s->n_states * sizeof(StRec) + (g->rel_et ? 2 * (size_t)s->n_rels + (size_t)s->n_und : 0) +
                          (size_t)g->n_head * sizeof(StHead) + nx.size() * sizeof(int2);
     }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
@@ -284,7 +290,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_rec, e->st_head, e->unit_next, e->rel_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
+                   e->st_off, e->st_rec, e->st_head, e->unit_next, e->rel_et, e->in_et, e->und_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off, e->m_ptab, e->m_ctl};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
@@ -686,7 +692,8 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.ctl = b.ctl; p.tstate = e->tstate;
         p.tcount = e->tcount; p.gsum = e->gsum; p.gscan = e->gscan;
         p.ptab = b.ptab;
-        p.rel_et = e->rel_et; p.arr_prune = pp.arr_prune;
+        p.rel_et = dir == RCA_DIR_OUT ? e->rel_et : dir == RCA_DIR_IN ? e->in_et : e->und_et;   // per slot of the array walked
+        p.arr_prune = pp.arr_prune;
         p.st_head = e->st_head; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         const long long first = std::max<long long>(1, (b.n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
@@ -711,6 +718,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                     p.row_lo = e->kind_start[rowk];
                     p.row_hi = e->kind_start[rowk + 1];
                     p.adj2 = e->in_adj;
+                    p.rel_et = sdir == RCA_DIR_OUT ? e->rel_et : e->in_et;
                 }
                 p.sub = j;
                 KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
@@ -1445,7 +1453,8 @@ extern "C" int rca_expand_static(rca_engine_t *e, const rca_plan_t *pl, const in
         p.ctl = reinterpret_cast<Ctl *>(ss + kSsCtl);
         p.tstate = reinterpret_cast<ulonglong2 *>(ss + kSsTstate);
         p.ptab = ss + kSsPtab;
-        p.rel_et = e->rel_et; p.arr_prune = arr_prune;
+        p.rel_et = dir == RCA_DIR_OUT ? e->rel_et : dir == RCA_DIR_IN ? e->in_et : e->und_et;
+        p.arr_prune = arr_prune;
         p.st_head = e->st_head; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
         const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(mode, s - 1) : pick_kernels<true>(mode, s - 1);
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);

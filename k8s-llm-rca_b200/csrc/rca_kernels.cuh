@@ -144,7 +144,8 @@ struct LevelParams {
     ulonglong2 *gsum;                 // split path: sums per group of 32 tile slots (zeroed per call)
     ulonglong2 *gscan;                // split path: exclusive prefix of gsum within the level
     const unsigned char *ptab;        // plan table (layout above)
-    const unsigned char *rel_et;      // edge type of every relationship (null: more than 256 edge types)
+    const unsigned char *rel_et;      // edge type per SLOT of the adjacency array this level walks (null: more than 256 edge
+                                      // types): the load needs the slot only, so it travels beside the adjacency load
     int arr_prune;                    // refine 'continue' by the arrival table (edge type, direction)
     // unit steps (count_unit / fill_unit): the far kind of the typed step is fixed, so its tests are per launch
     int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row
@@ -385,22 +386,38 @@ __device__ __forceinline__ int window_owner(const WarpSm &W, int it, int &jlo, i
     return o;
 }
 
+// A lane's candidate as it comes out of the adjacency arrays.  (Fetching it one window ahead of its use
+// was measured: no gain at level 1, slower at levels 2 and 3 - the loop is not waiting on this load.)
+struct Cand {
+    int v, rw, et;                    // neighbour, relationship word (bit 30: against the stored direction), edge type
+};
+template <bool ADJ2, int MODE>
+__device__ __forceinline__ Cand fetch_cand(const LevelParams &p, const Warp &w, int o, int c, int C) {
+    Cand x;
+    x.v = 0; x.rw = 0; x.et = 0;
+    if (c >= C) return x;
+    const int slot = w.W->crow[o] + c;
+    if (MODE != kModeChain && p.arr_prune) x.et = __ldg(p.rel_et + slot);
+    if (ADJ2) {
+        const int2 a = __ldg(p.adj2 + slot);
+        x.v = a.x; x.rw = a.y;
+    } else {
+        x.v = __ldg(p.adj1 + slot);
+        x.rw = slot;
+    }
+    return x;
+}
+
 // Classify the lane's candidate of window `it`: bit0 continue, bit1 emit.
 // QT: number of earlier path nodes minus one when known at compile time (0..3), else -1.
 template <bool ADJ2, int MODE, int QT>
 __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, const Warp &w, int o, int c, int C,
-                                        int &v, int &r, int &na) {
+                                        const Cand x, int &v, int &r, int &na) {
     v = 0; r = 0; na = 0;
     if (c >= C) return 0;
-    const int slot = w.W->crow[o] + c;
-    int against = 0;
-    if (ADJ2) {
-        const int2 a = __ldg(p.adj2 + slot);
-        v = a.x; r = a.y & kRelMask; against = (a.y >> 30) & 1;
-    } else {
-        v = __ldg(p.adj1 + slot);
-        r = slot;
-    }
+    v = x.v;
+    r = ADJ2 ? (x.rw & kRelMask) : x.rw;
+    const int against = ADJ2 ? ((x.rw >> 30) & 1) : 0, et = x.et;
     if (MODE == kModeChain) return p.chain_flag;
     bool dead = false;
     if (MODE == kModeSimple) {
@@ -419,7 +436,7 @@ __device__ __forceinline__ int classify(const LevelParams &p, const Tables &T, c
     const int inter = w.W->aux[o] >> 16;
     na = k | ((inter | (int)((a >> 2) & 1u)) << 16);
     int fl = (int)(a & kActCont) | (((a & kActEmit) && (!p.need_inter || inter)) ? 2 : 0);
-    if ((fl & 1) && p.arr_prune && !T.arr[2 * __ldg(p.rel_et + r) + against]) fl &= ~1;
+    if ((fl & 1) && p.arr_prune && !T.arr[2 * et + against]) fl &= ~1;
     return fl;
 }
 
@@ -499,8 +516,9 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
     int jlo = 0, qn = 0;
     for (int it = 0; it < n_it; ++it) {
         const int o = window_owner(W, it, jlo, lane);
+        const Cand x = fetch_cand<ADJ2, MODE>(p, w, o, (it << 5) + lane, C);
         int v, r, na;
-        const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + lane, C, v, r, na);
+        const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + lane, C, x, v, r, na);
         const unsigned bf = __ballot_sync(0xffffffffu, fl & 1), be = __ballot_sync(0xffffffffu, fl & 2);
         if (fl & 1) {
             const unsigned long long pos = fb_s + run_f + __popc(bf & w.lt);
@@ -540,8 +558,9 @@ __device__ __forceinline__ void tile_count(const LevelParams &p, const Tables &T
     cf = 0; ce = 0;
     for (int it = 0; it < n_it; ++it) {
         const int o = window_owner(*w.W, it, jlo, w.lane);
+        const Cand x = fetch_cand<ADJ2, MODE>(p, w, o, (it << 5) + w.lane, C);
         int v, r, na;
-        const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + w.lane, C, v, r, na);
+        const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + w.lane, C, x, v, r, na);
         cf += __popc(__ballot_sync(0xffffffffu, fl & 1));
         ce += __popc(__ballot_sync(0xffffffffu, fl & 2));
     }

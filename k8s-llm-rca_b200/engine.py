@@ -322,22 +322,25 @@ class Engine:
         n = len(plans)
         arr = (PlanDesc * n)(*plans)
         keep, sp, tp, ns, devs = [], (C.c_void_p * n)(), (C.c_void_p * n)(), (C.c_int64 * n)(), set()
+        seen = {}                       # plans of one submission usually share their seed / timestamp buffers
+
+        def ptr_of(x, dtype):
+            key = id(x)
+            hit = seen.get(key)
+            if hit is None:
+                if isinstance(x, (list, tuple)) or (isinstance(x, np.ndarray) and x.dtype != dtype):
+                    x = np.ascontiguousarray(x, dtype=dtype)
+                hit = seen[key] = _dev_ptr(x)
+                keep.append(hit[2])
+                devs.add(hit[1])
+            return hit
+
         for k in range(n):
-            s = seeds_list[k]
-            if isinstance(s, (list, tuple)) or (isinstance(s, np.ndarray) and s.dtype != np.int32):
-                s = np.ascontiguousarray(s, dtype=np.int32)
-            ptr, dev, ka = _dev_ptr(s)
-            keep.append(ka)
+            ptr, _, ka = ptr_of(seeds_list[k], np.int32)
             sp[k], ns[k] = ptr, int(ka.shape[0])
-            devs.add(dev)
             t = ts_list[k] if ts_list is not None else None
             if t is not None:
-                if not hasattr(t, "data_ptr"):
-                    t = np.ascontiguousarray(t, dtype=np.int64)
-                tptr, tdev, kt = _dev_ptr(t)
-                keep.append(kt)
-                tp[k] = tptr
-                devs.add(tdev)
+                tp[k] = ptr_of(t, np.int64)[0]
         if len(devs) > 1:
             raise ValueError("all seed / timestamp buffers must be host arrays or all device tensors")
         st = (StatsDesc * n)()
