@@ -191,6 +191,15 @@ int rca_text_load(rca_engine_t *e, const uint8_t *bytes, const int64_t *off, con
  * message; it is reported through out_first_node only. */
 int rca_text_contains(rca_engine_t *e, const uint8_t *pat_bytes, const int64_t *pat_off, int64_t n_pat,
                       int32_t *out_first_node, int32_t *out_pairs, int64_t pairs_cap, int64_t *n_pairs);
+/* replaces message_compatible, generate_query/generate_query.py:104-129 (the filter run_and_filter_query
+ * applies to every row of an instance query: keep the row iff the destination's name, or its kind, occurs in
+ * the event's message), for n_pairs rows at once.  Messages are those of the loaded arena (rca_text_load),
+ * addressed by their index in load order; needles (names, kind strings) come in one arena like patterns
+ * do.  out_flags[k] = 1 iff needle needle_a[k] or needle needle_b[k] occurs in message msg_index[k]
+ * (byte-wise, case-sensitive; the empty needle occurs everywhere; index -1 = no such needle). */
+int rca_text_match_pairs(rca_engine_t *e, const uint8_t *needle_bytes, const int64_t *needle_off, int64_t n_needles,
+                         const int32_t *msg_index, const int32_t *needle_a, const int32_t *needle_b, int64_t n_pairs,
+                         uint8_t *out_flags);
 
 /* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
  * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory

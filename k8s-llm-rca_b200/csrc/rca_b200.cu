@@ -1308,6 +1308,52 @@ extern "C" int rca_text_contains(rca_engine_t *e, const uint8_t *pat_bytes, cons
     return RCA_OK;
 }
 
+extern "C" int rca_text_match_pairs(rca_engine_t *e, const uint8_t *needle_bytes, const int64_t *needle_off, int64_t n_needles,
+                                    const int32_t *msg_index, const int32_t *needle_a, const int32_t *needle_b, int64_t n_pairs,
+                                    uint8_t *out_flags) {
+    if (!e) return RCA_ERR_ARG;
+    if (n_pairs < 0 || n_needles < 0 || (n_pairs > 0 && (!msg_index || !needle_a || !needle_b || !out_flags)) ||
+        (n_needles > 0 && (!needle_bytes || !needle_off)))
+        return fail(e, RCA_ERR_ARG, "rca_text_match_pairs: null argument");
+    if (n_pairs == 0) return RCA_OK;
+    if (n_pairs > 0x3fffffffLL) return fail(e, RCA_ERR_ARG, "rca_text_match_pairs: more than 2^30 pairs in one call");
+    for (int64_t k = 0; k < n_pairs; k++) {
+        if (msg_index[k] < 0 || msg_index[k] >= e->n_msgs)
+            return fail(e, RCA_ERR_ARG, "rca_text_match_pairs: pair %lld: message %d is not in the loaded arena (rca_text_load)", (long long)k, msg_index[k]);
+        if (needle_a[k] < -1 || needle_a[k] >= n_needles || needle_b[k] < -1 || needle_b[k] >= n_needles)
+            return fail(e, RCA_ERR_ARG, "rca_text_match_pairs: pair %lld: needle index out of range", (long long)k);
+    }
+    CK(cudaSetDevice(e->device));
+    const size_t nbytes = n_needles ? (size_t)needle_off[n_needles] : 0;
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t o_nb = 0, o_no = al(nbytes + 1), o_hay = o_no + al(((size_t)n_needles + 1) * 8), o_a = o_hay + al((size_t)n_pairs * 4),
+                 o_b = o_a + al((size_t)n_pairs * 4), o_out = o_b + al((size_t)n_pairs * 4), need = o_out + al((size_t)n_pairs);
+    if (need > e->io_cap) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->io_buf) CK(cudaFree(e->io_buf));
+        e->io_buf = nullptr; e->io_cap = 0;
+        CK(cudaMalloc(&e->io_buf, need));
+        e->io_cap = need;
+    }
+    char *b = (char *)e->io_buf;
+    const long long zero = 0;
+    if (nbytes) CK(cudaMemcpyAsync(b + o_nb, needle_bytes, nbytes, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_no, n_needles ? (const void *)needle_off : (const void *)&zero, ((size_t)n_needles + 1) * 8, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_hay, msg_index, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_a, needle_a, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(b + o_b, needle_b, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, e->stream));
+    PairParams pp;
+    pp.msg = e->msg_bytes; pp.msg_off = e->msg_off;
+    pp.ndl = (const unsigned char *)(b + o_nb); pp.ndl_off = (const long long *)(b + o_no);
+    pp.hay = (const int *)(b + o_hay); pp.na = (const int *)(b + o_a); pp.nb = (const int *)(b + o_b);
+    pp.n = n_pairs; pp.out = (unsigned char *)(b + o_out);
+    match_pairs<<<(unsigned)((n_pairs * 32 + 255) / 256), 256, 0, e->stream>>>(pp);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_flags, b + o_out, (size_t)n_pairs, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return RCA_OK;
+}
+
 // ================================================================================================
 // rca_expand_static: the same expansion for callers that must not allocate.
 //

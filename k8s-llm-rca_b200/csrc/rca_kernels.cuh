@@ -1412,4 +1412,47 @@ __global__ void __launch_bounds__(256) contains_scan(const __grid_constant__ Tex
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// match_pairs: the message filter that follows an instance query (generate_query/generate_query.py:104-129:
+// a row survives iff its destination's name, or its kind, occurs in the event's message), for many
+// (message, name, kind) triples at once.  One warp per triple: the lanes take the start positions of the
+// message 32 at a time and compare bytes; messages are a hundred bytes, needles ten or twenty.
+struct PairParams {
+    const unsigned char *msg;         // the loaded message arena (rca_text_load)
+    const long long *msg_off;
+    const unsigned char *ndl;         // needle bytes, concatenated
+    const long long *ndl_off;
+    const int *hay, *na, *nb;         // [n] message index, first and second needle index (-1: none)
+    long long n;
+    unsigned char *out;               // [n] 1 = one of the needles occurs in the message
+};
+
+__device__ __forceinline__ bool warp_find(const unsigned char *h, int hn, const unsigned char *x, int xn, int lane) {
+    if (xn == 0) return true;                         // '' in s
+    if (xn > hn) return false;
+    const unsigned char x0 = x[0];
+    for (int base = 0; base <= hn - xn; base += 32) {
+        const int pos = base + lane;
+        bool ok = pos <= hn - xn && h[pos] == x0;
+        for (int k = 1; ok && k < xn; k++) ok = h[pos + k] == x[k];
+        if (__any_sync(0xffffffffu, ok)) return true;
+    }
+    return false;
+}
+
+__global__ void __launch_bounds__(256) match_pairs(const __grid_constant__ PairParams p) {
+    const long long k = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (k >= p.n) return;
+    const int m = p.hay[k];
+    const long long hb = p.msg_off[m];
+    const int hn = (int)(p.msg_off[m + 1] - hb);
+    bool hit = false;
+    const int a = p.na[k], b = p.nb[k];
+    if (a >= 0) hit = warp_find(p.msg + hb, hn, p.ndl + p.ndl_off[a], (int)(p.ndl_off[a + 1] - p.ndl_off[a]), lane);
+    if (!hit && b >= 0) hit = warp_find(p.msg + hb, hn, p.ndl + p.ndl_off[b], (int)(p.ndl_off[b + 1] - p.ndl_off[b]), lane);
+    if (lane == 0) p.out[k] = hit ? 1 : 0;
+}
+
 }  // namespace rca

@@ -24,7 +24,7 @@ EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set
            "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_graph_bytes", "rca_reserve",
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_text_load",
-           "rca_text_contains", "rca_version")
+           "rca_text_contains", "rca_text_match_pairs", "rca_version")
 
 
 class RcaError(RuntimeError):
@@ -104,6 +104,8 @@ def load_library(path: str | None = None):
     lib.rca_state_window.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
     lib.rca_text_load.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    lib.rca_text_match_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_int64, C.c_void_p]
     lib.rca_text_contains.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
                                       C.POINTER(C.c_int64)]
     if path is None:
@@ -415,6 +417,32 @@ class Engine:
             elif u in by_u:
                 hits[i] = by_u[u]
         return first[idx], hits
+
+    def match_pairs(self, msg_nodes, needles_a, needles_b):
+        """The message filter of an instance query for many rows at once (generate_query.py:104-129):
+        flag[k] = needles_a[k] in message(msg_nodes[k]) or needles_b[k] in message(msg_nodes[k]).
+        msg_nodes: node ids whose messages were given to text_load(); needles: str, or None for 'no such text'."""
+        n = len(msg_nodes)
+        if n == 0:
+            return np.zeros(0, dtype=bool)
+        nodes = np.asarray(msg_nodes, dtype=np.int32)
+        idx = np.searchsorted(self._text_nodes, nodes)
+        if (idx >= len(self._text_nodes)).any() or (self._text_nodes[np.minimum(idx, len(self._text_nodes) - 1)] != nodes).any():
+            raise ValueError("match_pairs: a node has no message in the loaded arena")
+        uniq = {}
+        na, nb = np.empty(n, np.int32), np.empty(n, np.int32)
+        for col, arr in ((needles_a, na), (needles_b, nb)):
+            for k, t in enumerate(col):
+                arr[k] = -1 if t is None else uniq.setdefault(t, len(uniq))
+        enc = [t.encode("utf-8") for t in uniq]
+        off = np.zeros(len(enc) + 1, dtype=np.int64)
+        np.cumsum([len(b) for b in enc], out=off[1:])
+        blob = np.ascontiguousarray(np.frombuffer(b"".join(enc), dtype=np.uint8)) if off[-1] else np.zeros(1, np.uint8)
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        out = np.empty(n, np.uint8)
+        self._ck(self.lib.rca_text_match_pairs(self.h, blob.ctypes.data, off.ctypes.data, len(enc), idx.ctypes.data,
+                                               na.ctypes.data, nb.ctypes.data, n, out.ctypes.data))
+        return out.astype(bool)
 
     def state_lookup(self, nodes, ts, with_ids=True, ts_hi=None):
         """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids).

@@ -12,7 +12,7 @@ Two ways to run it here:
                            one chain expansion per involved-object edge type for the source kinds, the
                            metapath ladder once per distinct (srcKind, destKind) pair, one instance
                            expansion per metapath over all incidents of the group with the state
-                           predicate fused into emission.
+                           predicate fused into emission, one message-filter launch for all rows.
 Both return, per incident, the same canonical result: srcKind, metapaths, the filtered instance rows
 and, per row, the entities whose state is missing at the event's time.
 """
@@ -138,7 +138,7 @@ class IncidentReplayer:
             dest, inter = self.dest_fn(messages[i], src)
             results[i]["srcKind"] = src
             groups.setdefault((src, dest, tuple(inter)), []).append(i)
-        msg_of_evt = {}
+        cand = []                                                   # (incident, row, destination name, destination kind)
         for (src, dest, inter), members in groups.items():
             mps = self._metapaths(src, dest, list(inter))
             seeds = np.unique(evt[members])
@@ -167,22 +167,31 @@ class IncidentReplayer:
                         dprops[d] = (p[nk], p[kk])
                     by_evt.setdefault(e_, []).append((mp.key(), r, dprops[d]))
             for i in members:
-                res = results[i]
-                res["metapaths"] = [p.key() for p in mps]
+                results[i]["metapaths"] = [p.key() for p in mps]
                 for mpk, r, (dname, dkind) in by_evt.get(int(evt[i]), []):
-                    if dname in messages[i] or dkind in messages[i]:
-                        L = (len(r) - 2) // 3
-                        # column order of the instance query's RETURN: evt, r1, n1, r2, n2, ... (aliases by kind)
-                        cols = [r[0]]
-                        for k in range(1, L + 1):
-                            cols += [r[L + k], r[k]]
-                        miss_mask = r[3 * L + 2]
-                        missing = tuple(r[k] for k in range(2, L + 1) if (miss_mask >> k) & 1)
-                        res["rows"].append(tuple(cols))
-                        res["missing"].append(missing)
-                order = sorted(range(len(res["rows"])), key=lambda k: res["rows"][k])
-                res["rows"] = [res["rows"][k] for k in order]
-                res["missing"] = [res["missing"][k] for k in order]
+                    if dname is None or dkind is None:       # the reference's `None in message`
+                        raise TypeError("'in <string>' requires string as left operand, not NoneType")
+                    cand.append((i, r, dname, dkind))
+        # message filter (generate_query.py:104-129) for every row of every incident in one launch: the
+        # destination's name or kind must occur in the EVENT's message
+        keep = eng.match_pairs([int(evt[c[0]]) for c in cand], [c[2] for c in cand], [c[3] for c in cand])
+        for (i, r, _, _), ok in zip(cand, keep.tolist()):
+            if not ok:
+                continue
+            res = results[i]
+            L = (len(r) - 2) // 3
+            # column order of the instance query's RETURN: evt, r1, n1, r2, n2, ... (aliases by kind)
+            cols = [r[0]]
+            for k in range(1, L + 1):
+                cols += [r[L + k], r[k]]
+            miss_mask = r[3 * L + 2]
+            missing = tuple(r[k] for k in range(2, L + 1) if (miss_mask >> k) & 1)
+            res["rows"].append(tuple(cols))
+            res["missing"].append(missing)
+        for res in results:
+            order = sorted(range(len(res["rows"])), key=lambda k: res["rows"][k])
+            res["rows"] = [res["rows"][k] for k in order]
+            res["missing"] = [res["missing"][k] for k in order]
         return results
 
 

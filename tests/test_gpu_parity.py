@@ -375,3 +375,30 @@ def test_fused_state_filter_extreme_timestamps(eng_small, snap_small, csr_oracle
             miss |= (c == 0).astype(np.int64) << d
         assert np.array_equal(got[:, 3 * s + 2].astype(np.int64), miss)
     assert total > 0
+
+
+def test_message_filter_pairs(snap_10k):
+    """rca_text_match_pairs == Python's `a in m or b in m` (generate_query.py:104-129) over random pairs."""
+    from k8s_llm_rca_b200 import engine
+    eng = engine.Engine(snap_10k)
+    ids, msgs = snap_10k.props.messages()
+    eng.text_load(ids, msgs)
+    rng = np.random.default_rng(12)
+    pick = rng.integers(0, len(msgs), size=4000)
+    pool = [msgs[i][a:a + n] for i, a, n in zip(rng.integers(0, len(msgs), 300).tolist(), rng.integers(0, 40, 300).tolist(),
+                                                  rng.integers(1, 30, 300).tolist())]
+    pool += ["Pod", "pod-", "Node", "node-1", "", "é", "x" * 400, "configmap", "zzz", None]
+    a = [pool[i] for i in rng.integers(0, len(pool), size=len(pick))]
+    b = [pool[i] for i in rng.integers(0, len(pool), size=len(pick))]
+    # half of the pairs get a needle that really is in their message
+    for k in range(0, len(pick), 2):
+        m = msgs[pick[k]]
+        a[k] = m[len(m) // 3: len(m) // 3 + 12]
+    got = eng.match_pairs(ids[pick], a, b)
+    want = [((x is not None and x in msgs[i]) or (y is not None and y in msgs[i])) for i, x, y in zip(pick.tolist(), a, b)]
+    assert got.tolist() == want
+    assert 0.4 < np.mean(want) < 1.0
+    assert eng.match_pairs([], [], []).shape == (0,)
+    with pytest.raises(ValueError):
+        eng.match_pairs([0], ["a"], ["b"])                  # node 0 is a Pod: it has no message
+    eng.close()
