@@ -395,6 +395,43 @@ def parse(text):
     return Parser(text).parse()
 
 
+# The statements of one incident differ from those of the next only in their string literals (the message,
+# ids, timestamps - the reference interpolates them into the text, analyze_root_cause.py:70-79).  parse_shared
+# lifts the literals out as parameters and parses each distinct skeleton once.
+_STR_LIT = re.compile(r"""'(?:[^'\\]|\\.)*'|"(?:[^"\\]|\\.)*["]""")
+_RETURN_KW = re.compile(r"\bRETURN\b", re.I)
+_SKELETONS = {}
+
+
+def parse_shared(text):
+    """-> (clauses, {parameter name: literal value}).  Falls back to a plain parse (and its error
+    messages, which quote the text) whenever lifting is not clearly safe."""
+    if not isinstance(text, str) or "'" not in text and '"' not in text or "`" in text or "$__s" in text:
+        return parse(text), {}
+    lits = []
+
+    def lift(m):
+        lits.append(m.group())
+        return f"$__s{len(lits) - 1}"
+
+    skel = _STR_LIT.sub(lift, text)
+    last_ret = None
+    for last_ret in _RETURN_KW.finditer(skel):
+        pass
+    if last_ret is not None and "$__s" in skel[last_ret.end():]:
+        return parse(text), {}                           # a literal in RETURN names its column: keep the text
+    clauses = _SKELETONS.get(skel)
+    if clauses is None:
+        try:
+            clauses = Parser(skel).parse()
+        except CypherSyntaxError:
+            return parse(text), {}                       # report the error against the statement as written
+        if len(_SKELETONS) >= 512:
+            _SKELETONS.clear()
+        _SKELETONS[skel] = clauses
+    return clauses, {f"__s{i}": _unquote(v) for i, v in enumerate(lits)}
+
+
 # ------------------------------------------------------------------------------------------ evaluation
 class _Null:
     pass
@@ -562,10 +599,17 @@ def _unsupported(what):
                              f"k8s-llm-rca_b200/cypher.py")
 
 
-def compile_query(text, parameters=None):
-    """Parse `text` and recognise its shape.  Returns one of the *Plan dataclasses."""
+def compile_query(text, parameters=None, bind=None):
+    """Parse `text` and recognise its shape.  Returns one of the *Plan dataclasses.
+    bind: a dict that receives the string literals lifted out of the text (see parse_shared); a caller that
+    evaluates the plan's expressions later must pass the dict it evaluates with."""
     params = dict(parameters or {})
-    clauses = parse(text)
+    if bind is None:
+        clauses = parse(text)
+    else:
+        clauses, lifted = parse_shared(text)
+        params.update(lifted)
+        bind.update(lifted)
     matches = [c for c in clauses if c.kind == "MATCH"]
     ret = clauses[-1]
     if not matches:

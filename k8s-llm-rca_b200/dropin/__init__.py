@@ -36,6 +36,9 @@ def install(shim_only: bool = False, force_shim: bool = False) -> None:
 
 def _register_shim():
     import importlib
+    cur = sys.modules.get("neo4j")
+    if cur is not None and "k8s-llm-rca_b200" in (getattr(cur, "__file__", "") or "") and "neo4j.graph" in sys.modules:
+        return                                           # already in place: nothing to load again
     for name in ("neo4j", "neo4j.graph", "neo4j.exceptions"):
         if name in sys.modules and "k8s-llm-rca_b200" not in (getattr(sys.modules[name], "__file__", "") or ""):
             del sys.modules[name]

@@ -95,12 +95,23 @@ class GpuBackend:
         return self.engine.state_lookup(nodes, tmin_le, ts_hi=tmax_gt)
 
     def contains(self, texts):
-        """{index of text: sorted node ids whose `message` contains it} - on the device."""
+        """{index of text: sorted node ids whose `message` contains it} - on the device.
+        The statements of one incident ask for the same message more than once (S2, then every S4): the
+        answers of the last few hundred texts are kept (the snapshot does not change)."""
         if not self._text_loaded:
             ids, msgs = self.snap.props.messages()
             self.engine.text_load(ids, msgs)
             self._text_loaded = True
-        return self.engine.contains(texts)[1]
+            self._contains_memo = {}
+        memo = self._contains_memo
+        ask = [t for t in dict.fromkeys(texts) if t not in memo]
+        if ask:
+            hits = self.engine.contains(ask)[1]
+            if len(memo) + len(ask) > 1024:
+                memo.clear()
+            for i, t in enumerate(ask):
+                memo[t] = hits.get(i)
+        return {i: memo[t] for i, t in enumerate(texts) if memo.get(t) is not None}
 
 
 # ------------------------------------------------------------------------------------------ runner
@@ -114,7 +125,7 @@ class QueryRunner:
     # -- public
     def run(self, query, parameters=None):
         params = dict(parameters or {})
-        plan = cy.compile_query(query, params)
+        plan = cy.compile_query(query, params, bind=params)
         if isinstance(plan, cy.NodeScanPlan):
             return self._node_scan(plan, params)
         if isinstance(plan, cy.VarLenPlan):
