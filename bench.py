@@ -112,17 +112,36 @@ def run_reference(args, rank, world):
     dt = time.perf_counter() - t0
     v = inst / dt
     sample = f"first {n} of {w.n_inc} incidents of the config-3 batch per step"
-    print(json.dumps({
+    emit({
         "metric": METRIC, "value": v, "unit": "instances/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic", "impl": "reference",
         "config": {"workload": w.name, "objects": args.objects, "incidents_per_step": n},
         "cpu_baseline": {"value": v, "unit": "instances/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The one JSON line of this run, on the process's real stdout."""
+    data = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    # libraries (NCCL's version banner, for one) write to file descriptor 1; the contract is ONE JSON line there,
+    # so everything else that lands on fd 1 goes to stderr and the line is written to the saved descriptor
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -175,6 +194,18 @@ def main():
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
         counts = torch.zeros(world, dtype=torch.int64, device=dev)
         my_count = torch.zeros(1, dtype=torch.int64, device=dev)
+        peer_ok = False
+        if world > 1:
+            from k8s_llm_rca_b200 import parallel
+            try:
+                parallel.connect_peers(eng)
+                got = eng.peer_allgather(rank + 1)
+                peer_ok = got.tolist() == list(range(1, world + 1))
+            except Exception as ex:                                              # no peer access between these GPUs: NCCL does it
+                print(f"bench.py: peer-memory count exchange unavailable ({ex}); using NCCL all-gather", file=sys.stderr)
+            flag = torch.tensor([1 if peer_ok else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)                          # all ranks take the same road
+            peer_ok = bool(flag.item())
 
         # size the pinned result buffer from one untimed run
         tot0, res0 = w.run(eng, d_pods, d_ev, d_ts)
@@ -194,8 +225,11 @@ def main():
             else:
                 tot, res = w.run(eng, h_pods.numpy(), h_ev.numpy(), h_ts.numpy(), fetch=fetch)
             if world > 1:       # the only collective of the path: every rank learns every rank's count
-                my_count.fill_(tot)                                              # no host -> device copy, nothing to wait for
-                dist.all_gather_into_tensor(counts, my_count)
+                if peer_ok:     # ... over peer memory: one small kernel on the engine's stream, nothing on the host
+                    eng.peer_allgather(tot, wait=False)
+                else:
+                    my_count.fill_(tot)
+                    dist.all_gather_into_tensor(counts, my_count)
             return tot, res
 
         def timed(resident, steps):
@@ -235,6 +269,9 @@ def main():
         t0 = time.perf_counter()
         ms_e2e, inst_e2e, _, _ = timed(False, args.steps)
         wall_e2e = time.perf_counter() - t0
+        if peer_ok:                                                              # what the last exchange delivered
+            last = eng.peer_wait()
+            assert len(last) == world and (last > 0).all(), f"count exchange returned {last}"
         barrier()
         sampler.window(t_win0, time.time())
         clocks = sampler.stop() if rank == 0 else None
@@ -305,7 +342,8 @@ def main():
                        "instances_per_step": inst_res // args.steps, "max_hops": w.max_hops,
                        "graph_bytes_in_hbm": int(eng.graph_bytes()),
                        "l2": f"flushed between timed steps (256 MiB write); graph ({eng.graph_bytes() / 1e6:.0f} MB) also exceeds the 126 MB L2",
-                       "parallelism": f"graph replicated x{world}, one incident batch per GPU, all-gather of counts"},
+                       "parallelism": f"graph replicated x{world}, one incident batch per GPU, all-gather of counts"
+                                      + (" over peer memory (rca_peer_allgather)" if peer_ok else " (NCCL)" if world > 1 else "")},
             "e2e": {"value": inst_e2e / (ms_e2e * 1e-3), "unit": "instances/s",
                     "h2d_bytes_per_step": int(6 * (pods.nbytes + ts.nbytes)),
                     "d2h_bytes_per_step": int(d2h[0] // args.steps), "ms_per_step": ms_e2e / args.steps,
@@ -330,7 +368,7 @@ def main():
             dt = time.perf_counter() - t0
             out["cpu_baseline"] = {"value": ctot / dt, "unit": "instances/s", "cores": cores, "kind": "port",
                                    "sample": f"first {n} of {len(pods)} incidents of the same batch, one pass, {dt:.1f} s"}
-        print(json.dumps(out))
+        emit(out)
     eng.close()
     if world > 1:
         dist.destroy_process_group()

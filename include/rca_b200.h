@@ -201,6 +201,25 @@ int rca_text_match_pairs(rca_engine_t *e, const uint8_t *needle_bytes, const int
                          const int32_t *msg_index, const int32_t *needle_a, const int32_t *needle_b, int64_t n_pairs,
                          uint8_t *out_flags);
 
+/* ---- Count exchange over peer memory -------------------------------------------------------------
+ * The one collective of the path (every rank learns every rank's instance count; the reference has no
+ * counterpart - it is one process) done by the GPUs themselves over NVLink / NVSwitch: each rank stores its
+ * value into a slot of every peer's array and waits until its own array is complete.  One launch of
+ * `world` threads on the engine's stream; nothing on the host, no NCCL call on the step's critical path.
+ * Ranks are processes of ONE box (at most 8); the arrays are shared with CUDA IPC handles, which the caller
+ * carries between the processes (any channel: torch.distributed, a file, a pipe).
+ *   rca_peer_handle   allocate this engine's array, return its handle (RCA_PEER_HANDLE_BYTES bytes)
+ *   rca_peer_connect  map the arrays of all ranks (handles in rank order, this rank's own included)
+ *   rca_peer_allgather publish `value`; out_values != NULL: wait and return all `world` values (rank
+ *                     order); NULL: only enqueue, the result is collected by rca_peer_wait.  Collective:
+ *                     every rank calls it the same number of times.  A peer that does not show up within
+ *                     two seconds makes the call fail instead of hanging the GPU. */
+#define RCA_PEER_HANDLE_BYTES 64
+int rca_peer_handle(rca_engine_t *e, int32_t world, uint8_t *out_handle);
+int rca_peer_connect(rca_engine_t *e, int32_t rank, const uint8_t *handles);
+int rca_peer_allgather(rca_engine_t *e, int64_t value, int64_t *out_values);
+int rca_peer_wait(rca_engine_t *e, int64_t *out_values);
+
 /* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
  * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory
  * that every GPU which loads the library keeps until the process exits. */

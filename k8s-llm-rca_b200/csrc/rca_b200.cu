@@ -119,6 +119,13 @@ struct rca_engine {
     std::vector<cudaStream_t> side;
     std::vector<cudaEvent_t> ev_side;
     cudaEvent_t ev_fork = nullptr;
+    // count exchange over peer memory (rca_peer_*)
+    int peer_rank = -1, peer_world = 0;
+    PeerSlot *peer_own = nullptr;         // [2][world] this rank's slots, written by the peers
+    PeerSlot *peer_slots[8] = {nullptr};  // every rank's slot array (own one included), as mapped into this process
+    long long *peer_out = nullptr, *peer_out_h = nullptr;   // [world] device / pinned
+    unsigned *peer_err = nullptr;
+    unsigned long long peer_seq = 0;
     // results of the last submission (one per plan) and the one the accessors address
     std::vector<PlanResult> results;
     int selected = 0;
@@ -297,6 +304,12 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->h_ptab) cudaFreeHost(e->h_ptab);
     if (e->mh_ptab) cudaFreeHost(e->mh_ptab);
     if (e->mh_ctl) cudaFreeHost(e->mh_ctl);
+    for (int r = 0; r < e->peer_world; r++)
+        if (r != e->peer_rank && e->peer_slots[r]) cudaIpcCloseMemHandle(e->peer_slots[r]);
+    if (e->peer_own) cudaFree(e->peer_own);
+    if (e->peer_out) cudaFree(e->peer_out);
+    if (e->peer_err) cudaFree(e->peer_err);
+    if (e->peer_out_h) cudaFreeHost(e->peer_out_h);
     for (auto ev : e->ev_many) cudaEventDestroy(ev);
     for (auto ev : e->ev_side) cudaEventDestroy(ev);
     for (auto st : e->side) cudaStreamDestroy(st);
@@ -1186,6 +1199,76 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
 extern "C" int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt,
                                 int64_t n, int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
     return state_query(e, "rca_state_window", nodes, tmin_le, tmax_gt, n, on_device, out_first, out_cnt, out_ids);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Count exchange over peer memory: see peer_exchange in rca_kernels.cuh.
+static_assert(sizeof(cudaIpcMemHandle_t) == RCA_PEER_HANDLE_BYTES, "RCA_PEER_HANDLE_BYTES must be the size of cudaIpcMemHandle_t");
+
+extern "C" int rca_peer_handle(rca_engine_t *e, int32_t world, uint8_t *out_handle) {
+    if (!e) return RCA_ERR_ARG;
+    if (world < 1 || world > 8 || !out_handle) return fail(e, RCA_ERR_ARG, "rca_peer_handle: world %d not in 1..8, or null handle", world);
+    if (e->peer_own) return fail(e, RCA_ERR_ARG, "rca_peer_handle: already called on this engine");
+    CK(cudaSetDevice(e->device));
+    CK(cudaMalloc((void **)&e->peer_own, 2 * (size_t)world * sizeof(PeerSlot)));
+    CK(cudaMemset(e->peer_own, 0, 2 * (size_t)world * sizeof(PeerSlot)));
+    CK(cudaMalloc((void **)&e->peer_out, (size_t)world * sizeof(long long)));
+    CK(cudaMalloc((void **)&e->peer_err, sizeof(unsigned)));
+    CK(cudaMemset(e->peer_err, 0, sizeof(unsigned)));
+    CK(cudaMallocHost((void **)&e->peer_out_h, ((size_t)world + 1) * sizeof(long long)));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, e->peer_own));
+    std::memcpy(out_handle, &h, sizeof h);
+    e->peer_world = world;
+    return RCA_OK;
+}
+
+extern "C" int rca_peer_connect(rca_engine_t *e, int32_t rank, const uint8_t *handles) {
+    if (!e) return RCA_ERR_ARG;
+    if (!e->peer_own) return fail(e, RCA_ERR_ARG, "rca_peer_connect: call rca_peer_handle first");
+    if (rank < 0 || rank >= e->peer_world || !handles) return fail(e, RCA_ERR_ARG, "rca_peer_connect: rank %d not in 0..%d, or null handles", rank, e->peer_world - 1);
+    if (e->peer_rank >= 0) return fail(e, RCA_ERR_ARG, "rca_peer_connect: already connected");
+    CK(cudaSetDevice(e->device));
+    for (int r = 0; r < e->peer_world; r++) {
+        if (r == rank) { e->peer_slots[r] = e->peer_own; continue; }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + (size_t)r * sizeof h, sizeof h);
+        void *ptr = nullptr;
+        CK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+        e->peer_slots[r] = (PeerSlot *)ptr;
+    }
+    e->peer_rank = rank;
+    return RCA_OK;
+}
+
+extern "C" int rca_peer_allgather(rca_engine_t *e, int64_t value, int64_t *out_values) {
+    if (!e) return RCA_ERR_ARG;
+    if (e->peer_rank < 0) return fail(e, RCA_ERR_ARG, "rca_peer_allgather: not connected (rca_peer_handle, rca_peer_connect)");
+    CK(cudaSetDevice(e->device));
+    PeerParams p;
+    std::memset(&p, 0, sizeof p);
+    const unsigned long long seq = ++e->peer_seq;
+    for (int r = 0; r < e->peer_world; r++) p.slots[r] = e->peer_slots[r] + (seq & 1) * (size_t)e->peer_world;
+    p.rank = e->peer_rank; p.world = e->peer_world; p.seq = seq;
+    p.dev_value = nullptr; p.host_value = value;
+    p.out = e->peer_out; p.err = e->peer_err;
+    peer_exchange<<<1, 32, 0, e->stream>>>(p);
+    CK(cudaGetLastError());
+    if (out_values) return rca_peer_wait(e, out_values);
+    return RCA_OK;
+}
+
+extern "C" int rca_peer_wait(rca_engine_t *e, int64_t *out_values) {
+    if (!e) return RCA_ERR_ARG;
+    if (e->peer_rank < 0 || !out_values) return fail(e, RCA_ERR_ARG, "rca_peer_wait: not connected, or null buffer");
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemcpyAsync(e->peer_out_h, e->peer_out, (size_t)e->peer_world * sizeof(long long), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(e->peer_out_h + e->peer_world, e->peer_err, sizeof(unsigned), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    if (*(const unsigned *)(e->peer_out_h + e->peer_world))
+        return fail(e, RCA_ERR_CUDA, "rca_peer_allgather: a peer did not publish its value within two seconds");
+    for (int r = 0; r < e->peer_world; r++) out_values[r] = e->peer_out_h[r];
+    return RCA_OK;
 }
 
 // ---- message CONTAINS on the device

@@ -1455,4 +1455,50 @@ __global__ void __launch_bounds__(256) match_pairs(const __grid_constant__ PairP
     if (lane == 0) p.out[k] = hit ? 1 : 0;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// peer_exchange: the one collective of the path - every rank learns every rank's instance count
+//  - done by the ranks themselves over NVLink / NVSwitch peer memory.  Every engine
+// owns an array of `world` slots {value, seq}; rank r's thread t stores its value, then the sequence
+// number, into slot r of rank t's array (a plain remote store and a release store), and then waits
+// until slot t of its OWN array carries the same sequence number.  One launch of `world` threads, no
+// host involvement, no NCCL call on the step's critical path; the wait gives up after about two
+// seconds and raises *err instead of hanging the GPU.
+struct PeerSlot {
+    long long value;
+    unsigned long long seq;
+};
+struct PeerParams {
+    PeerSlot *slots[8];               // slots[t]: rank t's array of this exchange's parity (own array at index rank);
+                                      // two arrays alternate, so a fast rank's next value cannot land before a slow
+                                      // rank has read this one (it cannot be two exchanges ahead: it waits for everyone)
+    int rank, world;
+    unsigned long long seq;           // this exchange's number (1, 2, ...; the same on every rank)
+    const unsigned long long *dev_value;   // value to publish, read on the device ...
+    long long host_value;             // ... or given by the host (dev_value null)
+    long long *out;                   // [world] the values of all ranks, rank order (device memory of this rank)
+    unsigned *err;
+};
+
+__global__ void peer_exchange(const __grid_constant__ PeerParams p) {
+    const int t = threadIdx.x;
+    if (t >= p.world) return;
+    const long long mine = p.dev_value ? (long long)*p.dev_value : p.host_value;
+    PeerSlot *dst = p.slots[t] + p.rank;
+    dst->value = mine;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&dst->seq), "l"(p.seq) : "memory");
+    const PeerSlot *src = p.slots[p.rank] + t;
+    unsigned long long t0 = 0, now = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (true) {
+        unsigned long long s;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(s) : "l"(&src->seq) : "memory");
+        if (s >= p.seq) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > 2000000000ull) { atomicOr(p.err, 1u); break; }
+        __nanosleep(200);
+    }
+    p.out[t] = src->value;
+}
+
 }  // namespace rca

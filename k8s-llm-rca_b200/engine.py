@@ -24,7 +24,8 @@ EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set
            "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_graph_bytes", "rca_reserve",
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_text_load",
-           "rca_text_contains", "rca_text_match_pairs", "rca_version")
+           "rca_text_contains", "rca_text_match_pairs", "rca_peer_handle", "rca_peer_connect", "rca_peer_allgather",
+           "rca_peer_wait", "rca_version")
 
 
 class RcaError(RuntimeError):
@@ -104,6 +105,10 @@ def load_library(path: str | None = None):
     lib.rca_state_window.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
     lib.rca_text_load.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    lib.rca_peer_handle.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    lib.rca_peer_connect.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    lib.rca_peer_allgather.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    lib.rca_peer_wait.argtypes = [C.c_void_p, C.c_void_p]
     lib.rca_text_match_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int64, C.c_void_p]
     lib.rca_text_contains.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
@@ -417,6 +422,36 @@ class Engine:
             elif u in by_u:
                 hits[i] = by_u[u]
         return first[idx], hits
+
+    # -- count exchange over peer memory (include/rca_b200.h: rca_peer_*)
+    PEER_HANDLE_BYTES = 64
+
+    def peer_handle(self, world: int) -> bytes:
+        buf = C.create_string_buffer(self.PEER_HANDLE_BYTES)
+        self._ck(self.lib.rca_peer_handle(self.h, int(world), buf))
+        self._peer_world = int(world)
+        return buf.raw
+
+    def peer_connect(self, rank: int, handles) -> None:
+        """handles: the peer_handle() bytes of every rank, in rank order."""
+        blob = b"".join(handles)
+        assert len(blob) == self._peer_world * self.PEER_HANDLE_BYTES
+        self._ck(self.lib.rca_peer_connect(self.h, int(rank), blob))
+
+    def peer_allgather(self, value: int, wait: bool = True):
+        """Publish `value` to every rank and (wait=True) return all ranks' values; wait=False only enqueues
+        the exchange on the engine's stream - collect with peer_wait()."""
+        if not wait:
+            self._ck(self.lib.rca_peer_allgather(self.h, int(value), None))
+            return None
+        out = np.empty(self._peer_world, np.int64)
+        self._ck(self.lib.rca_peer_allgather(self.h, int(value), out.ctypes.data))
+        return out
+
+    def peer_wait(self):
+        out = np.empty(self._peer_world, np.int64)
+        self._ck(self.lib.rca_peer_wait(self.h, out.ctypes.data))
+        return out
 
     def match_pairs(self, msg_nodes, needles_a, needles_b):
         """The message filter of an instance query for many rows at once (generate_query.py:104-129):

@@ -72,6 +72,20 @@ def allgather_counts(local_counts, device="cpu"):
     return out.view(world, mine.numel())
 
 
+def connect_peers(engine):
+    """Set up the engine's count exchange over peer memory (rca_peer_*): the CUDA IPC handles of the ranks'
+    slot arrays travel through torch.distributed once; afterwards engine.peer_allgather(value) is one small
+    kernel on the engine's stream - no NCCL call, nothing on the host - per exchange."""
+    rank, world = world_info()
+    mine = engine.peer_handle(world)
+    if world == 1:
+        handles = [mine]
+    else:
+        handles = [None] * world
+        _dist().all_gather_object(handles, mine)
+    engine.peer_connect(rank, handles)
+
+
 def ladder_decision(counts_by_rank):
     """From allgather_counts output: (any rows anywhere?, globally shortest length with rows or -1)."""
     tot = counts_by_rank.sum(dim=0)

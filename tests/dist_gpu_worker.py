@@ -45,6 +45,16 @@ def main():
             got = out["rows"][s].cpu().numpy()
             assert np.array_equal(sort_rows(got), sort_rows(rows))
             assert np.all(np.diff(got[:, 0]) >= 0)           # rank-order concatenation is ordered by seed
+    # the count exchange over peer memory gives what NCCL's all-gather gives, round after round
+    parallel.connect_peers(eng)
+    for k in range(20):
+        mine = 1000 * k + 7 * rank + (1 << 40) * (k % 3)
+        got = eng.peer_allgather(mine)
+        ref = parallel.allgather_counts([mine], device=f"cuda:{local}")[:, 0].cpu().numpy()
+        assert np.array_equal(got, ref), (k, got, ref)
+    eng.peer_allgather(rank, wait=False)                     # enqueue only ...
+    eng.peer_allgather(10 + rank, wait=False)
+    assert eng.peer_wait().tolist() == [10 + r for r in range(world)]      # ... the last exchange is what wait returns
     dist.barrier()
     eng.close()
     dist.destroy_process_group()
