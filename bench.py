@@ -345,7 +345,7 @@ def main():
                        "parallelism": f"graph replicated x{world}, one incident batch per GPU, all-gather of counts"
                                       + (" over peer memory (rca_peer_allgather)" if peer_ok else " (NCCL)" if world > 1 else "")},
             "e2e": {"value": inst_e2e / (ms_e2e * 1e-3), "unit": "instances/s",
-                    "h2d_bytes_per_step": int(6 * (pods.nbytes + ts.nbytes)),
+                    "h2d_bytes_per_step": int(pods.nbytes + ev.nbytes + 2 * ts.nbytes),     # the five instance queries share one seed list
                     "d2h_bytes_per_step": int(d2h[0] // args.steps), "ms_per_step": ms_e2e / args.steps,
                     "wall_ms_per_step": 1e3 * wall_e2e / args.steps},
             "gpu_launches": int(launches),

@@ -496,12 +496,14 @@ static KernelSet pick_kernels(int mode, int q) {
     }
 }
 
-// unit steps (rca_kernels.cuh): typed step, at most one candidate per path, path so far of 2..4 nodes
+// unit steps (rca_kernels.cuh): typed step, at most one candidate per path, path so far of 2..6 nodes
 static KernelSet pick_unit_kernels(int q) {
     switch (q) {
         case 1: return KernelSet{count_unit<1>, fill_unit<1>, nullptr};
         case 2: return KernelSet{count_unit<2>, fill_unit<2>, nullptr};
-        default: return KernelSet{count_unit<3>, fill_unit<3>, nullptr};
+        case 3: return KernelSet{count_unit<3>, fill_unit<3>, nullptr};
+        case 4: return KernelSet{count_unit<4>, fill_unit<4>, nullptr};
+        default: return KernelSet{count_unit<5>, fill_unit<5>, nullptr};
     }
 }
 
@@ -736,7 +738,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 p.sub = j;
                 KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
                 size_t dyn_c = dyn, dyn_f = dyn;
-                if (pp.level_typed[s] && e->unit_steps && pp.mode == kModeSimple && s >= 2 && s <= 4 &&
+                if (pp.level_typed[s] && e->unit_steps && pp.mode == kModeSimple && s >= 2 && s <= 6 &&
                     (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t] >= 0) {
                     ks = pick_unit_kernels(s - 1);
                     p.unit_next = e->unit_next + (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t];
@@ -750,6 +752,10 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 if (s == 1) grid = (int)std::min<long long>(grid, first);
                 ks.count<<<grid, kThreads, dyn_c, e->stream>>>(p);
                 scan_groups<<<1, 1024, 0, e->stream>>>(p);
+                if (pl->count_only && s == L) {       // nothing continues after the last level and no row is stored
+                    *launches += 2;
+                    continue;
+                }
                 grid = max_grid(e, ks.fill, dyn_f);
                 if (s == 1) grid = (int)std::min<long long>(grid, first);
                 ks.fill<<<grid, kThreads, dyn_f, e->stream>>>(p);
@@ -976,6 +982,13 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
     if (!seeds_on_device) {
         long long off = 0;
         for (int k = 0; k < n_plans; k++) {
+            int same = -1;                            // plans of a submission often share one seed list: it is copied once
+            for (int j = 0; j < k && same < 0; j++) {
+                if (seeds[j] != seeds[k] || n_seeds[j] != n_seeds[k]) continue;
+                if (plans[k].with_states && !(plans[j].with_states && seed_ts[j] == seed_ts[k])) continue;
+                same = j;
+            }
+            if (same >= 0) { at[k] = at[same]; continue; }
             at[k] = off;
             rc = stage_seeds(e, seeds[k], seed_ts ? seed_ts[k] : nullptr, n_seeds[k], plans[k].with_states != 0, off, total_seeds);
             if (rc) return rc;

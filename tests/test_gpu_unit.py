@@ -41,7 +41,7 @@ def test_every_kind_pair_same_bytes_as_general_kernels(eng, snap_small, csr_orac
         for src in ENTITY_KINDS:
             seeds = snap_small.nodes_of_kind(snap_small.kind_index(src))
             for dst in ENTITY_KINDS:
-                for hops in (2, 3, 4, 5):
+                for hops in (2, 3, 4, 5, 6):
                     kw = dict(dest_kind=snap_small.kind_index(dst), excl_kinds=excl, entity_only=True)
                     plan = engine.varlen_plan(direction, hops, **kw)
                     (on, rows_on), (off, rows_off) = _both(eng, plan, seeds)
