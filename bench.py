@@ -177,7 +177,7 @@ def main():
     from k8s_llm_rca_b200 import workloads
     w = workloads.Config3(n_objects=args.objects, n_events=args.events)
     eng = E.Engine(w.snap, device=local_rank)
-    stream = torch.cuda.Stream()
+    stream = torch.cuda.Stream(priority=-1)      # above the engine's side streams (include/rca_b200.h: rca_set_stream)
     eng.set_stream(stream.cuda_stream)
     pods, ev, ts = w.batch(rank)
     dev = torch.device("cuda", local_rank)

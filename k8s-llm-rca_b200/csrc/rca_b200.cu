@@ -191,7 +191,11 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
     g->device = device;
     g->sm_count = prop.multiProcessorCount;
     OCK(cudaSetDevice(device));
-    OCK(cudaStreamCreateWithFlags(&g->own_stream, cudaStreamNonBlocking));
+    {
+        int least = 0, greatest = 0;
+        OCK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        OCK(cudaStreamCreateWithPriority(&g->own_stream, cudaStreamNonBlocking, greatest));
+    }
     g->stream = g->own_stream;
     OCK(cudaEventCreate(&g->ev0));
     OCK(cudaEventCreate(&g->ev1));
@@ -638,33 +642,41 @@ struct RunBufs {
     unsigned long long ocap = 0;                 // output words this plan may use (0: the whole arena)
 };
 
+// Parameters of a one-launch chain (chain_walk / chain_line / chain_batch).
+static void chain_params(rca_engine *e, const PreparedPlan &pp, const RunBufs &b, ChainParams &c, bool &line) {
+    const rca_plan_t *pl = pp.pl;
+    const int L = pp.L;
+    std::memset(&c, 0, sizeof c);
+    c.L = L;
+    for (int i = 0; i < L; i++) {
+        const int t = pl->step_etype[i];
+        const bool out = pl->step_dir[i] == RCA_DIR_OUT;
+        const int rowk = out ? e->et_src[t] : e->et_dst[t];
+        c.rng[i] = out ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t];
+        const long long ub = e->unit_steps ? (out ? e->unit_out_base : e->unit_in_base)[t] : -1;
+        c.unit[i] = ub >= 0 ? e->unit_next + ub : nullptr;
+        c.row_lo[i] = e->kind_start[rowk];
+        c.row_hi[i] = e->kind_start[rowk + 1];
+        c.against[i] = out ? 0 : 1;
+    }
+    c.adj1 = e->out_dst; c.adj2 = e->in_adj; c.n_nodes = e->n_nodes;
+    c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
+    c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
+    c.out = e->out; c.ocap = b.ocap ? b.ocap : e->ocap; c.ctl = b.ctl; c.tstate = e->tstate + b.tstate_at;
+    c.st_head = e->st_head; c.n_head = e->n_head; c.st_off = e->st_off; c.st_rec = e->st_rec;
+    line = true;                                      // all steps before the last are unit steps: no search needed
+    for (int i = 0; i + 1 < L; i++) line &= c.unit[i] != nullptr;
+}
+
 // Enqueue every level of a prepared plan on the engine's stream.  ev_lv (nullable): one event per level.
 static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b, cudaEvent_t *ev_lv, int *launches) {
     const rca_plan_t *pl = pp.pl;
     const int L = pp.L;
     if (pp.walk) {                                    // the whole chain in one launch
         ChainParams c;
-        std::memset(&c, 0, sizeof c);
-        c.L = L;
-        for (int i = 0; i < L; i++) {
-            const int t = pl->step_etype[i];
-            const bool out = pl->step_dir[i] == RCA_DIR_OUT;
-            const int rowk = out ? e->et_src[t] : e->et_dst[t];
-            c.rng[i] = out ? e->typed_out + e->typed_out_base[t] : e->typed_in + e->typed_in_base[t];
-            const long long ub = e->unit_steps ? (out ? e->unit_out_base : e->unit_in_base)[t] : -1;
-            c.unit[i] = ub >= 0 ? e->unit_next + ub : nullptr;
-            c.row_lo[i] = e->kind_start[rowk];
-            c.row_hi[i] = e->kind_start[rowk + 1];
-            c.against[i] = out ? 0 : 1;
-        }
-        c.adj1 = e->out_dst; c.adj2 = e->in_adj; c.n_nodes = e->n_nodes;
-        c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
-        c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
-        c.out = e->out; c.ocap = b.ocap ? b.ocap : e->ocap; c.ctl = b.ctl; c.tstate = e->tstate + b.tstate_at;
-        c.st_head = e->st_head; c.n_head = e->n_head; c.st_off = e->st_off; c.st_rec = e->st_rec;
+        bool line;
+        chain_params(e, pp, b, c, line);
         const long long blocks = std::max<long long>(1, (b.n_seeds + kThreads - 1) / kThreads);
-        bool line = true;                             // all steps before the last are unit steps: no search needed
-        for (int i = 0; i + 1 < L; i++) line &= c.unit[i] != nullptr;
         if (line) chain_line<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
         else chain_walk<<<(unsigned)std::min<long long>(blocks, 148LL * 8), kThreads, 0, e->stream>>>(c);
         ++*launches;
@@ -1021,7 +1033,9 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
         const size_t want = std::min<size_t>((size_t)n_aside, 4);
         while (e->side.size() < want) {
             cudaStream_t st;
-            CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            int least = 0, greatest = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+            CK(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, least));     // the main stream's kernels go first
             e->side.push_back(st);
             cudaEvent_t ev;
             CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -1031,7 +1045,7 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
     }
 
     int retries = 0;
-    std::vector<int> launches((size_t)n_plans, 0);
+    std::vector<int> launches((size_t)n_plans, 0), leader((size_t)n_plans, -1);
     while (true) {
         unsigned long long groups = 0;
         rc = ensure_tile_arrays(e, max_seeds, any_fused, any_split, &groups, side_tiles);
@@ -1054,26 +1068,56 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
         CK(cudaMemcpyAsync(e->m_ctl, e->mh_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
         cudaStream_t main_stream = e->stream;
         if (n_aside) CK(cudaEventRecord(e->ev_fork, main_stream));          // uploads are done before any side plan starts
-        int prev = -1, n_side_used = 0;                                     // prev: the last plan that runs in the main stream
-        for (int k = 0; k < n_plans; k++) {
-            cudaEvent_t *evk = e->ev_many.data() + (size_t)k * ev_stride;
-            RunBufs b;
+        int prev = -1;                                                      // the last plan that runs in the main stream
+        auto bufs_of = [&](int k, RunBufs &b) -> int {
             b.seeds = seeds_on_device ? seeds[k] : e->seeds_buf + at[k];
             b.ts = plans[k].with_states ? (seeds_on_device ? (const long long *)seed_ts[k] : e->ts_buf + at[k]) : nullptr;
             b.n_seeds = n_seeds[k]; b.ctl = e->m_ctl + k; b.ptab = e->m_ptab + (size_t)k * pt_stride; b.epoch = 0; b.groups = groups;
-            if (pps[k].fused) { rc = next_epoch(e, &b.epoch); if (rc) return rc; }
-            if (aside[k]) {
-                cudaStream_t st = e->side[(size_t)n_side_used % e->side.size()];
-                if ((size_t)n_side_used < e->side.size()) CK(cudaStreamWaitEvent(st, e->ev_fork, 0));
-                n_side_used++;
-                b.tstate_at = side_tstate + tile_at[k];
-                e->stream = st;
-                CK(cudaEventRecord(evk[0], st));
-                rc = launch_levels(e, pps[k], b, evk, &launches[k]);
-                e->stream = main_stream;
-                if (rc) return rc;
-                continue;
+            if (pps[k].fused) return next_epoch(e, &b.epoch);
+            return RCA_OK;
+        };
+        // The side plans go first, kChainBatch of them per launch (chain_batch), all on one side stream: they
+        // start on an idle GPU and run beside the first levels of the main-stream plans.  (Enqueued after those,
+        // they waited for SM slots held by the main plans' kernels; one launch per plan cost the host more time
+        // than the chains take.)  The plans of a batch share its two timing events.
+        if (n_aside) {
+            cudaStream_t st = e->side[0];
+            CK(cudaStreamWaitEvent(st, e->ev_fork, 0));
+            int k = 0;
+            while (k < n_plans) {
+                ChainBatch cb;
+                std::memset(&cb, 0, sizeof cb);
+                int members[kChainBatch], nb = 0;
+                long long blocks = 1;
+                for (; k < n_plans && nb < kChainBatch; k++) {
+                    if (!aside[k]) continue;
+                    RunBufs b;
+                    rc = bufs_of(k, b);
+                    if (rc) return rc;
+                    b.tstate_at = side_tstate + tile_at[k];
+                    bool line;
+                    chain_params(e, pps[k], b, cb.p[nb], line);
+                    cb.p[nb].one_ticket = 1;
+                    cb.line[nb] = line ? 1 : 0;
+                    blocks = std::max<long long>(blocks, (n_seeds[k] + kThreads - 1) / kThreads);
+                    members[nb++] = k;
+                }
+                if (!nb) break;
+                cudaEvent_t *ev0 = e->ev_many.data() + (size_t)members[0] * ev_stride;
+                CK(cudaEventRecord(ev0[0], st));
+                chain_batch<<<dim3((unsigned)blocks, (unsigned)nb), kThreads, 0, st>>>(cb);     // one CTA per tile
+                CK(cudaGetLastError());
+                CK(cudaEventRecord(ev0[1], st));
+                for (int j = 0; j < nb; j++) { leader[members[j]] = members[0]; launches[members[j]] = j == 0 ? 1 : 0; }
             }
+            CK(cudaEventRecord(e->ev_side[0], st));
+        }
+        for (int k = 0; k < n_plans; k++) {
+            if (aside[k]) continue;
+            cudaEvent_t *evk = e->ev_many.data() + (size_t)k * ev_stride;
+            RunBufs b;
+            rc = bufs_of(k, b);
+            if (rc) return rc;
             b.ocap = e->ocap - top_words;
             if (!pps[k].fused) CK(cudaMemsetAsync(e->gsum, 0, groups * sizeof(ulonglong2), e->stream));
             if (prev >= 0) {                          // this plan's rows start where the previous main-stream plan's end
@@ -1087,10 +1131,7 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
             if (rc) return rc;
             prev = k;
         }
-        for (size_t j = 0; j < std::min<size_t>((size_t)n_side_used, e->side.size()); j++) {   // join
-            CK(cudaEventRecord(e->ev_side[j], e->side[j]));
-            CK(cudaStreamWaitEvent(main_stream, e->ev_side[j], 0));
-        }
+        if (n_aside) CK(cudaStreamWaitEvent(main_stream, e->ev_side[0], 0));    // join
         CK(cudaMemcpyAsync(e->mh_ctl, e->m_ctl, (size_t)n_plans * sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
         unsigned ov = 0;
@@ -1114,10 +1155,12 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
     for (int k = 0; k < n_plans; k++) {
         publish_result(e, e->results[k], &plans[k], pps[k].L, &e->mh_ctl[k]);
         if (stats) {
-            cudaEvent_t *evk = e->ev_many.data() + (size_t)k * ev_stride;
+            const bool batched = leader[k] >= 0;       // ran inside a chain_batch launch: the batch's two events
+            cudaEvent_t *evk = e->ev_many.data() + (size_t)(batched ? leader[k] : k) * ev_stride;
             float ms = 0.f;
-            cudaEventElapsedTime(&ms, evk[0], evk[pps[k].L]);
+            cudaEventElapsedTime(&ms, evk[0], evk[batched ? 1 : pps[k].L]);
             fill_stats(&stats[k], &plans[k], pps[k].L, n_seeds[k], &e->mh_ctl[k], ms, launches[k], retries);
+            if (batched) { stats[k].level_ms[pps[k].L] = ms; continue; }
             for (int s = pps[k].walk ? pps[k].L : 1; s <= pps[k].L; s++) {
                 float t = 0.f;
                 if (cudaEventElapsedTime(&t, evk[pps[k].walk ? 0 : s - 1], evk[s]) == cudaSuccess) stats[k].level_ms[s] = t;

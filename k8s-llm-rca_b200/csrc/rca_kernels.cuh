@@ -1010,6 +1010,8 @@ struct ChainParams {
     const int2 *adj2;
     int n_nodes;
     int with_states, count_only, row_len;
+    int one_ticket;                   // every CTA takes ONE tile and leaves (the grid has a CTA per tile): SM slots come
+                                      // free all the time, so a kernel of another stream can move in beside this one
     unsigned epoch;
     const int *seeds;
     const long long *seed_ts;
@@ -1095,7 +1097,7 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
     return rows;
 }
 
-__global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ ChainParams p) {
+__device__ __forceinline__ void chain_walk_body(const ChainParams &p) {
     // One ticket = 256 seeds (one per thread).  Row counts are scanned inside the CTA first and only the
     // CTA totals go through the look-back: every tile of a call is in flight at once (100 k seeds fill a
     // third of the GPU), so a tile waits for (tiles before it) / 32 look-back steps - 8 x fewer this way.
@@ -1108,7 +1110,7 @@ __global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ C
     unsigned long long sc[RCA_MAX_HOPS + 1], al[RCA_MAX_HOPS + 1];
     for (int k = 0; k <= RCA_MAX_HOPS; k++) { sc[k] = 0; al[k] = 0; }
     bool ov = false;
-    while (true) {
+    for (bool once = true; once || !p.one_ticket; once = false) {
         __syncthreads();                              // the previous tile's readers of s_* are done
         if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->ticket[L], 1u);
         __syncthreads();
@@ -1171,7 +1173,7 @@ __global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ C
 // relationships stay in registers across the look-back (no second walk, no local-memory stacks), the
 // state headers of the nodes are requested as the walk passes them, and only the last step may fan out
 // into several rows.  Same rows, same order, same counters as chain_walk.
-__global__ void __launch_bounds__(kThreads) chain_line(const __grid_constant__ ChainParams p) {
+__device__ __forceinline__ void chain_line_body(const ChainParams &p) {
     __shared__ unsigned s_tile;
     __shared__ unsigned long long s_wsum[kWarps], s_pre;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1184,7 +1186,7 @@ __global__ void __launch_bounds__(kThreads) chain_line(const __grid_constant__ C
 #pragma unroll
     for (int k = 0; k <= RCA_MAX_HOPS; k++) { sc[k] = 0; al[k] = 0; }
     bool ov = false;
-    while (true) {
+    for (bool once = true; once || !p.one_ticket; once = false) {
         __syncthreads();                              // the previous tile's readers of s_* are done
         if (threadIdx.x == 0) s_tile = atomicAdd(&ctl->ticket[L], 1u);
         __syncthreads();
@@ -1309,6 +1311,28 @@ __global__ void __launch_bounds__(kThreads) chain_line(const __grid_constant__ C
         }
     }
     if (ov && lane == 0) atomicOr(&ctl->overflow, 2u);
+}
+
+__global__ void __launch_bounds__(kThreads) chain_walk(const __grid_constant__ ChainParams p) { chain_walk_body(p); }
+__global__ void __launch_bounds__(kThreads) chain_line(const __grid_constant__ ChainParams p) { chain_line_body(p); }
+
+// Several one-launch chains in ONE launch (rca_expand_many: the instance queries of a submission): blockIdx.y
+// picks the chain.  Five chains of 100 k seeds each fill the GPU together where each alone fills a third of it,
+// and the host enqueues one kernel instead of five.  CTAs beyond a chain's own tile count leave at their first
+// ticket.
+constexpr int kChainBatch = 8;
+struct ChainBatch {
+    ChainParams p[kChainBatch];
+    int line[kChainBatch];            // 1: chain_line, 0: chain_walk
+};
+static_assert(sizeof(ChainBatch) <= 4000, "ChainBatch must fit the kernel parameter space");
+#ifndef RCA_MINB_BATCH
+#define RCA_MINB_BATCH 2
+#endif
+__global__ void __launch_bounds__(kThreads, RCA_MINB_BATCH) chain_batch(const __grid_constant__ ChainBatch b) {
+    const ChainParams &p = b.p[blockIdx.y];
+    if (b.line[blockIdx.y]) chain_line_body(p);
+    else chain_walk_body(p);
 }
 
 // rca_expand_many: the next plan's rows start where this plan's end (row_len 0 for count-only plans)
