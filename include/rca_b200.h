@@ -118,7 +118,10 @@ int rca_open(const rca_snapshot_t *snap, int device, rca_engine_t **out);
 int rca_close(rca_engine_t *e);
 /* text of the last error on this engine (or of the last failed rca_open when e == NULL) */
 const char *rca_last_error(const rca_engine_t *e);
-/* run the engine's work on this CUDA stream (cudaStream_t as an integer); 0 = its own stream */
+/* run the engine's work on this CUDA stream (cudaStream_t as an integer); 0 = its own stream (created
+ * with the highest priority).  rca_expand_many runs bounded plans on side streams of the LOWEST priority
+ * so that they fill the gaps the main plans leave: a caller's stream should be created above the lowest
+ * priority (cudaStreamCreateWithPriority / torch.cuda.Stream(priority=-1)) to get the same effect. */
 int rca_set_stream(rca_engine_t *e, uint64_t cuda_stream);
 /* Plans with at most `max_seeds` seeds run one fused launch per hop (fewest launches: the
  * per-incident latency case); larger seed sets run count / scan / fill launches per hop (no
