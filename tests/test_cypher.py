@@ -157,3 +157,34 @@ def test_three_valued_logic():
     assert ev("n.a = 1") is True and ev("n.missing = 1") is None and ev("not n.missing = 1") is None
     assert ev("n.missing = 1 or n.a = 1") is True and ev("n.missing = 1 and n.a = 2") is False
     assert ev("n.missing in ['x']") is None and ev("n.missing is null") is True
+
+
+def test_shared_parse_lifts_string_literals_and_falls_back_when_unsafe():
+    """parse_shared: statements that differ only in their string literals share one parse; the literals come
+    back as parameters; anything unsafe (a literal in RETURN, bad text) is parsed as written."""
+    a = S5
+    b = S5.replace("66637a34-b552-448f-9da6-976aa7462533", "0000").replace("06:35:02.011", "07:00:00.000")
+    ca, la = cy.parse_shared(a)
+    cb, lb = cy.parse_shared(b)
+    assert ca is cb                                            # one skeleton, parsed once
+    assert la == {"__s0": "66637a34-b552-448f-9da6-976aa7462533", "__s1": "2020-12-11 06:35:02.011",
+                  "__s2": "2020-12-11 06:35:02.011"}
+    assert lb["__s0"] == "0000" and lb["__s1"] == "2020-12-11 07:00:00.000"
+    # the compiled plan asks for the same things either way
+    bind = {}
+    lifted, plain = cy.compile_query(a, None, bind=bind), cy.compile_query(a)
+    assert type(lifted) is type(plain) and bind == la
+    assert cy.eval_expr(("param", "__s0"), {}, bind) == "66637a34-b552-448f-9da6-976aa7462533"
+    # quotes and escapes inside literals survive the lifting
+    for msg in ['with "double" quotes', "with 'single' quotes", "both ' and \"", "back\\slash and \n newline", "$__not a param"]:
+        q = f"MATCH (evt:EVENT) WHERE evt.message CONTAINS {msg!r} WITH evt LIMIT 1 MATCH (e:Event)-[r:HasEvent]->(evt) RETURN e"
+        bind = {}
+        p = cy.compile_query(q, None, bind=bind)
+        assert cy.eval_expr(p.seed_where[3], {}, bind) == msg
+    # a literal in RETURN names its column: not lifted
+    c, l = cy.parse_shared("MATCH (n:Pod) WHERE n.id = 'x' RETURN 'tag', n")
+    assert l == {} and c[-1].items[0][2] == "'tag'"
+    # errors quote the statement as written, not the skeleton
+    with pytest.raises(cy.CypherSyntaxError) as ei:
+        cy.compile_query("MATCH (n:Pod) WHERE n.id = 'abc' RETURN", None, bind={})
+    assert "__s0" not in str(ei.value)
