@@ -129,6 +129,8 @@ class Clause:
     items: list = field(default_factory=list)     # (expr, alias or None, source text)
     distinct: bool = False
     limit: int | None = None
+    order: list = field(default_factory=list)      # ORDER BY: (expr, descending)
+    skip: int = 0
 
 
 class Parser:
@@ -184,8 +186,23 @@ class Parser:
                 c.items.append(self.ret_item())
                 while self.accept("op", ","):
                     c.items.append(self.ret_item())
+                if self.accept("kw", "ORDER"):
+                    self.expect("kw", "BY", "BY after ORDER")
+                    while True:
+                        e = self.expr()
+                        t = self.accept("ident")
+                        if t is not None and t[1].upper() not in ("ASC", "ASCENDING", "DESC", "DESCENDING"):
+                            self.i -= 1
+                            self.err("ASC, DESC, SKIP, LIMIT or the end of the clause")
+                        c.order.append((e, t is not None and t[1].upper().startswith("DESC")))
+                        if not self.accept("op", ","):
+                            break
+                if self.accept("kw", "SKIP"):
+                    c.skip = int(self.expect("num", what="an integer after SKIP")[1])
                 if self.accept("kw", "LIMIT"):
                     c.limit = int(self.expect("num", what="an integer after LIMIT")[1])
+                if c.kind == "WITH" and (c.order or c.skip):
+                    raise _unsupported("ORDER BY / SKIP in a WITH clause")
                 clauses.append(c)
             elif self.at("kw"):
                 raise CypherSyntaxError(f"The clause {self.peek()[1]} is not supported by this executor "
@@ -563,6 +580,8 @@ class ChainPlan:
     steps: list                    # in walk order
     walk: list                     # per step: (from_var, to_var, 'out' | 'in')
     ret: Clause
+    unique: list = field(default_factory=list)   # groups of step indices written in ONE MATCH clause: Cypher binds
+                                                 # no relationship twice within a clause (across clauses it may)
 
 
 @dataclass
@@ -614,12 +633,9 @@ def compile_query(text, parameters=None, bind=None):
     ret = clauses[-1]
     if not matches:
         raise _unsupported("queries without MATCH")
-    for c in matches:
-        if len(c.patterns) != 1:
-            raise _unsupported("comma-separated patterns in one MATCH")
     pats = [c.patterns[0] for c in matches]
 
-    if len(matches) == 1:
+    if len(matches) == 1 and len(matches[0].patterns) == 1:
         p, where = pats[0], matches[0].where
         if not p.rels:
             return _compile_node_scan(p, where, ret, params)
@@ -802,9 +818,10 @@ def _compile_chain(clauses, params):
         for k, v in n.props.items():
             preds.append(("cmp", "=", ("prop", ("var", n.var), k), v))
 
-    for c in clauses[:-1]:
+    clause_of = []                                   # per hop: index of the MATCH clause it was written in
+    for ci, c in enumerate(clauses[:-1]):
         if c.kind == "MATCH":
-            p = c.patterns[0]
+          for p in c.patterns:                       # 'MATCH p1, p2' = both patterns in one clause
             if p.path_var:
                 raise _unsupported("path variables over typed patterns")
             for n in p.nodes:
@@ -822,10 +839,11 @@ def _compile_chain(clauses, params):
                 start, end = (a, b) if r.direction == "out" else (b, a)
                 key = r.props.get("key")
                 hops.append(ChainStep(r.var, list(r.types), key, start, end))
+                clause_of.append(ci)
                 for k, v in r.props.items():
                     if k != "key":
                         raise _unsupported("relationship property maps other than {key: ...}")
-            preds.extend(conjuncts(c.where))
+          preds.extend(conjuncts(c.where))
         elif c.kind == "WITH":
             if c.limit is not None:
                 if seed_limit is not None:
@@ -837,6 +855,9 @@ def _compile_chain(clauses, params):
                     raise _unsupported("WITH items other than plain variables")
     if not hops:
         raise _unsupported("this query shape")
+    used = {h.start_var for h in hops} | {h.end_var for h in hops}
+    if any(v not in used for v in labels):
+        raise _unsupported("patterns that are not connected to the others (cartesian products)")
 
     rel_vars = {h.rel_var: h for h in hops if h.rel_var}
     seed_preds, seed_var = [], None
@@ -888,7 +909,11 @@ def _compile_chain(clauses, params):
     seed_where = None
     for c in seed_preds:
         seed_where = c if seed_where is None else ("and", seed_where, c)
-    return ChainPlan(seed_var, seed_where, seed_limit, labels, steps, walk, clauses[-1])
+    groups = {}
+    for i, h in enumerate(steps):
+        groups.setdefault(clause_of[next(j for j, x in enumerate(hops) if x is h)], []).append(i)
+    unique = [g for g in groups.values() if len(g) > 1]
+    return ChainPlan(seed_var, seed_where, seed_limit, labels, steps, walk, clauses[-1], unique)
 
 
 def _vars_of(e):

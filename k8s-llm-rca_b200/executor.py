@@ -141,9 +141,11 @@ class QueryRunner:
         return [k for k in range(self.snap.n_kinds) if self._kconst[k].get(prop) == value]
 
     def _project(self, ret, envs, params):
-        """RETURN items over a list of environments (var -> entity), DISTINCT and LIMIT applied."""
+        """RETURN items over a list of environments (var -> entity): DISTINCT, ORDER BY, SKIP and LIMIT applied."""
         keys = [alias or src for (_, alias, src) in ret.items]
-        out, seen = [], set()
+        aliases = {alias: i for i, (_, alias, _) in enumerate(ret.items) if alias}
+        out, seen, sort_keys = [], set(), []
+        stop_at = None if ret.order else (None if ret.limit is None else ret.skip + ret.limit)
         for env in envs:
             vals = tuple(cy.eval_expr(e, env, params) for (e, _, _) in ret.items)
             if ret.distinct:
@@ -153,9 +155,32 @@ class QueryRunner:
                     seen.add(vals)
                 except TypeError:
                     pass
+            if ret.order:                            # ORDER BY sees the variables of the row and the RETURN aliases
+                scope = dict(env)
+                scope.update({a: vals[i] for a, i in aliases.items()})
+                sort_keys.append(tuple(cy.eval_expr(e, scope, params) for (e, _) in ret.order))
             out.append(Record(keys, vals))
-            if ret.limit is not None and len(out) >= ret.limit:
+            if stop_at is not None and len(out) >= stop_at:
                 break
+        if ret.order:
+            def rank(v):                             # Cypher's order across types: values, then null last (ascending)
+                if v is None:
+                    return (9, 0)
+                if isinstance(v, bool):
+                    return (3, v)
+                if isinstance(v, (int, float)):
+                    return (2, v)
+                if isinstance(v, str):
+                    return (1, v)
+                return (0, getattr(v, "id", 0))     # nodes / relationships: by id
+            idx = list(range(len(out)))
+            for j in range(len(ret.order) - 1, -1, -1):          # stable sorts, last key first
+                idx.sort(key=lambda i: rank(sort_keys[i][j]), reverse=ret.order[j][1])
+            out = [out[i] for i in idx]
+        if ret.skip:
+            out = out[ret.skip:]
+        if ret.limit is not None:
+            out = out[:ret.limit]
         return out
 
     # -- S1 / S6
@@ -310,6 +335,10 @@ class QueryRunner:
         if not all_rows:
             return []
         rows = np.concatenate(all_rows) if len(all_rows) > 1 else all_rows[0]
+        for g in plan.unique:                       # no relationship is bound twice within one MATCH clause
+            for x in range(len(g)):
+                for y in range(x + 1, len(g)):
+                    rows = rows[rows[:, L + 1 + g[x]] != rows[:, L + 1 + g[y]]]
 
         def envs():
             for r in rows.tolist():

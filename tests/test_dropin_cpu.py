@@ -165,3 +165,49 @@ def test_executor_uri_resolution():
     meta = executor.resolve_snapshot("synth://?objects=200&events=20&seed=5#metagraph")
     assert snap.n_nodes > 200 and meta.n_nodes == sum(1 for k in snap.kinds if not k.is_state)
     assert executor.resolve_snapshot("synth://?objects=200&events=20&seed=5") is snap
+
+
+def test_llm_style_variants_of_the_instance_query(snap_small):
+    """Statements an LLM may write instead of the generated template: comma-separated
+    patterns in one MATCH, several hops in one pattern, ORDER BY / SKIP / LIMIT - same rows as the template
+    form, and Cypher's rule that one MATCH clause binds no relationship twice."""
+    snap = snap_small
+    sx = oracle_executor(snap)
+    msg = snap.props.msgs[3]
+    template = f"""MATCH (evt:EVENT) WHERE evt.message CONTAINS {msg!r} WITH evt LIMIT 1
+        MATCH (event:Event)-[r1:HasEvent]->(evt) WHERE r1.key = 'metadata_uid'
+        MATCH (event)-[r2:ReferInternal]->(pod:Pod) WHERE r2.key = 'involvedObject_uid'
+        RETURN event, r1, evt, r2, pod"""
+    comma = f"""MATCH (evt:EVENT) WHERE evt.message CONTAINS {msg!r} WITH evt LIMIT 1
+        MATCH (event:Event)-[r1:HasEvent {{key:'metadata_uid'}}]->(evt), (event)-[r2:ReferInternal {{key:'involvedObject_uid'}}]->(pod:Pod)
+        RETURN event, r1, evt, r2, pod"""
+    one_path = f"""MATCH (evt:EVENT) WHERE evt.message CONTAINS {msg!r} WITH evt LIMIT 1
+        MATCH (evt)<-[r1:HasEvent]-(event:Event)-[r2:ReferInternal]->(pod:Pod)
+        WHERE r1.key = 'metadata_uid' AND r2.key = 'involvedObject_uid'
+        RETURN event, r1, evt, r2, pod"""
+    want = [tuple(x.id for x in r) for r in sx.run_query(template)]
+    assert want
+    for q in (comma, one_path):
+        assert [tuple(x.id for x in r) for r in sx.run_query(q)] == want
+    # one MATCH clause never binds a relationship twice: pods that share a ConfigMap, the pod itself excluded
+    pod = want[0][4]
+    from k8s_llm_rca_b200.props import node_uuid
+    share = ("MATCH (p1:Pod)-[r1:ReferInternal {key:'spec_volumes_configMap_name'}]->(cm:ConfigMap)"
+             "<-[r2:ReferInternal {key:'spec_volumes_configMap_name'}]-(p2:Pod) "
+             f"WHERE p1.id = '{node_uuid(pod)}' RETURN p1, r1, cm, r2, p2")
+    rows = [tuple(x.id for x in r) for r in sx.run_query(share)]
+    assert all(r[1] != r[3] for r in rows)
+    two = ("MATCH (p1:Pod)-[r1:ReferInternal {key:'spec_volumes_configMap_name'}]->(cm:ConfigMap) "
+           f"WHERE p1.id = '{node_uuid(pod)}' "
+           "MATCH (cm)<-[r2:ReferInternal {key:'spec_volumes_configMap_name'}]-(p2:Pod) RETURN p1, r1, cm, r2, p2")
+    rows2 = [tuple(x.id for x in r) for r in sx.run_query(two)]         # two clauses: the relationship may be reused
+    assert sorted(rows) == sorted(r for r in rows2 if r[1] != r[3])
+    if rows2:
+        assert any(r[1] == r[3] for r in rows2)
+    # ORDER BY / SKIP / LIMIT
+    q = "MATCH (n:Node) RETURN n.name2 AS name, n ORDER BY name DESC"
+    names = [r["name"] for r in sx.run_query(q)]
+    assert names == sorted(names, reverse=True) and len(names) == len(snap.nodes_of_kind(snap.kind_index("Node")))
+    assert [r["name"] for r in sx.run_query(q + " SKIP 1 LIMIT 2")] == names[1:3]
+    ids = [r["n"].id for r in sx.run_query("MATCH (n:Node) RETURN n ORDER BY n.id DESC LIMIT 3")]
+    assert ids == sorted(snap.nodes_of_kind(snap.kind_index("Node")).tolist(), reverse=True)[:3]
