@@ -724,6 +724,30 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.st_head = e->st_head; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         const long long first = std::max<long long>(1, (b.n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
+        // count-only plan whose last level is one unit step that emits: level L-1 takes that step while it counts
+        // (rca_kernels.cuh: LevelParams::la_n) - no partial path of level L-1 is stored, level L is not launched
+        // does sub-launch j of level lv run through count_unit / fill_unit ?
+        auto takes_unit = [&](int lv, int j) {
+            return !pp.fused && pp.level_typed[lv] && e->unit_steps && pp.mode == kModeSimple && lv >= 2 && lv <= 6 &&
+                   (pp.subs[lv][j].d ? e->unit_in_base : e->unit_out_base)[pp.subs[lv][j].t] >= 0;
+        };
+        bool merged_last = !pp.fused && pl->count_only && e->unit_steps && pp.mode == kModeSimple && L >= 2 &&
+                           pp.level_typed[L] && pp.subs[L].size() == 1 && (pp.subs[L][0].fl & 2) &&
+                           (pp.subs[L][0].d ? e->unit_in_base : e->unit_out_base)[pp.subs[L][0].t] >= 0;
+        if (merged_last && pp.level_typed[L - 1])     // ... unless level L-1 is itself a unit step (no fan-out to save on)
+            for (size_t j = 0; j < pp.subs[L - 1].size(); j++) merged_last &= !takes_unit(L - 1, (int)j);
+        if (merged_last && s == L) {
+            if (ev_lv) CK(cudaEventRecord(ev_lv[s], e->stream));
+            continue;
+        }
+        if (merged_last && s == L - 1) {
+            const Sub &u = pp.subs[L][0];
+            const int rowk = u.d ? e->et_dst[u.t] : e->et_src[u.t];
+            p.la_n = 1;
+            p.la_lo = e->kind_start[rowk];
+            p.la_hi = e->kind_start[rowk + 1];
+            p.la_next = e->unit_next + (u.d ? e->unit_in_base : e->unit_out_base)[u.t];
+        }
         if (pp.fused) {
             const KernelSet ks = dir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
             int grid = max_grid(e, ks.fused, dyn);
@@ -750,8 +774,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 p.sub = j;
                 KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
                 size_t dyn_c = dyn, dyn_f = dyn;
-                if (pp.level_typed[s] && e->unit_steps && pp.mode == kModeSimple && s >= 2 && s <= 6 &&
-                    (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t] >= 0) {
+                if (takes_unit(s, j)) {
                     ks = pick_unit_kernels(s - 1);
                     p.unit_next = e->unit_next + (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t];
                     p.unit_fl = pp.subs[s][j].fl;
@@ -764,7 +787,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 if (s == 1) grid = (int)std::min<long long>(grid, first);
                 ks.count<<<grid, kThreads, dyn_c, e->stream>>>(p);
                 scan_groups<<<1, 1024, 0, e->stream>>>(p);
-                if (pl->count_only && s == L) {       // nothing continues after the last level and no row is stored
+                if (pl->count_only && (s == L || p.la_n)) {   // nothing is stored: no row, and no path a later level would read
                     *launches += 2;
                     continue;
                 }

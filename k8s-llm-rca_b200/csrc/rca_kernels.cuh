@@ -151,6 +151,11 @@ struct LevelParams {
     int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row
     int unit_aux;                     // kind | intermediate-kind flag << 16 of the far kind
     const int2 *unit_next;            // per node of the near kind: its one (neighbour, relationship), or (-1, -1)
+    // count-only plans whose LAST level is one unit step: the level before it takes that step while it counts
+    // (count_level only: nothing is stored, so neither its own fill nor the last level is launched)
+    int la_n;
+    int la_lo, la_hi;                 // node-id range of the last step's near kind
+    const int2 *la_next;              // its next-hop table
     // HasState intervals
     const StHead *st_head;            // [n_head]: nodes at or above n_head have no intervals
     int n_head;
@@ -549,13 +554,14 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
     if (qn) flush_rows<(QT >= 0 && QT <= 3) ? QT + 1 : -1>(p, w, qn, ob_s, run_e);
 }
 
-// Walk the tile's windows and count the survivors.
+// Walk the tile's windows and count the survivors.  With p.la_n (see LevelParams) every path that continues also
+// takes the plan's last step - one load from a next-hop table - and c2 / s2 count the rows and the entries looked at.
 template <bool ADJ2, int MODE, int QT>
 __device__ __forceinline__ void tile_count(const LevelParams &p, const Tables &T, const Warp &w, int C, int &cf,
-                                           int &ce) {
+                                           int &ce, int &c2, int &s2) {
     const int n_it = (C + 31) >> 5;
     int jlo = 0;
-    cf = 0; ce = 0;
+    cf = 0; ce = 0; c2 = 0; s2 = 0;
     for (int it = 0; it < n_it; ++it) {
         const int o = window_owner(*w.W, it, jlo, w.lane);
         const Cand x = fetch_cand<ADJ2, MODE>(p, w, o, (it << 5) + w.lane, C);
@@ -563,6 +569,21 @@ __device__ __forceinline__ void tile_count(const LevelParams &p, const Tables &T
         const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + w.lane, C, x, v, r, na);
         cf += __popc(__ballot_sync(0xffffffffu, fl & 1));
         ce += __popc(__ballot_sync(0xffffffffu, fl & 2));
+        if (MODE == kModeSimple && p.la_n) {
+            int2 nx = make_int2(-1, -1);
+            if ((fl & 1) && v >= p.la_lo && v < p.la_hi) nx = __ldg(p.la_next + (v - p.la_lo));
+            bool ok = nx.x >= 0 && nx.x != v && (!p.need_inter || (na >> 16));
+            if (ok) {
+                if (QT >= 0) {
+#pragma unroll
+                    for (int d = 0; d <= QT; d++) ok &= (w.anc_n[d * kTile + o] != nx.x);
+                } else {
+                    for (int d = 0; d < p.s; d++) ok &= (w.anc_n[d * kTile + o] != nx.x);
+                }
+            }
+            s2 += __popc(__ballot_sync(0xffffffffu, nx.x >= 0));
+            c2 += __popc(__ballot_sync(0xffffffffu, ok));
+        }
     }
 }
 
@@ -621,13 +642,15 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) count_level(const __grid_c
     __shared__ unsigned long long s_fb[kLv];
     if (overflow_seen(p.ctl)) return;
     const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
-    unsigned long long scanned = 0;
+    unsigned long long scanned = 0, rows2 = 0, scanned2 = 0;
     const unsigned nwarps = gridDim.x * kWarps;
     for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
         const int C = tile_prologue<MODE>(p, c.T, c.w, tile, c.Fq, s_fb);
         scanned += (unsigned long long)C;
-        int cf, ce;
-        tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce);
+        int cf, ce, c2, s2;
+        tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce, c2, s2);
+        rows2 += (unsigned long long)c2;
+        scanned2 += (unsigned long long)s2;
         if (c.w.lane == 0) {
             const unsigned long long slot = c.slot0 + tile;
             p.tcount[slot] = make_uint2((unsigned)cf, (unsigned)ce);
@@ -635,7 +658,11 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) count_level(const __grid_c
             if (ce) atomicAdd(&p.gsum[slot / kGroup].y, (unsigned long long)ce);
         }
     }
-    if (c.w.lane == 0 && scanned) atomicAdd(&p.ctl->E[p.s], scanned);
+    if (c.w.lane == 0) {
+        if (scanned) atomicAdd(&p.ctl->E[p.s], scanned);
+        if (rows2) atomicAdd(&p.ctl->N[p.s + 1], rows2);      // the merged last step's rows and entries
+        if (scanned2) atomicAdd(&p.ctl->E[p.s + 1], scanned2);
+    }
 }
 
 // split path, step 2 (one CTA): exclusive scan of the group sums, level totals, overflow check
@@ -688,7 +715,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
         ctl->F[s] = base_f + s_run[0];
         ctl->N[s] = base_n + s_run[1];
         unsigned ov = 0;
-        if (fb_s + base_f + s_run[0] > p.fcap) ov |= 1u;
+        if (!p.la_n && fb_s + base_f + s_run[0] > p.fcap) ov |= 1u;     // la_n: the paths are counted, never stored
         if (!p.count_only && ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (ov) ctl->overflow = ov;
     }
@@ -973,8 +1000,8 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
         if (tile >= c.ntiles) break;
         const int C = tile_prologue<MODE>(p, c.T, c.w, tile, c.Fq, s_fb);
         scanned += (unsigned long long)C;
-        int cf, ce;
-        tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce);
+        int cf, ce, c2, s2;
+        tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce, c2, s2);
         unsigned long long run_f, run_e;
         tile_lookback(tstate, tile, p.epoch, (unsigned long long)cf, (unsigned long long)ce, run_f, run_e);
         if (run_f + cf > 0xffffffffull) ov |= 1u;     // the 32-bit count field of the state word

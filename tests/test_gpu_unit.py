@@ -135,3 +135,24 @@ def test_chain_line_same_bytes_as_chain_walk(snap_10k, csr_oracle_lib):
         cnt = e.expand(engine.chain_plan(ets, dirs, count_only=True), seeds)
         assert cnt.emitted == na
     e.close()
+
+
+def test_count_only_last_unit_step_taken_by_the_level_before(eng, snap_small):
+    """Count-only plans whose last level is one unit step never store the level before it: that level's count
+    pass takes the last step itself.  Every counter must equal those of the general kernels (unit steps off)."""
+    from k8s_llm_rca_b200 import engine
+    excl = [snap_small.kind_index("Event"), snap_small.kind_index("Namespace")]
+    nonzero = 0
+    for direction in ("und", "out", "in"):
+        for src in ENTITY_KINDS:
+            seeds = snap_small.nodes_of_kind(snap_small.kind_index(src))
+            for dst in ENTITY_KINDS:
+                for hops in (2, 3, 4, 5):
+                    for inter in ([], [snap_small.kind_index("ReplicaSet"), snap_small.kind_index("PersistentVolume")]):
+                        plan = engine.varlen_plan(direction, hops, dest_kind=snap_small.kind_index(dst), excl_kinds=excl,
+                                                  inter_kinds=inter, entity_only=True, count_only=True)
+                        (on, _), (off, _) = _both(eng, plan, seeds)
+                        tag = (direction, src, dst, hops, inter)
+                        assert on.emitted == off.emitted and on.scanned == off.scanned and on.frontier == off.frontier, tag
+                        nonzero += on.emitted[hops] > 0
+    assert nonzero >= 20
