@@ -214,9 +214,11 @@ int rca_text_match_pairs(rca_engine_t *e, const uint8_t *needle_bytes, const int
  *   rca_peer_handle   allocate this engine's array, return its handle (RCA_PEER_HANDLE_BYTES bytes)
  *   rca_peer_connect  map the arrays of all ranks (handles in rank order, this rank's own included)
  *   rca_peer_allgather publish `value`; out_values != NULL: wait and return all `world` values (rank
- *                     order); NULL: only enqueue, the result is collected by rca_peer_wait.  Collective:
- *                     every rank calls it the same number of times.  A peer that does not show up within
- *                     two seconds makes the call fail instead of hanging the GPU. */
+ *                     order).  NULL: only enqueue - the value is published and the PREVIOUS exchange is
+ *                     waited for on the device, so the ranks stay within one exchange of each other without
+ *                     waiting for the slowest one at every step; rca_peer_wait collects the last exchange.
+ *                     Collective: every rank calls it the same number of times.  A peer that does not show
+ *                     up within two seconds makes the call fail instead of hanging the GPU. */
 #define RCA_PEER_HANDLE_BYTES 64
 int rca_peer_handle(rca_engine_t *e, int32_t world, uint8_t *out_handle);
 int rca_peer_connect(rca_engine_t *e, int32_t rank, const uint8_t *handles);

@@ -126,6 +126,7 @@ struct rca_engine {
     long long *peer_out = nullptr, *peer_out_h = nullptr;   // [world] device / pinned
     unsigned *peer_err = nullptr;
     unsigned long long peer_seq = 0;
+    bool peer_collected = true;           // peer_out holds the values of exchange peer_seq
     // results of the last submission (one per plan) and the one the accessors address
     std::vector<PlanResult> results;
     int selected = 0;
@@ -1289,8 +1290,8 @@ extern "C" int rca_peer_handle(rca_engine_t *e, int32_t world, uint8_t *out_hand
     if (world < 1 || world > 8 || !out_handle) return fail(e, RCA_ERR_ARG, "rca_peer_handle: world %d not in 1..8, or null handle", world);
     if (e->peer_own) return fail(e, RCA_ERR_ARG, "rca_peer_handle: already called on this engine");
     CK(cudaSetDevice(e->device));
-    CK(cudaMalloc((void **)&e->peer_own, 2 * (size_t)world * sizeof(PeerSlot)));
-    CK(cudaMemset(e->peer_own, 0, 2 * (size_t)world * sizeof(PeerSlot)));
+    CK(cudaMalloc((void **)&e->peer_own, kPeerBuffers * (size_t)world * sizeof(PeerSlot)));
+    CK(cudaMemset(e->peer_own, 0, kPeerBuffers * (size_t)world * sizeof(PeerSlot)));
     CK(cudaMalloc((void **)&e->peer_out, (size_t)world * sizeof(long long)));
     CK(cudaMalloc((void **)&e->peer_err, sizeof(unsigned)));
     CK(cudaMemset(e->peer_err, 0, sizeof(unsigned)));
@@ -1320,19 +1321,30 @@ extern "C" int rca_peer_connect(rca_engine_t *e, int32_t rank, const uint8_t *ha
     return RCA_OK;
 }
 
+static int peer_launch(rca_engine *e, unsigned long long seq, int publish, int deferred, long long value) {
+    PeerParams p;
+    std::memset(&p, 0, sizeof p);
+    for (int r = 0; r < e->peer_world; r++) {
+        p.slots[r] = e->peer_slots[r] + (seq % kPeerBuffers) * (size_t)e->peer_world;
+        p.prev[r] = e->peer_slots[r] + ((seq + kPeerBuffers - 1) % kPeerBuffers) * (size_t)e->peer_world;
+    }
+    p.rank = e->peer_rank; p.world = e->peer_world; p.seq = seq;
+    p.publish = publish; p.deferred = deferred; p.host_value = value;
+    p.out = e->peer_out; p.err = e->peer_err;
+    peer_exchange<<<1, 32, 0, e->stream>>>(p);
+    CK(cudaGetLastError());
+    return RCA_OK;
+}
+
 extern "C" int rca_peer_allgather(rca_engine_t *e, int64_t value, int64_t *out_values) {
     if (!e) return RCA_ERR_ARG;
     if (e->peer_rank < 0) return fail(e, RCA_ERR_ARG, "rca_peer_allgather: not connected (rca_peer_handle, rca_peer_connect)");
     CK(cudaSetDevice(e->device));
-    PeerParams p;
-    std::memset(&p, 0, sizeof p);
-    const unsigned long long seq = ++e->peer_seq;
-    for (int r = 0; r < e->peer_world; r++) p.slots[r] = e->peer_slots[r] + (seq & 1) * (size_t)e->peer_world;
-    p.rank = e->peer_rank; p.world = e->peer_world; p.seq = seq;
-    p.dev_value = nullptr; p.host_value = value;
-    p.out = e->peer_out; p.err = e->peer_err;
-    peer_exchange<<<1, 32, 0, e->stream>>>(p);
-    CK(cudaGetLastError());
+    // with a buffer for the result the exchange is complete when the call returns; without one the value is only
+    // published (and the PREVIOUS exchange collected): the ranks stay within one exchange of each other
+    int rc = peer_launch(e, ++e->peer_seq, 1, out_values ? 0 : 1, value);
+    if (rc) return rc;
+    e->peer_collected = out_values != nullptr;
     if (out_values) return rca_peer_wait(e, out_values);
     return RCA_OK;
 }
@@ -1341,6 +1353,11 @@ extern "C" int rca_peer_wait(rca_engine_t *e, int64_t *out_values) {
     if (!e) return RCA_ERR_ARG;
     if (e->peer_rank < 0 || !out_values) return fail(e, RCA_ERR_ARG, "rca_peer_wait: not connected, or null buffer");
     CK(cudaSetDevice(e->device));
+    if (!e->peer_collected && e->peer_seq) {          // the last exchange was only published: collect it now
+        int rc = peer_launch(e, e->peer_seq, 0, 0, 0);
+        if (rc) return rc;
+        e->peer_collected = true;
+    }
     CK(cudaMemcpyAsync(e->peer_out_h, e->peer_out, (size_t)e->peer_world * sizeof(long long), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(e->peer_out_h + e->peer_world, e->peer_err, sizeof(unsigned), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));

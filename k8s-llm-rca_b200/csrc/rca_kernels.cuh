@@ -1512,39 +1512,48 @@ __global__ void __launch_bounds__(256) match_pairs(const __grid_constant__ PairP
 //  - done by the ranks themselves over NVLink / NVSwitch peer memory.  Every engine
 // owns an array of `world` slots {value, seq}; rank r's thread t stores its value, then the sequence
 // number, into slot r of rank t's array (a plain remote store and a release store), and then waits
-// until slot t of its OWN array carries the same sequence number.  One launch of `world` threads, no
-// host involvement, no NCCL call on the step's critical path; the wait gives up after about two
-// seconds and raises *err instead of hanging the GPU.
+// until slot t of its OWN array carries the same sequence number (or, deferred, the previous one).  One launch
+// of `world` threads, no host involvement, no NCCL call on the step's critical path; the wait gives up after
+// about two seconds and raises *err instead of hanging the GPU.
 struct PeerSlot {
     long long value;
     unsigned long long seq;
 };
 struct PeerParams {
-    PeerSlot *slots[8];               // slots[t]: rank t's array of this exchange's parity (own array at index rank);
-                                      // two arrays alternate, so a fast rank's next value cannot land before a slow
-                                      // rank has read this one (it cannot be two exchanges ahead: it waits for everyone)
+    PeerSlot *slots[8];               // slots[t]: rank t's array of this exchange's buffer (own array at index rank)
+    PeerSlot *prev[8];                // ... and of the previous exchange's buffer (deferred mode)
     int rank, world;
     unsigned long long seq;           // this exchange's number (1, 2, ...; the same on every rank)
-    const unsigned long long *dev_value;   // value to publish, read on the device ...
-    long long host_value;             // ... or given by the host (dev_value null)
-    long long *out;                   // [world] the values of all ranks, rank order (device memory of this rank)
+    int publish;                      // 0: only wait for / collect exchange `seq` (rca_peer_wait)
+    int deferred;                     // 1: publish `seq`, but wait for and collect exchange seq-1: the ranks are then
+                                      //    coupled one step apart instead of step by step (no per-step wait for the
+                                      //    slowest rank); the last exchange is collected by rca_peer_wait
+    long long host_value;             // value to publish
+    long long *out;                   // [world] the collected values, rank order (device memory of this rank)
     unsigned *err;
 };
+// Four buffers rotate (seq & 3).  A rank can run ahead of another by at most one finished exchange plus the one in
+// flight; with the deferred wait that is three buffers in use at once, so the fourth write never lands on values a
+// slow rank has yet to read.
+constexpr int kPeerBuffers = 4;
 
 __global__ void peer_exchange(const __grid_constant__ PeerParams p) {
     const int t = threadIdx.x;
     if (t >= p.world) return;
-    const long long mine = p.dev_value ? (long long)*p.dev_value : p.host_value;
-    PeerSlot *dst = p.slots[t] + p.rank;
-    dst->value = mine;
-    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&dst->seq), "l"(p.seq) : "memory");
-    const PeerSlot *src = p.slots[p.rank] + t;
+    if (p.publish) {
+        PeerSlot *dst = p.slots[t] + p.rank;
+        dst->value = p.host_value;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&dst->seq), "l"(p.seq) : "memory");
+    }
+    const unsigned long long want = p.deferred ? p.seq - 1 : p.seq;
+    if (want == 0) { p.out[t] = 0; return; }
+    const PeerSlot *src = (p.deferred ? p.prev[p.rank] : p.slots[p.rank]) + t;
     unsigned long long t0 = 0, now = 0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     while (true) {
         unsigned long long s;
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(s) : "l"(&src->seq) : "memory");
-        if (s >= p.seq) break;
+        if (s >= want) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
         if (now - t0 > 2000000000ull) { atomicOr(p.err, 1u); break; }
         __nanosleep(200);
