@@ -402,3 +402,34 @@ def test_message_filter_pairs(snap_10k):
     with pytest.raises(ValueError):
         eng.match_pairs([0], ["a"], ["b"])                  # node 0 is a Pod: it has no message
     eng.close()
+
+
+def test_expand_many_with_more_side_plans_than_one_batch(snap_10k):
+    """Thirteen one-launch chains (two chain_batch launches), a count-only one among them, around two
+    variable-length plans: every plan's rows and counters equal those of a call of its own."""
+    from k8s_llm_rca_b200 import engine, workloads
+    w = workloads.Config3(snap=snap_10k)
+    eng = engine.Engine(snap_10k)
+    pods, ev, ts = w.batch(0)
+    chains = [c[2] for c in w.chains.values()]
+    ets0, dirs0, _ = next(iter(w.chains.values()))
+    cnt = engine.chain_plan(ets0, dirs0, count_only=True)
+    short = engine.varlen_plan("und", 2, dest_kind=snap_10k.kind_index("Node"), excl_kinds=w.excl, entity_only=True)
+    plans = chains[:3] + [w.varlen] + chains + [cnt] + chains[1:5] + [short]
+    seeds = [pods if p.kind == engine.PLAN_VARLEN else ev for p in plans]
+    # different seed subsets per plan, so that a mix-up of plans cannot go unnoticed
+    seeds = [s[k % 3::3] if k % 2 else s for k, s in enumerate(seeds)]
+    tss = [ts[k % 3::3] if k % 2 else ts for k in range(len(plans))]
+    tss = [t if p.with_states else None for p, t in zip(plans, tss)]
+    many = eng.expand_many(plans, seeds, tss)
+    kept = [(r.emitted, r.frontier, r.scanned, None if r.count_only else r.all_rows()) for r in many]
+    for k, (p, s, t) in enumerate(zip(plans, seeds, tss)):
+        r = eng.expand(p, s, t)
+        em, fr, sc, rows = kept[k]
+        assert r.emitted == em and r.frontier == fr and r.scanned == sc, k
+        if rows is not None:
+            one = r.all_rows()
+            assert one.keys() == rows.keys()
+            for lvl in rows:
+                assert np.array_equal(one[lvl], rows[lvl]), (k, lvl)
+    eng.close()
