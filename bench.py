@@ -169,6 +169,16 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU path (use --impl reference)")
     torch.cuda.set_device(local_rank)
+    if world > 1 and os.environ.get("RCA_BENCH_PIN", "1") == "1":
+        # one process per GPU shares the host with the others: keep each rank on its own pair of cores, so that the
+        # host side of a step (about 0.15 ms of launches per 0.5 ms step) is not migrated or preempted by a neighbour
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = len(cores) // world
+            if per >= 1:
+                os.sched_setaffinity(0, set(cores[local_rank * per:(local_rank + 1) * per]))
+        except (AttributeError, OSError):
+            pass
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
