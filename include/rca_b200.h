@@ -168,6 +168,15 @@ int rca_result_level(const rca_engine_t *e, int level, const int32_t **dev_rows,
                      int32_t *row_len);
 /* replaces records = list(result), neo4j_query_executor.py:21: copy one level's rows to the host */
 int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows);
+/* Overlapping the copy-out with the next submission (no counterpart in the reference, whose driver hands over
+ * materialised records).  rca_set_double_buffer(e, 1): submissions alternate between two output arenas.
+ * rca_result_copy_async: like rca_result_copy, but only enqueues the copy (host_rows should be pinned) on a
+ * copy stream of the engine and returns; the rows keep travelling while the NEXT rca_expand / rca_expand_many
+ * runs (it writes the other arena; a submission waits, on the device, for copies that still read the arena it
+ * is about to reuse).  rca_result_wait: all enqueued copies have arrived. */
+int rca_set_double_buffer(rca_engine_t *e, int on);
+int rca_result_copy_async(rca_engine_t *e, int level, int32_t *host_rows);
+int rca_result_wait(rca_engine_t *e);
 
 /* replaces the per-node state query of check_states_of_entity, analyze_root_cause.py:173-176:
  * for i < n: STATE nodes of entity nodes[i] whose interval holds ts[i].  out_first[i] = lowest

@@ -76,6 +76,15 @@ struct rca_engine {
     unsigned long long fcap = 0;
     int *out = nullptr;
     unsigned long long ocap = 0;
+    // double buffering of the output arena (rca_set_double_buffer): every submission takes the other arena, so
+    // the rows of the previous one can still be travelling to the host (rca_result_copy_async) while it runs
+    bool double_buffer = false;
+    int *out_alt = nullptr;
+    unsigned long long ocap_alt = 0;
+    int arena = 0;                        // which of the two is `out`
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr};   // last asynchronous copy out of arena 0 / 1
+    bool copies_pending[2] = {false, false};
     ulonglong2 *tstate = nullptr;         // fused path: tile-state words, tagged with `epoch`; zeroed when (re)allocated
     unsigned long long tcap = 0;
     unsigned epoch = 0;
@@ -309,6 +318,9 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->h_ptab) cudaFreeHost(e->h_ptab);
     if (e->mh_ptab) cudaFreeHost(e->mh_ptab);
     if (e->mh_ctl) cudaFreeHost(e->mh_ctl);
+    if (e->copy_stream) { cudaStreamSynchronize(e->copy_stream); cudaStreamDestroy(e->copy_stream); }
+    for (auto ev : e->ev_copied) if (ev) cudaEventDestroy(ev);
+    if (e->out_alt) cudaFree(e->out_alt);
     for (int r = 0; r < e->peer_world; r++)
         if (r != e->peer_rank && e->peer_slots[r]) cudaIpcCloseMemHandle(e->peer_slots[r]);
     if (e->peer_own) cudaFree(e->peer_own);
@@ -887,6 +899,32 @@ static int stage_seeds(rca_engine *e, const int32_t *seeds, const int64_t *seed_
     return RCA_OK;
 }
 
+// With double buffering on, a submission writes into the arena the previous one did not use, after the
+// asynchronous copies that still read that arena (issued two submissions ago) are through.
+static int begin_submission(rca_engine *e) {
+    if (!e->double_buffer) return RCA_OK;
+    std::swap(e->out, e->out_alt);
+    std::swap(e->ocap, e->ocap_alt);
+    e->arena ^= 1;
+    if (e->copies_pending[e->arena]) {
+        CK(cudaStreamWaitEvent(e->stream, e->ev_copied[e->arena], 0));
+        e->copies_pending[e->arena] = false;
+    }
+    return RCA_OK;
+}
+
+extern "C" int rca_set_double_buffer(rca_engine_t *e, int on) {
+    if (!e) return RCA_ERR_ARG;
+    CK(cudaSetDevice(e->device));
+    if (on && !e->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        for (auto &ev : e->ev_copied) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    }
+    if (!on && e->copy_stream) CK(cudaStreamSynchronize(e->copy_stream));
+    e->double_buffer = on != 0;
+    return RCA_OK;
+}
+
 extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *seeds, int64_t n_seeds,
                           const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats) {
     if (!e) return RCA_ERR_ARG;
@@ -896,6 +934,8 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     int rc = validate_plan(e, pl);
     if (rc) return rc;
     CK(cudaSetDevice(e->device));
+    rc = begin_submission(e);
+    if (rc) return rc;
     e->results.assign(1, PlanResult());
     e->selected = 0;
     PreparedPlan pp;
@@ -982,7 +1022,8 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
         any_ts |= plans[k].with_states != 0;
     }
     CK(cudaSetDevice(e->device));
-    int rc;
+    int rc = begin_submission(e);
+    if (rc) return rc;
     // per-plan tables and control blocks, host (pinned) and device
     const size_t pt_stride = ((size_t)kPtBytes + 255) & ~(size_t)255;
     if ((size_t)n_plans > e->many_cap) {
@@ -1226,6 +1267,31 @@ extern "C" int rca_result_copy(rca_engine_t *e, int level, int32_t *host_rows) {
     CK(cudaSetDevice(e->device));
     CK(cudaMemcpyAsync(host_rows, e->out + r->base[level], words * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    return RCA_OK;
+}
+
+extern "C" int rca_result_copy_async(rca_engine_t *e, int level, int32_t *host_rows) {
+    if (!e || level < 0 || level > RCA_MAX_HOPS) return RCA_ERR_ARG;
+    if (!e->double_buffer) return fail(e, RCA_ERR_ARG, "rca_result_copy_async: switch double buffering on first (rca_set_double_buffer)");
+    const PlanResult *r = current_result(e);
+    if (!r) return fail(e, RCA_ERR_ARG, "rca_result_copy_async: no result held (call rca_expand first)");
+    const size_t words = (size_t)r->rows[level] * (size_t)r->row_len[level];
+    if (!words) return RCA_OK;
+    if (!host_rows) return fail(e, RCA_ERR_ARG, "rca_result_copy_async: null buffer");
+    CK(cudaSetDevice(e->device));
+    // the submission that produced the rows ended with a synchronisation: the copy stream may start at once
+    CK(cudaMemcpyAsync(host_rows, e->out + r->base[level], words * sizeof(int), cudaMemcpyDeviceToHost, e->copy_stream));
+    CK(cudaEventRecord(e->ev_copied[e->arena], e->copy_stream));
+    e->copies_pending[e->arena] = true;
+    return RCA_OK;
+}
+
+extern "C" int rca_result_wait(rca_engine_t *e) {
+    if (!e) return RCA_ERR_ARG;
+    if (!e->copy_stream) return RCA_OK;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->copy_stream));
+    e->copies_pending[0] = e->copies_pending[1] = false;
     return RCA_OK;
 }
 

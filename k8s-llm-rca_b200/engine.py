@@ -23,7 +23,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold",
            "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_graph_bytes", "rca_reserve",
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
-           "rca_result_level", "rca_result_copy", "rca_state_lookup", "rca_state_window", "rca_text_load",
+           "rca_result_level", "rca_result_copy", "rca_set_double_buffer", "rca_result_copy_async", "rca_result_wait", "rca_state_lookup", "rca_state_window", "rca_text_load",
            "rca_text_contains", "rca_text_match_pairs", "rca_peer_handle", "rca_peer_connect", "rca_peer_allgather",
            "rca_peer_wait", "rca_version")
 
@@ -105,6 +105,9 @@ def load_library(path: str | None = None):
     lib.rca_state_window.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
     lib.rca_text_load.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    lib.rca_set_double_buffer.argtypes = [C.c_void_p, C.c_int]
+    lib.rca_result_copy_async.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    lib.rca_result_wait.argtypes = [C.c_void_p]
     lib.rca_peer_handle.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
     lib.rca_peer_connect.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
     lib.rca_peer_allgather.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
@@ -218,6 +221,20 @@ class ExpandResult:
             self.engine._ck(self.engine.lib.rca_result_copy(self.engine.h, level, out.ctypes.data))
         return out
 
+    def rows_async(self, level: int, out: np.ndarray) -> np.ndarray:
+        """Enqueue the copy of one level's rows into `out` (pinned int32 memory) and return at once; the data is
+        there after engine.result_wait().  Needs engine.set_double_buffer(True): the next expand() then runs
+        while these rows are still travelling."""
+        assert self._gen == self.engine._gen, "result was overwritten by a later expand()"
+        n, w = self.emitted[level], self.row_len[level]
+        flat = out.reshape(-1)
+        assert flat.dtype == np.int32 and flat.size >= n * w and flat.flags.c_contiguous
+        view = flat[:n * w].reshape(n, w)
+        if n:
+            self.engine._ck(self.engine.lib.rca_result_select(self.engine.h, self.index))
+            self.engine._ck(self.engine.lib.rca_result_copy_async(self.engine.h, level, view.ctypes.data))
+        return view
+
     def all_rows(self) -> dict:
         return {s: self.rows(s) for s in range(self.levels + 1) if self.emitted[s]}
 
@@ -296,6 +313,15 @@ class Engine:
     def set_unit_steps(self, on: bool):
         """Typed steps with at most one candidate per path run through the one-lane-per-path kernels (default on)."""
         self._ck(self.lib.rca_set_unit_steps(self.h, 1 if on else 0))
+
+    def set_double_buffer(self, on: bool):
+        """Submissions alternate between two output arenas, so ExpandResult.rows_async() copies can overlap the
+        next submission (include/rca_b200.h)."""
+        self._ck(self.lib.rca_set_double_buffer(self.h, 1 if on else 0))
+
+    def result_wait(self):
+        """All rows_async() copies have arrived."""
+        self._ck(self.lib.rca_result_wait(self.h))
 
     def graph_bytes(self) -> int:
         """Device memory the snapshot occupies on this engine's GPU."""

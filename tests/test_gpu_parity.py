@@ -433,3 +433,39 @@ def test_expand_many_with_more_side_plans_than_one_batch(snap_10k):
             for lvl in rows:
                 assert np.array_equal(one[lvl], rows[lvl]), (k, lvl)
     eng.close()
+
+
+def test_double_buffered_async_copy_out(snap_10k):
+    """rca_set_double_buffer + rca_result_copy_async: rows keep travelling to the host while the next submissions
+    run; a later submission never overwrites rows that are still being copied."""
+    import torch
+    from k8s_llm_rca_b200 import engine
+    node, ev, ns, pod = _kinds(snap_10k, "Node", "Event", "Namespace", "Pod")
+    plan = engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    pods = snap_10k.nodes_of_kind(pod)
+    parts = [pods[k::4] for k in range(4)]
+    ref_eng = engine.Engine(snap_10k)
+    want = [ref_eng.expand(plan, p).rows(3).copy() for p in parts]
+    ref_eng.close()
+    eng = engine.Engine(snap_10k)
+    with pytest.raises(engine.RcaError):
+        eng.expand(plan, parts[0]).rows_async(3, np.empty((len(want[0]), 7), np.int32))      # not switched on yet
+    eng.set_double_buffer(True)
+    bufs = [torch.empty(max(len(w) for w in want) * 7, dtype=torch.int32).pin_memory().numpy() for _ in range(4)]
+    views = []
+    for rnd in range(3):                                  # arenas alternate: every arena is reused several times
+        views.clear()
+        for k, p in enumerate(parts):
+            r = eng.expand(plan, p)
+            views.append(r.rows_async(3, bufs[k]))       # enqueue, do not wait: the next expand() runs meanwhile
+        eng.result_wait()
+        for k in range(4):
+            assert np.array_equal(views[k], want[k]), (rnd, k)
+    # the synchronous copy still works with double buffering on, and device pointers of the last TWO results differ
+    r1 = eng.expand(plan, parts[0])
+    p1 = r1.device_rows(3)[0]
+    r2 = eng.expand(plan, parts[1])
+    assert np.array_equal(r2.rows(3), want[1]) and r2.device_rows(3)[0] != p1
+    eng.set_double_buffer(False)
+    assert np.array_equal(eng.expand(plan, parts[2]).rows(3), want[2])
+    eng.close()
