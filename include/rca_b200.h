@@ -149,7 +149,9 @@ int rca_reserve(rca_engine_t *e, int64_t frontier_entries, int64_t output_words)
 /* replaces session.run(query, parameters) for the path-producing statements,
  * neo4j_query_executor.py:16-21.  seeds: node ids (host or device memory, seeds_on_device says
  * which); seed_ts: one timestamp (ms) per seed, needed only with plan->with_states.
- * Results stay in the engine until the next rca_expand / rca_close on it. */
+ * Results stay in the engine until the next rca_expand / rca_close on it.
+ * Device seed buffers (seeds_on_device = 1) are read on the engine's stream, which is not ordered against the
+ * stream that wrote them: give the engine that stream (rca_set_stream) or finish the writes first. */
 int rca_expand(rca_engine_t *e, const rca_plan_t *plan, const int32_t *seeds, int64_t n_seeds,
                const int64_t *seed_ts, int seeds_on_device, rca_stats_t *stats);
 /* Several plans in one submission (no counterpart in the reference, which sends one statement at a
@@ -190,6 +192,12 @@ int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int64_t *ts, i
 int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt, int64_t n,
                      int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
 
+/* The same with the label of the state node applied: `(n2:KIND)` of analyze_root_cause.py:72 - only STATE nodes
+ * of kind `state_kind` are counted and returned (-1 = any kind), so the cut at RCA_STATE_LIMIT falls after the
+ * label test, as the reference's `RETURN n2 LIMIT 10` does (analyze_root_cause.py:76-77). */
+int rca_state_window_kind(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt, int64_t n,
+                          int on_device, int32_t state_kind, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids);
+
 /* Message arena for rca_text_contains: n_msgs UTF-8 strings, concatenated in `bytes`, message i =
  * bytes[off[i] .. off[i+1]), belonging to node node_ids[i] (ascending node ids give 'lowest id first'
  * answers).  Copied to the device; replaces nothing in the reference - there the text lives in Neo4j. */
@@ -227,12 +235,17 @@ int rca_text_match_pairs(rca_engine_t *e, const uint8_t *needle_bytes, const int
  *                     waited for on the device, so the ranks stay within one exchange of each other without
  *                     waiting for the slowest one at every step; rca_peer_wait collects the last exchange.
  *                     Collective: every rank calls it the same number of times.  A peer that does not show
- *                     up within two seconds makes the call fail instead of hanging the GPU. */
+ *                     up within the timeout (two seconds unless rca_peer_set_timeout says otherwise) makes the
+ *                     call fail instead of hanging the GPU; the error is reported once and the ranks' exchange
+ *                     counts may then disagree - set the exchange up again (new engines) or stop.
+ *   rca_peer_set_timeout  how long a rank waits for a peer, in milliseconds (first launches, arena growth on
+ *                     one rank and similar skew are legitimate reasons to wait longer than the default) */
 #define RCA_PEER_HANDLE_BYTES 64
 int rca_peer_handle(rca_engine_t *e, int32_t world, uint8_t *out_handle);
 int rca_peer_connect(rca_engine_t *e, int32_t rank, const uint8_t *handles);
 int rca_peer_allgather(rca_engine_t *e, int64_t value, int64_t *out_values);
 int rca_peer_wait(rca_engine_t *e, int64_t *out_values);
+int rca_peer_set_timeout(rca_engine_t *e, int64_t milliseconds);
 
 /* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
  * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory
@@ -244,14 +257,23 @@ int rca_peer_wait(rca_engine_t *e, int64_t *out_values);
 /* No counterpart in the reference.  rca_expand for callers that cannot allocate device memory:
  * a service whose device-memory budget was handed to a pool at start-up, a latency path where
  * cudaMalloc (which may synchronise the whole device) is not allowed, a process under a memory
- * cap.  Same plans, same results and row order as rca_expand at these sizes, but
+ * cap.  Same plans and the same set of rows as rca_expand, but
  *   - it calls no cudaMalloc / cudaFree and no allocating library routine: its scratch is a fixed
  *     array inside the library, limited by the three constants above; a plan that needs more is
  *     refused with RCA_ERR_ARG / RCA_ERR_NOMEM and a message naming the limit - nothing grows;
  *   - seeds, timestamps and rows are the CALLER's DEVICE buffers: dev_seeds[n_seeds],
  *     dev_seed_ts[n_seeds] (only with plan->with_states), dev_rows[rows_capacity_words].  Rows of
  *     length 1 come first, then length 2, ...; stats->emitted[s] and stats->row_len[s] say how
- *     many and how wide, so level s starts at word sum_{j<s} emitted[j] * row_len[j];
+ *     many and how wide, so level s starts at word sum_{j<s} emitted[j] * row_len[j].  Within a
+ *     level the rows are in the order of the single-launch-per-hop kernels, i.e. the order
+ *     rca_expand gives below its fused threshold (rca_set_fused_threshold); above that threshold
+ *     rca_expand may order a level differently - same rows, compare as sets;
+ *   - the kernels run on the ENGINE's stream (its own non-blocking stream unless rca_set_stream
+ *     gave it another), which is not ordered against the stream that produced the caller's
+ *     buffers: either hand the engine that stream with rca_set_stream, or finish the work that
+ *     writes dev_seeds / dev_seed_ts / dev_rows (synchronise, or an event wait) before the call.
+ *     The call returns after it has waited for the engine's stream and read the counters back, so
+ *     the rows are complete when it returns;
  *   - the first call on a device looks up the scratch array's device address; make that first
  *     call before starting any stream capture;
  *   - all calls on one GPU share the one scratch array, which keeps what the previous call left in

@@ -136,6 +136,7 @@ struct rca_engine {
     unsigned *peer_err = nullptr;
     unsigned long long peer_seq = 0;
     bool peer_collected = true;           // peer_out holds the values of exchange peer_seq
+    unsigned long long peer_timeout_ns = 2000000000ull;
     // results of the last submission (one per plan) and the one the accessors address
     std::vector<PlanResult> results;
     int selected = 0;
@@ -1296,7 +1297,8 @@ extern "C" int rca_result_wait(rca_engine_t *e) {
 }
 
 static int state_query(rca_engine_t *e, const char *who, const int32_t *nodes, const int64_t *ta, const int64_t *tb, int64_t n,
-                       int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
+                       int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids, int st_lo = 0,
+                       int st_hi = 0x7fffffff) {
     if (!e) return RCA_ERR_ARG;
     if (n < 0 || (n > 0 && (!nodes || !ta || !tb || !out_first || !out_cnt))) return fail(e, RCA_ERR_ARG, "%s: null argument", who);
     if (n == 0) return RCA_OK;
@@ -1326,7 +1328,7 @@ static int state_query(rca_engine_t *e, const char *who, const int32_t *nodes, c
         CK(cudaMemcpyAsync((void *)d_nodes, nodes, 4 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
     }
     state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_rec, e->n_nodes, d_nodes, d_ta, d_tb, n,
-                                                                    d_first, d_cnt, d_ids);
+                                                                    st_lo, st_hi, d_first, d_cnt, d_ids);
     CK(cudaGetLastError());
     if (!on_device) {
         CK(cudaMemcpyAsync(out_first, d_first, 4 * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
@@ -1345,6 +1347,15 @@ extern "C" int rca_state_lookup(rca_engine_t *e, const int32_t *nodes, const int
 extern "C" int rca_state_window(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt,
                                 int64_t n, int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids) {
     return state_query(e, "rca_state_window", nodes, tmin_le, tmax_gt, n, on_device, out_first, out_cnt, out_ids);
+}
+
+extern "C" int rca_state_window_kind(rca_engine_t *e, const int32_t *nodes, const int64_t *tmin_le, const int64_t *tmax_gt,
+                                     int64_t n, int on_device, int32_t state_kind, int32_t *out_first, int32_t *out_cnt,
+                                     int32_t *out_ids) {
+    if (!e) return RCA_ERR_ARG;
+    if (state_kind < -1 || state_kind >= e->n_kinds) return fail(e, RCA_ERR_ARG, "rca_state_window_kind: kind %d unknown", state_kind);
+    const int lo = state_kind < 0 ? 0 : e->kind_start[state_kind], hi = state_kind < 0 ? 0x7fffffff : e->kind_start[state_kind + 1];
+    return state_query(e, "rca_state_window_kind", nodes, tmin_le, tmax_gt, n, on_device, out_first, out_cnt, out_ids, lo, hi);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1387,6 +1398,12 @@ extern "C" int rca_peer_connect(rca_engine_t *e, int32_t rank, const uint8_t *ha
     return RCA_OK;
 }
 
+extern "C" int rca_peer_set_timeout(rca_engine_t *e, int64_t milliseconds) {
+    if (!e || milliseconds < 1) return RCA_ERR_ARG;
+    e->peer_timeout_ns = (unsigned long long)milliseconds * 1000000ull;
+    return RCA_OK;
+}
+
 static int peer_launch(rca_engine *e, unsigned long long seq, int publish, int deferred, long long value) {
     PeerParams p;
     std::memset(&p, 0, sizeof p);
@@ -1396,7 +1413,7 @@ static int peer_launch(rca_engine *e, unsigned long long seq, int publish, int d
     }
     p.rank = e->peer_rank; p.world = e->peer_world; p.seq = seq;
     p.publish = publish; p.deferred = deferred; p.host_value = value;
-    p.out = e->peer_out; p.err = e->peer_err;
+    p.out = e->peer_out; p.err = e->peer_err; p.timeout_ns = e->peer_timeout_ns;
     peer_exchange<<<1, 32, 0, e->stream>>>(p);
     CK(cudaGetLastError());
     return RCA_OK;
@@ -1427,8 +1444,14 @@ extern "C" int rca_peer_wait(rca_engine_t *e, int64_t *out_values) {
     CK(cudaMemcpyAsync(e->peer_out_h, e->peer_out, (size_t)e->peer_world * sizeof(long long), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(e->peer_out_h + e->peer_world, e->peer_err, sizeof(unsigned), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
-    if (*(const unsigned *)(e->peer_out_h + e->peer_world))
-        return fail(e, RCA_ERR_CUDA, "rca_peer_allgather: a peer did not publish its value within two seconds");
+    if (*(const unsigned *)(e->peer_out_h + e->peer_world)) {
+        // reported once: the flag is cleared so that later exchanges are judged on their own.  The ranks' exchange
+        // counts may now differ (a peer that was late, not dead, is one exchange behind): callers should re-create
+        // the engines' peer set-up, or stop.
+        CK(cudaMemsetAsync(e->peer_err, 0, sizeof(unsigned), e->stream));
+        return fail(e, RCA_ERR_CUDA, "rca_peer_allgather: a peer did not publish its value within %.1f s (rca_peer_set_timeout)",
+                    (double)e->peer_timeout_ns * 1e-9);
+    }
     for (int r = 0; r < e->peer_world; r++) out_values[r] = e->peer_out_h[r];
     return RCA_OK;
 }

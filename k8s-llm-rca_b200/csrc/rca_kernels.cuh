@@ -1376,8 +1376,11 @@ __global__ void chain_plans(const Ctl *prev, Ctl *next, RowLens rl) {
 // Stand-alone HasState predicate, one thread per query: intervals of entity nodes[i] with
 // tmin <= ta[i] and tmax > tb[i].  ta == tb is the strict form (analyze_root_cause.py:70-79);
 // (ta, tb) = (window end, window start) is the loose form (:51-60).
+// [st_lo, st_hi): only STATE nodes in this id range count (ids are kind-major, so this is the `(n2:KIND)` label of
+// the statement; the reference applies the label before its LIMIT 10).
 __global__ void state_lookup(const int *st_off, const StRec *rec, int n_nodes, const int *nodes, const long long *ta,
-                             const long long *tb, long long n, int *out_first, int *out_cnt, int *out_ids) {
+                             const long long *tb, long long n, int st_lo, int st_hi, int *out_first, int *out_cnt,
+                             int *out_ids) {
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= n) return;
     int v = nodes[i], c = 0, f = -1;
@@ -1386,6 +1389,7 @@ __global__ void state_lookup(const int *st_off, const StRec *rec, int n_nodes, c
         for (int j = st_off[v]; j < st_off[v + 1]; j++) {
             if (rec[j].tmin <= a && rec[j].tmax > b) {
                 const int sn = rec[j].node;
+                if (sn < st_lo || sn >= st_hi) continue;
                 if (c == 0) f = sn;
                 if (out_ids && c < RCA_STATE_LIMIT) out_ids[i * RCA_STATE_LIMIT + c] = sn;
                 c++;
@@ -1531,6 +1535,7 @@ struct PeerParams {
     long long host_value;             // value to publish
     long long *out;                   // [world] the collected values, rank order (device memory of this rank)
     unsigned *err;
+    unsigned long long timeout_ns;    // give up waiting for a peer after this long (rca_peer_set_timeout)
 };
 // Four buffers rotate (seq & 3).  A rank can run ahead of another by at most one finished exchange plus the one in
 // flight; with the deferred wait that is three buffers in use at once, so the fourth write never lands on values a
@@ -1555,7 +1560,7 @@ __global__ void peer_exchange(const __grid_constant__ PeerParams p) {
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(s) : "l"(&src->seq) : "memory");
         if (s >= want) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (now - t0 > 2000000000ull) { atomicOr(p.err, 1u); break; }
+        if (now - t0 > p.timeout_ns) { atomicOr(p.err, 1u); p.out[t] = -1; return; }     // the slot was never written
         __nanosleep(200);
     }
     p.out[t] = src->value;

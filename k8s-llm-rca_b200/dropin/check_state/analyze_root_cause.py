@@ -30,7 +30,12 @@ def _entity_name_key(entity):
         return "name2"
     if entity["isAtomic"] == "true":
         return "val"
-    return {"nfs": "path", "hostPath": "path", "container": "containerName", "image": "imageName"}[entity["tag"]]
+    by_tag = {"nfs": "path", "hostPath": "path", "container": "containerName", "image": "imageName"}
+    tag = entity["tag"]
+    if tag not in by_tag:
+        # the reference's if/elif ladder leaves `key` unassigned for any other tag (:210-221)
+        raise UnboundLocalError("cannot access local variable 'key' where it is not associated with a value")
+    return by_tag[tag]
 
 
 def ad_hoc_find_entity_name(entity_kind, entity_id, query_executor):

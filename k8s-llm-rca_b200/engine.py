@@ -23,9 +23,9 @@ LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold",
            "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_graph_bytes", "rca_reserve",
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
-           "rca_result_level", "rca_result_copy", "rca_set_double_buffer", "rca_result_copy_async", "rca_result_wait", "rca_state_lookup", "rca_state_window", "rca_text_load",
+           "rca_result_level", "rca_result_copy", "rca_set_double_buffer", "rca_result_copy_async", "rca_result_wait", "rca_state_lookup", "rca_state_window", "rca_state_window_kind", "rca_text_load",
            "rca_text_contains", "rca_text_match_pairs", "rca_peer_handle", "rca_peer_connect", "rca_peer_allgather",
-           "rca_peer_wait", "rca_version")
+           "rca_peer_wait", "rca_peer_set_timeout", "rca_version")
 
 
 class RcaError(RuntimeError):
@@ -104,6 +104,8 @@ def load_library(path: str | None = None):
                                      C.c_void_p]
     lib.rca_state_window.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p]
+    lib.rca_state_window_kind.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int32,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rca_text_load.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
     lib.rca_set_double_buffer.argtypes = [C.c_void_p, C.c_int]
     lib.rca_result_copy_async.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -112,6 +114,7 @@ def load_library(path: str | None = None):
     lib.rca_peer_connect.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
     lib.rca_peer_allgather.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
     lib.rca_peer_wait.argtypes = [C.c_void_p, C.c_void_p]
+    lib.rca_peer_set_timeout.argtypes = [C.c_void_p, C.c_int64]
     lib.rca_text_match_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int64, C.c_void_p]
     lib.rca_text_contains.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
@@ -392,10 +395,22 @@ class Engine:
         """rca_expand_static: expansion that allocates nothing (fixed scratch inside the library; see
         include/rca_b200.h for the limits and the sharing rule).  All three buffers are device
         tensors owned by the caller: int32 seeds, int64 timestamps (or None), int32 row buffer.
+        The kernels run on the engine's stream: call set_stream(torch.cuda.current_stream().cuda_stream)
+        first, or synchronise after filling the tensors.
         Returns a StatsDesc; rows of length s start at word sum_{j<s} emitted[j]*row_len[j]."""
-        for t in (dev_seeds, dev_rows) + ((dev_seed_ts,) if dev_seed_ts is not None else ()):
+        import torch
+        want = [("dev_seeds", dev_seeds, torch.int32), ("dev_rows", dev_rows, torch.int32)]
+        if dev_seed_ts is not None:
+            want.append(("dev_seed_ts", dev_seed_ts, torch.int64))
+        for name, t, dt in want:
             if not (hasattr(t, "is_cuda") and t.is_cuda and t.is_contiguous()):
-                raise ValueError("expand_static takes contiguous device tensors")
+                raise ValueError(f"expand_static: {name} must be a contiguous device tensor")
+            if t.dtype != dt:
+                raise ValueError(f"expand_static: {name} must be {dt}, got {t.dtype}")
+            if t.device.index != self.device:
+                raise ValueError(f"expand_static: {name} lives on cuda:{t.device.index}, the engine on cuda:{self.device}")
+        if dev_seed_ts is not None and dev_seed_ts.numel() < dev_seeds.numel():
+            raise ValueError("expand_static: dev_seed_ts is shorter than dev_seeds")
         st = StatsDesc()
         self._ck(self.lib.rca_expand_static(
             self.h, C.byref(plan), dev_seeds.data_ptr(), int(dev_seeds.numel()),
@@ -474,6 +489,9 @@ class Engine:
         self._ck(self.lib.rca_peer_allgather(self.h, int(value), out.ctypes.data))
         return out
 
+    def peer_set_timeout(self, milliseconds: int):
+        self._ck(self.lib.rca_peer_set_timeout(self.h, int(milliseconds)))
+
     def peer_wait(self):
         out = np.empty(self._peer_world, np.int64)
         self._ck(self.lib.rca_peer_wait(self.h, out.ctypes.data))
@@ -505,16 +523,22 @@ class Engine:
                                                na.ctypes.data, nb.ctypes.data, n, out.ctypes.data))
         return out.astype(bool)
 
-    def state_lookup(self, nodes, ts, with_ids=True, ts_hi=None):
+    def state_lookup(self, nodes, ts, with_ids=True, ts_hi=None, state_kind=None):
         """HasState predicate for (entity node, timestamp ms) pairs -> (first, count, ids).
-        With ts_hi: intervals with tmin <= ts and tmax > ts_hi (the reference's 'loose' form)."""
+        With ts_hi: intervals with tmin <= ts and tmax > ts_hi (the reference's 'loose' form).
+        state_kind: only STATE nodes of this kind (the statement's `(n2:KIND)` label)."""
         nodes = np.ascontiguousarray(nodes, dtype=np.int32)
         ts = np.ascontiguousarray(ts, dtype=np.int64)
         n = len(nodes)
         first = np.empty(n, np.int32)
         cnt = np.empty(n, np.int32)
         ids = np.empty((n, STATE_LIMIT), np.int32) if with_ids else None
-        if ts_hi is None:
+        if state_kind is not None:
+            hi = np.ascontiguousarray(ts if ts_hi is None else ts_hi, dtype=np.int64)
+            self._ck(self.lib.rca_state_window_kind(self.h, nodes.ctypes.data, ts.ctypes.data, hi.ctypes.data, n, 0,
+                                                    int(state_kind), first.ctypes.data, cnt.ctypes.data,
+                                                    ids.ctypes.data if with_ids else None))
+        elif ts_hi is None:
             self._ck(self.lib.rca_state_lookup(self.h, nodes.ctypes.data, ts.ctypes.data, n, 0, first.ctypes.data,
                                                cnt.ctypes.data, ids.ctypes.data if with_ids else None))
         else:

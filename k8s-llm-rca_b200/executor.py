@@ -91,8 +91,8 @@ class GpuBackend:
         res = self.engine.expand(E.chain_plan(etypes, dirs), np.ascontiguousarray(seeds, dtype=np.int32))
         return res.rows(len(etypes))
 
-    def states(self, nodes, tmin_le, tmax_gt):
-        return self.engine.state_lookup(nodes, tmin_le, ts_hi=tmax_gt)
+    def states(self, nodes, tmin_le, tmax_gt, state_kind=None):
+        return self.engine.state_lookup(nodes, tmin_le, ts_hi=tmax_gt, state_kind=state_kind)
 
     def contains(self, texts):
         """{index of text: sorted node ids whose `message` contains it} - on the device.
@@ -367,14 +367,16 @@ class QueryRunner:
                 f"state query: {exc} - the engine compares timestamps as integers, which equals the reference's "
                 f"string comparison only for this fixed-width form") from None
         nodes = np.array(ents, dtype=np.int32)
-        _, cnt, ids = self.backend.states(nodes, np.full(len(nodes), lo, np.int64), np.full(len(nodes), hi, np.int64))
-        found = []
+        # the label of the state node is applied on the device, BEFORE the cut at ten ids per entity: the reference's
+        # `RETURN n2 LIMIT 10` (analyze_root_cause.py:76-77) also limits the rows that passed `(n2:KIND)`
+        sk = self._label[plan.state_label] if plan.state_label is not None else None
+        _, cnt, ids = self.backend.states(nodes, np.full(len(nodes), lo, np.int64), np.full(len(nodes), hi, np.int64), sk)
+        found = []                                   # (entity, state) pairs: every state stays with its own entity
         for i in range(len(nodes)):
             for sn in ids[i][:min(int(cnt[i]), ids.shape[1])].tolist():
-                if plan.state_label is None or int(s.kind_of(sn)) == self._label[plan.state_label]:
-                    found.append(sn)
-        found.sort()
-        envs = ({plan.entity_var: Node(s, int(nodes[0])), plan.state_var: Node(s, sn)} for sn in found)
+                found.append((int(nodes[i]), sn))
+        found.sort(key=lambda t: (t[1], t[0]))
+        envs = ({plan.entity_var: Node(s, en), plan.state_var: Node(s, sn)} for en, sn in found)
         return self._project(plan.ret, envs, params)
 
 

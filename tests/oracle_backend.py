@@ -23,8 +23,22 @@ class OracleBackend:
         rows, _ = self.orc.chain(seeds, etypes, [{"out": 0, "in": 1}[d] for d in dirs])
         return rows
 
-    def states(self, nodes, tmin_le, tmax_gt):
-        return self.orc.states(nodes, tmin_le, ts_hi=tmax_gt)
+    def states(self, nodes, tmin_le, tmax_gt, state_kind=None):
+        if state_kind is None:
+            return self.orc.states(nodes, tmin_le, ts_hi=tmax_gt)
+        # label first, LIMIT 10 afterwards (reference analyze_root_cause.py:72-77)
+        import numpy as np
+        _, cnt, ids = self.orc.states(nodes, tmin_le, limit=4096, ts_hi=tmax_gt)
+        lo, hi = self.snap.kind_range(state_kind)
+        n = len(nodes)
+        first, c2, out = np.full(n, -1, np.int32), np.zeros(n, np.int32), np.full((n, 10), -1, np.int32)
+        for i in range(n):
+            keep = [v for v in ids[i][:int(cnt[i])].tolist() if lo <= v < hi]
+            c2[i] = len(keep)
+            if keep:
+                first[i] = keep[0]
+                out[i, :min(10, len(keep))] = keep[:10]
+        return first, c2, out
 
     def contains(self, texts):
         ids, msgs = self.snap.props.messages()

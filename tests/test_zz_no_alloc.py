@@ -9,7 +9,13 @@ rca_expand_static works out of that array only.  The caller brings the seeds and
 Checked here, through the C ABI: the rows equal, word for word, what rca_expand returns for the
 same plan and seeds (integer data, so the tolerance is zero), on several calls in a row - the
 second call meets whatever the first one left in the shared scratch - and requests beyond the
-stated maxima are refused with a clear message instead of growing anything.
+stated maxima are refused with a clear message instead of growing anything.  One call is also
+held against the CPU oracle, and the property the entry point exists for is measured: the
+device's free memory (cudaMemGetInfo) is the same before and after a call.
+
+The entry point works on the engine's stream, which knows nothing of the stream torch fills the
+caller's tensors on; the test hands the engine torch's stream (set_stream), as a real caller of
+this kind would, so that "fill the buffer, then expand into it" is ordered on the device.
 
 The file name sorts last on purpose: with `-x` a failure here cannot hide the other tests.
 """
@@ -37,13 +43,14 @@ def _same(a, b):
         assert np.array_equal(a[s], b[s])          # same rows in the same order
 
 
-def test_static_entry_matches_expand_on_consecutive_calls(snap_10k):
+def test_static_entry_matches_expand_on_consecutive_calls(snap_10k, csr_oracle_lib):
     import torch
     from k8s_llm_rca_b200 import engine
     from k8s_llm_rca_b200.synth import T_BASE, DAY
 
     snap = snap_10k
     eng = engine.Engine(snap)
+    eng.set_stream(torch.cuda.current_stream().cuda_stream)     # the stream the tensors below are filled on
     eng.set_fused_threshold(1 << 40)               # the reference run uses the same single-launch kernels
     K = snap.kind_index
     pod, node, ev, ns = K("Pod"), K("Node"), K("Event"), K("Namespace")
@@ -63,9 +70,15 @@ def test_static_entry_matches_expand_on_consecutive_calls(snap_10k):
         (engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True, with_states=True), 3, d_ts, ts),
         (engine.varlen_plan("out", 4, dest_kind=node, excl_kinds=[ev, ns], entity_only=True), 4, None, None),
     ]
-    for plan, levels, dts, hts in plans:          # back to back: each call finds the previous call's leftovers
+    for it, (plan, levels, dts, hts) in enumerate(plans):   # back to back: each call finds the previous call's leftovers
         d_rows.fill_(-7)
+        if it != 2:                                # a plan's first call may make the driver load its kernels' code
+            eng.expand_static(plan, d_seeds, dts, d_rows)
+            d_rows.fill_(-7)
+        torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]
         st = eng.expand_static(plan, d_seeds, dts, d_rows)
+        assert torch.cuda.mem_get_info()[0] == free_before       # the call took no device memory
         got = _rows_from_static(st, d_rows, levels)
         ref = eng.expand(plan, seeds, hts)
         _same(got, ref.all_rows())
@@ -73,6 +86,36 @@ def test_static_entry_matches_expand_on_consecutive_calls(snap_10k):
         assert list(st.frontier)[:levels + 1] == ref.frontier and list(st.scanned)[:levels + 1] == ref.scanned
         used = sum(int(st.emitted[s]) * int(st.row_len[s]) for s in range(levels + 1))
         assert bool((d_rows[used:used + 64] == -7).all())         # nothing written past the result
+
+    # against the CPU oracle (not only against the library's other entry point)
+    orc = csr_oracle_lib.CsrOracle(snap)
+    plan, levels, dts, hts = plans[3]
+    d_rows.fill_(-7)
+    st = eng.expand_static(plan, d_seeds, None, d_rows)
+    got = _rows_from_static(st, d_rows, levels)
+    want, _ = orc.varlen(seeds, "out", 4, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    assert got.keys() == want.keys()
+    for s in want:
+        a, b = got[s], want[s]
+        assert np.array_equal(a[np.lexsort(a.T[::-1])], b[np.lexsort(b.T[::-1])])
+    plan, levels, dts, hts = plans[0]
+    d_rows.fill_(-7)
+    st = eng.expand_static(plan, d_seeds, dts, d_rows)
+    got = _rows_from_static(st, d_rows, levels)
+    want, _ = orc.varlen(seeds, "und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
+    order = np.argsort(seeds, kind="stable")
+    for s in want:
+        a, b = got[s], want[s]
+        a = a[np.lexsort(a[:, :2 * s + 1].T[::-1])]
+        b = b[np.lexsort(b.T[::-1])]
+        assert np.array_equal(a[:, :2 * s + 1], b)
+        t = ts[order[np.searchsorted(seeds[order], b[:, 0])]]
+        miss = np.zeros(len(b), np.int64)
+        for d in range(s + 1):                     # the fused HasState columns: first state id per node, missing mask
+            first, cnt, _ = orc.states(b[:, d], t, limit=1)
+            assert np.array_equal(a[:, 2 * s + 1 + d], first)
+            miss |= (cnt == 0).astype(np.int64) << d
+        assert np.array_equal(a[:, 3 * s + 2], miss.astype(np.int32))
 
     # and against the count / scan / fill kernels: same set of rows
     eng.set_fused_threshold(0)
@@ -92,6 +135,7 @@ def test_static_entry_refuses_what_does_not_fit(snap_10k):
 
     snap = snap_10k
     eng = engine.Engine(snap)
+    eng.set_stream(torch.cuda.current_stream().cuda_stream)
     K = snap.kind_index
     pod, node, ev, ns = K("Pod"), K("Node"), K("Event"), K("Namespace")
     plan = engine.varlen_plan("und", 3, dest_kind=node, excl_kinds=[ev, ns], entity_only=True)
@@ -113,6 +157,9 @@ def test_static_entry_refuses_what_does_not_fit(snap_10k):
     with pytest.raises(engine.RcaError) as ei:
         eng.expand_static(wide, seeds, None, big)
     assert "RCA_STATIC_MAX_FRONTIER" in str(ei.value) or "row buffer" in str(ei.value)
+    # tensors of the wrong type are turned away by the binding before they reach the kernels
+    with pytest.raises(ValueError):
+        eng.expand_static(plan, seeds.to(torch.int64), None, rows)
     # the engine is still usable afterwards
     ok = eng.expand_static(plan, seeds[:100].contiguous(), None, rows)
     assert int(ok.total) == eng.expand(plan, snap.nodes_of_kind(pod)[:100]).total
