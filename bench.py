@@ -6,13 +6,25 @@
 One step = one pass of the hot path over one incident batch (workloads.Config3): the undirected
 <=4-hop Pod->Node enumeration from 100k seed Pods plus the five per-incident instance queries,
 with the state predicate fused into emission.  Multi-GPU: graph replicated, one incident batch
-per rank (weak scaling), NCCL all-gather of the per-rank instance counts; no data-path collective.
+per rank (weak scaling), all-gather of the per-rank instance counts; no data-path collective.
 
 Printed line (rank 0): see the contract in the project brief.  `value` = instances of all ranks /
 max-over-ranks device time with inputs resident in HBM; `e2e` = the same through host buffers
 (pinned H2D of seeds and timestamps, D2H of every result row inside the timed region).
+
+Beside the headline the line carries
+  parity_check  untimed, before the clock starts: ONE seed list (rank 0's batch) cut into contiguous
+                work-balanced shards over the ranks, counts exchanged over peer memory AND over NCCL,
+                rows gathered to rank 0 through the C ABI (rca_gather_rows) AND through NCCL, the
+                gathered rows compared with rank 0's own expansion of the whole list and a seed
+                sample with the CPU oracle.  A mismatch ends the run with a non-zero exit code.
+  sharded       BASELINE config 4's shape as a strong-scaling measurement: one fixed job (10M-object
+                graph, a million sorted seed Pods) cut over the ranks, with and without the payload
+                gather to rank 0.
+  latency       BASELINE config 5: per-incident RCA graph latency.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -37,6 +49,32 @@ def peaks():
         except Exception:
             pass
     return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def csrc_digest():
+    """Digest of the kernel sources: profiles/traffic.json names the digest it was captured at, and a capture
+    that no longer matches the sources is not quoted."""
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, "k8s-llm-rca_b200", "csrc")
+    for f in sorted(os.listdir(d)) + [os.path.join(ROOT, "include", "rca_b200.h")]:
+        if f.endswith((".cu", ".cuh", ".h")):
+            with open(f if os.path.isabs(f) else os.path.join(d, f), "rb") as fh:
+                h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def captured_traffic(key):
+    """(bytes per launch set or None, note) from profiles/traffic.json, only if it was captured from these sources."""
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(tp):
+        return None, "no ncu capture committed"
+    try:
+        d = json.load(open(tp))
+    except Exception:
+        return None, "profiles/traffic.json unreadable"
+    if d.get("csrc_sha") != csrc_digest():
+        return None, f"capture is from other kernel sources (captured at {d.get('csrc_sha')}, commit {d.get('commit')})"
+    return d.get(key), f"ncu --set full capture at commit {d.get('commit')} ({d.get('source')})"
 
 
 class ClockSampler:
@@ -88,36 +126,52 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm), "samples_in_timed_window": in_window}
 
 
+def cpu_arm(w, pods, ev, ts, steps, warm):
+    """The CPU restatement of the reference's path (oracle/csr_oracle.c, kind "port" - Neo4j itself is unavailable
+    on this box) on the WHOLE batch the GPU arm runs: every step is one set of C calls (enumeration, the five
+    instance queries, the state predicate per node of every row), built -O3 -march=native for this host, all host
+    threads.  Two figures: the restatement as the reference's statements read (no pruning - Neo4j's variable-length
+    expand evaluates the path predicates after expanding), and the same job with the kind-level schema pruning the
+    engine's plans use - the stronger CPU program, reported beside it."""
+    from oracle import csr
+    orc = csr.CsrOracle(w.snap, csr.build_native())
+    threads = os.cpu_count() or orc.max_threads()        # torchrun exports OMP_NUM_THREADS=1: ask for the cores explicitly
+    n = len(pods)
+    k = max(1, n // 20)
+    out = {}
+    for name, pruned in (("plain", False), ("pruned", True)):
+        for _ in range(max(1, warm)):
+            w.oracle_step(orc, pods[:k], ev[:k], ts[:k], threads=threads, pruned=pruned)
+        t0 = time.perf_counter()
+        inst = 0
+        for _ in range(steps):
+            tot, _ = w.oracle_step(orc, pods, ev, ts, threads=threads, pruned=pruned)
+            inst += tot
+        dt = time.perf_counter() - t0
+        out[name] = (inst / dt, dt / steps, inst // steps)
+    return out, threads
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the CPU restatement of the reference's path (oracle/csr_oracle.c, kind
-    "port" - Neo4j itself is unavailable on this box), all host threads, bounded sample."""
+    """--impl reference: see cpu_arm.  Rank 0 alone runs it."""
     if rank != 0:
         return
     from k8s_llm_rca_b200 import workloads
-    from oracle.csr import CsrOracle, build
-    build()
     w = workloads.Config3(n_objects=args.objects, n_events=args.events)
-    orc = CsrOracle(w.snap)
     pods, ev, ts = w.batch(0)
-    n = min(len(pods), args.cpu_sample)
-    pods, ev, ts = pods[:n], ev[:n], ts[:n]
-    threads = os.cpu_count() or orc.max_threads()        # torchrun exports OMP_NUM_THREADS=1: ask for the cores explicitly
-    for _ in range(args.warmup):
-        w.oracle_run(orc, pods[:max(1, n // 10)], ev[:max(1, n // 10)], ts[:max(1, n // 10)], threads=threads)
-    t0 = time.perf_counter()
-    inst = 0
-    for _ in range(args.steps):
-        tot, _ = w.oracle_run(orc, pods, ev, ts, threads=threads)
-        inst += tot
-    dt = time.perf_counter() - t0
-    v = inst / dt
-    sample = f"first {n} of {w.n_inc} incidents of the config-3 batch per step"
+    res, threads = cpu_arm(w, pods, ev, ts, args.steps, min(args.warmup, 2))
+    v, sec, inst = res["plain"]
+    sample = f"all {len(pods)} incidents of the config-3 batch per step ({inst} instances, {sec:.2f} s per step)"
     emit({
         "metric": METRIC, "value": v, "unit": "instances/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * sec, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic", "impl": "reference",
-        "config": {"workload": w.name, "objects": args.objects, "incidents_per_step": n},
-        "cpu_baseline": {"value": v, "unit": "instances/s", "cores": threads, "kind": "port", "sample": sample},
+        "config": {"workload": w.name, "objects": args.objects, "incidents_per_step": int(len(pods)),
+                   "instances_per_step": int(inst), "max_hops": w.max_hops},
+        "cpu_baseline": {"value": v, "unit": "instances/s", "cores": threads, "kind": "port", "sample": sample,
+                         "pruned": {"value": res["pruned"][0], "ms_per_step": 1e3 * res["pruned"][1],
+                                    "what": "the same C restatement with kind-level schema pruning (result-neutral)"},
+                         "build": "gcc -O3 -march=native -fopenmp, state predicate in C, one call set per step"},
         "e2e": {"value": v, "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
 
@@ -135,6 +189,216 @@ def emit(obj):
         os.write(_REAL_STDOUT, data)
 
 
+def sort_rows_t(t):
+    """Rows of an int32 tensor in lexicographic order (stable sorts, last column first) - on the device."""
+    import torch
+    for c in range(t.shape[1] - 1, -1, -1):
+        t = t[torch.sort(t[:, c], stable=True).indices]
+    return t
+
+
+def parity_leg(w, eng, rank, world, dev, peer_ok, oracle_sample):
+    """Untimed: the seed-PARTITIONED path checked end to end.  Returns the dict for the JSON line (rank 0)."""
+    import torch
+    import torch.distributed as dist
+    from k8s_llm_rca_b200 import parallel
+    pods, ev, ts = w.batch(0)                       # ONE seed list for all ranks: rank 0's batch
+    order = np.argsort(pods, kind="stable")
+    pods, ts = pods[order], ts[order]               # sorted: rank-order concatenation is then ordered by seed
+    L = w.max_hops
+    my_pods, my_ts, (lo, hi) = parallel.shard_seeds(w.snap, pods, rank, world, "und", True, seed_ts=ts)
+    res = eng.expand(w.varlen, my_pods, my_ts)
+    info = {"ranks": world, "seeds": int(len(pods)), "shard": [int(lo), int(hi)], "ok": False}
+    fails = []
+    # counts: peer memory vs NCCL
+    nccl = parallel.allgather_counts(res.emitted, device=dev)             # [world, L+1]
+    if world > 1 and peer_ok:
+        for s in range(1, L + 1):
+            got = eng.peer_allgather(res.emitted[s])
+            if got.tolist() != nccl[:, s].tolist():
+                fails.append(f"level {s}: peer count exchange {got.tolist()} != NCCL {nccl[:, s].tolist()}")
+        info["counts_peer_eq_nccl"] = not fails
+    totals = nccl.sum(dim=0).tolist()
+    info["rows"] = int(sum(totals))
+    # rows: C-ABI gather over peer memory vs NCCL gather, every level, into one window
+    gathered = {}
+    if world > 1 and peer_ok:
+        offs, at = {}, 0
+        for s in range(1, L + 1):
+            offs[s] = at
+            at += totals[s] * res.row_len[s]
+        parallel.connect_gather(eng, at + 16, dst=0)
+        for s in range(1, L + 1):
+            if not totals[s]:
+                continue
+            got, per, _ = parallel.gathered_rows(eng, res, s, dst=0, offset_words=offs[s])
+            ref = parallel.gather_rows(parallel.device_rows(res, s), nccl[:, s], dst=0)
+            if rank == 0:
+                if not torch.equal(got, ref):
+                    fails.append(f"level {s}: rca_gather_rows differs from the NCCL gather")
+                gathered[s] = got.clone()
+        info["gather_peer_eq_nccl"] = not fails
+    else:
+        for s in range(1, L + 1):
+            if totals[s]:
+                ref = parallel.gather_rows(parallel.device_rows(res, s), nccl[:, s], dst=0)
+                if rank == 0:
+                    gathered[s] = ref.clone()
+    if rank == 0:
+        # the gathered rows against this rank's own expansion of the WHOLE list (same multiset, row for row)
+        d_p, d_t = torch.from_numpy(pods).to(dev), torch.from_numpy(ts).to(dev)
+        torch.cuda.synchronize()
+        whole = eng.expand(w.varlen, d_p, d_t)
+        for s in range(1, L + 1):
+            if whole.emitted[s] != totals[s]:
+                fails.append(f"level {s}: {totals[s]} rows over the shards, {whole.emitted[s]} from one GPU")
+                continue
+            if totals[s] and not torch.equal(sort_rows_t(gathered[s]), sort_rows_t(parallel.device_rows(whole, s).clone())):
+                fails.append(f"level {s}: sharded rows differ from the single-GPU rows")
+        info["sharded_eq_single_gpu"] = not any("single" in f or "one GPU" in f for f in fails)
+        # a seed sample against the CPU oracle, state columns included
+        from oracle import csr
+        orc = csr.CsrOracle(w.snap)
+        uniq = np.unique(pods)                       # a Pod may have more than one incident: take all of a chosen Pod's
+        vals = uniq[np.unique(np.linspace(0, len(uniq) - 1, min(oracle_sample, len(uniq))).astype(np.int64))]
+        mask = np.isin(pods, vals)
+        sp, st = pods[mask], ts[mask]
+        want, _, _ = orc.varlen_step(sp, st, "und", L, dest_kind=w.snap.kind_index("Node"), excl_kinds=w.excl,
+                                     entity_only=True)
+        d_sp = torch.from_numpy(sp).to(dev)
+        n_cmp = 0
+        for s in range(1, L + 1):
+            if not totals[s]:
+                if s in want:
+                    fails.append(f"level {s}: oracle has rows, the GPUs none")
+                continue
+            g = gathered[s]
+            g = g[torch.isin(g[:, 0], d_sp)]
+            a = sort_rows_t(g).cpu().numpy()
+            b = want.get(s, np.zeros((0, res.row_len[s]), np.int32))
+            b = b[np.lexsort(b.T[::-1])] if len(b) else b
+            n_cmp += len(b)
+            if a.shape != b.shape or not np.array_equal(a, b):
+                fails.append(f"level {s}: rows of the seed sample differ from the CPU oracle")
+        info["oracle_sample"] = {"seeds": int(len(sp)), "rows": int(n_cmp)}
+        info["ok"] = not fails
+        if fails:
+            info["failures"] = fails[:6]
+    flag = torch.tensor([0 if (rank == 0 and fails) else 1], device=dev)
+    if world > 1:
+        dist.broadcast(flag, src=0)
+    info["ok"] = bool(flag.item()) and not fails
+    return info
+
+
+def sharded_leg(args, rank, world, local_rank, dev, barrier):
+    """BASELINE config 4's shape, strong scaling: one fixed job over `world` GPUs."""
+    import torch
+    import torch.distributed as dist
+    from k8s_llm_rca_b200 import engine as E
+    from k8s_llm_rca_b200 import parallel, workloads
+    t0 = time.time()
+    w4 = workloads.Config4(n_objects=args.sharded_objects, n_seeds=args.sharded_seeds, rank=rank, barrier=barrier)
+    t_graph = time.time() - t0
+    eng = E.Engine(w4.snap, device=local_rank)
+    stream = torch.cuda.Stream(priority=-1)
+    eng.set_stream(stream.cuda_stream)
+    seeds, _, (lo, hi) = parallel.shard_seeds(w4.snap, w4.seeds, rank, world, "und", True)
+    steps = max(2, min(args.steps, args.sharded_steps))
+    out = {"workload": w4.name, "objects": args.sharded_objects, "seeds": int(len(w4.seeds)), "steps": steps,
+           "graph_bytes_in_hbm": int(eng.graph_bytes()), "graph_ready_s": round(t_graph, 1)}
+    with torch.cuda.stream(stream):
+        d_seeds = torch.from_numpy(np.ascontiguousarray(seeds)).to(dev)
+        torch.cuda.synchronize()
+        peer_ok = False
+        if world > 1:
+            try:
+                parallel.connect_peers(eng)
+                eng.peer_set_timeout(20_000)
+                peer_ok = eng.peer_allgather(rank + 1).tolist() == list(range(1, world + 1))
+            except Exception as ex:
+                print(f"bench.py: sharded leg: peer memory unavailable ({ex})", file=sys.stderr)
+            flag = torch.tensor([1 if peer_ok else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            peer_ok = bool(flag.item())
+
+        def timed(fn):
+            for _ in range(2):
+                fn()
+            barrier()
+            ms_kernel, e0, e1 = 0.0, torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            last = None
+            for _ in range(steps):
+                last = fn()
+                ms_kernel += last[1]
+            e1.record(stream)
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / steps, ms_kernel / steps, last[0]
+
+        def reduce_ms(ms, kernel_ms, inst):
+            t = torch.tensor([ms, kernel_ms, -kernel_ms], dtype=torch.float64, device=dev)
+            n = torch.tensor([inst], dtype=torch.int64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dist.all_reduce(n, op=dist.ReduceOp.SUM)
+            return float(t[0]), float(t[1]), float(-t[2]), int(n[0])
+
+        # (1) <= 5 hops, counted; the count exchange is the only thing that crosses NVLink
+        def count5():
+            r = eng.expand(w4.count5, d_seeds)
+            if world > 1 and peer_ok:
+                eng.peer_allgather(r.total)
+            return r.total, r.kernel_ms
+        ms, kmax, kmin, inst = reduce_ms(*timed(count5))
+        out["count5"] = {"instances": inst, "ms_per_step": ms, "value": inst / (ms * 1e-3), "unit": "instances/s",
+                         "rank_kernel_ms": {"max": kmax, "min": kmin}}
+
+        # (2) <= 4 hops with rows: (a) rows stay on their ranks, (b) gathered to rank 0's window
+        def rows4():
+            r = eng.expand(w4.rows4, d_seeds)
+            if world > 1 and peer_ok:
+                eng.peer_allgather(r.total)
+            return r.total, r.kernel_ms, r
+        r0 = rows4()[2]
+        cnt = parallel.allgather_counts(r0.emitted, device=dev)
+        totals = cnt.sum(dim=0).tolist()
+        ms, kmax, kmin, inst = reduce_ms(*timed(lambda: rows4()[:2]))
+        out["rows4"] = {"instances": inst, "ms_per_step": ms, "value": inst / (ms * 1e-3), "unit": "instances/s",
+                        "rank_kernel_ms": {"max": kmax, "min": kmin}}
+        if world > 1 and peer_ok:
+            offs, at = {}, 0
+            for s in range(1, 5):
+                offs[s] = at
+                at += totals[s] * r0.row_len[s]
+            parallel.connect_gather(eng, at + 16, dst=0)
+            push = [0.0]
+
+            def rows4_gather():
+                tot, kms, r = rows4()
+                for s in range(1, 5):
+                    if totals[s]:
+                        _, _, _, pms = eng.gather_rows(r, s, offs[s])
+                        push[0] += pms
+                return tot, kms
+            push[0] = 0.0
+            ms_g, _, _, inst_g = reduce_ms(*timed(rows4_gather))
+            words_in = sum((totals[s] - int(cnt[0, s])) * r0.row_len[s] for s in range(1, 5))     # what crosses NVLink into rank 0
+            gather_ms = max(ms_g - ms, 1e-6)
+            out["rows4_gathered"] = {"instances": inst_g, "ms_per_step": ms_g, "value": inst_g / (ms_g * 1e-3),
+                                     "unit": "instances/s", "bytes_into_rank0_per_step": int(4 * words_in),
+                                     "gather_ms_per_step": gather_ms,
+                                     "gather_GBps_into_rank0": 4 * words_in / (gather_ms * 1e-3) / 1e9,
+                                     "how": "rca_gather_rows: every rank stores its rows into rank 0's window over NVLink "
+                                            "peer memory (16-byte remote stores), offsets from the count exchange"}
+            # the gathered level 4 is what one GPU produces for the whole list (counts; rows are checked by parity_check)
+        out["limiter_note"] = ("strong scaling: per-rank kernel time falls with the shard; what does not shrink is the fixed "
+                               "cost of a submission (uploads, launches, one synchronisation) and, with the payload gather, "
+                               "rank 0's NVLink ingress")
+    eng.close()
+    return out
+
+
 def main():
     # libraries (NCCL's version banner, for one) write to file descriptor 1; the contract is ONE JSON line there,
     # so everything else that lands on fd 1 goes to stderr and the line is written to the saved descriptor
@@ -149,11 +413,14 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--objects", type=int, default=1_000_000)
     ap.add_argument("--events", type=int, default=108_696)
-    ap.add_argument("--cpu-sample", type=int, default=50_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--latency-incidents", type=int, default=10_000,
                     help="config 5: incidents replayed as one batch (drawn with replacement); 0 skips the latency leg")
     ap.add_argument("--latency-singles", type=int, default=200, help="incidents replayed one by one for p50/p99")
+    ap.add_argument("--parity-sample", type=int, default=2000, help="seeds of the parity leg compared with the CPU oracle; 0 skips the leg")
+    ap.add_argument("--sharded-objects", type=int, default=10_000_000, help="config 4 shape, strong scaling; 0 skips the leg")
+    ap.add_argument("--sharded-seeds", type=int, default=1_000_000)
+    ap.add_argument("--sharded-steps", type=int, default=10)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -198,6 +465,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    parity = None
     with torch.cuda.stream(stream):
         d_pods, d_ev, d_ts = (torch.from_numpy(x).to(dev) for x in (pods, ev, ts))
         h_pods, h_ev, h_ts = (torch.from_numpy(x).pin_memory() for x in (pods, ev, ts))
@@ -210,6 +478,7 @@ def main():
             from k8s_llm_rca_b200 import parallel
             try:
                 parallel.connect_peers(eng)
+                eng.peer_set_timeout(20_000)         # the parity leg gives rank 0 seconds of extra work
                 got = eng.peer_allgather(rank + 1)
                 peer_ok = got.tolist() == list(range(1, world + 1))
             except Exception as ex:                                              # no peer access between these GPUs: NCCL does it
@@ -217,6 +486,17 @@ def main():
             flag = torch.tensor([1 if peer_ok else 0], device=dev)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)                          # all ranks take the same road
             peer_ok = bool(flag.item())
+
+        # ---- parity of the seed-partitioned path, before any clock starts
+        if args.parity_sample > 0:
+            torch.cuda.synchronize()
+            parity = parity_leg(w, eng, rank, world, dev, peer_ok, args.parity_sample)
+            barrier()
+            if not parity["ok"]:
+                if rank == 0:
+                    emit({"metric": METRIC, "value": None, "n_gpus": world, "parity_check": parity,
+                          "error": "the seed-partitioned path does not reproduce the single-GPU / oracle rows"})
+                raise SystemExit(3)
 
         # size the pinned result buffer from one untimed run
         tot0, res0 = w.run(eng, d_pods, d_ev, d_ts)
@@ -386,59 +666,65 @@ def main():
                                "run_query one statement at a time, batch = one launch set for all incidents"}
         sx.close()
         mx.close()
+    graph_bytes = int(eng.graph_bytes())
+    eng.close()
+    del d_pods, d_ev, d_ts, flush
+    torch.cuda.empty_cache()
+
+    # ---- config 4's shape: strong scaling of one fixed job, with and without the payload gather
+    sharded = None
+    if args.sharded_objects > 0:
+        barrier()
+        sharded = sharded_leg(args, rank, world, local_rank, dev, barrier)
+        barrier()
 
     if rank == 0:
         peak, peak_src = peaks()
         # dominant kernel = the level launch with the largest share of the step
         (kname, ks), (kms, kbytes, kcalls) = max(per_level.items(), key=lambda kv: kv[1][0])
         achieved = (kbytes / kcalls) / (kms / kcalls * 1e-3) / 1e9
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            try:
-                traffic = json.load(open(tp)).get(f"{kname}/level{ks}")
-            except Exception:
-                traffic = None
+        traffic, traffic_note = captured_traffic(f"{kname}/level{ks}")
+        dram_frac = (traffic / (kms / kcalls * 1e-3) / 1e9 / peak) if traffic else None
         out = {
             "metric": METRIC, "value": inst_res / (ms_res * 1e-3), "unit": "instances/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_res / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
             "config": {"workload": w.name, "objects": args.objects, "incidents_per_step_per_gpu": int(len(pods)),
                        "instances_per_step": inst_res // args.steps, "max_hops": w.max_hops,
-                       "graph_bytes_in_hbm": int(eng.graph_bytes()),
-                       "l2": f"flushed between timed steps (256 MiB write); graph ({eng.graph_bytes() / 1e6:.0f} MB) also exceeds the 126 MB L2",
+                       "graph_bytes_in_hbm": graph_bytes,
+                       "l2": f"flushed between timed steps (256 MiB write); graph ({graph_bytes / 1e6:.0f} MB) also exceeds the 126 MB L2",
                        "parallelism": f"graph replicated x{world}, one incident batch per GPU, all-gather of counts"
                                       + (" over peer memory (rca_peer_allgather)" if peer_ok else " (NCCL)" if world > 1 else "")},
             "e2e": {"value": inst_e2e / (ms_e2e * 1e-3), "unit": "instances/s",
                     "h2d_bytes_per_step": int(pods.nbytes + ev.nbytes + 2 * ts.nbytes),     # the five instance queries share one seed list
                     "d2h_bytes_per_step": int(d2h[0] // args.steps), "ms_per_step": ms_e2e / args.steps,
                     "wall_ms_per_step": 1e3 * wall_e2e / args.steps,
+                    "d2h_GBps_per_rank": (d2h[0] / args.steps) / (ms_e2e / args.steps * 1e-3) / 1e9,
                     "how": "every step: seeds host->device from pinned memory, rca_expand_many, ALL rows device->host into "
                            "pinned memory; the copy-out of a step overlaps the next step (two output arenas, "
                            "rca_result_copy_async); one pair of CUDA events around all steps, L2 flushes included",
                     "serial_ms_per_step": ms_serial / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": f"level {ks} of the {kname} plan (its count + scan + fill launches)",
+                         "traffic": traffic, "dram_frac": dram_frac, "traffic_source": traffic_note,
+                         "kernel": f"level {ks} of the {kname} plan (its count + scan + fill launches)",
                          "peak_source": peak_src, "bytes_per_launch": kbytes // kcalls,
-                         "ms_per_launch": kms / kcalls, "share_of_step": (kms / kcalls) / (ms_res / args.steps)},
+                         "ms_per_launch": kms / kcalls, "share_of_step": (kms / kcalls) / (ms_res / args.steps),
+                         "frac_is": "SURVEY 8(d)'s algorithmic bytes / time / peak; dram_frac = ncu DRAM bytes / time / peak"},
             "clocks": clocks,
+            "parity_check": parity,
+            "sharded": sharded,
             "latency": latency,
         }
         if world == 1 and not args.no_cpu_baseline:
-            from oracle.csr import CsrOracle, build
-            build()
-            orc = CsrOracle(w.snap)
-            n = min(len(pods), args.cpu_sample)
-            cores = os.cpu_count() or orc.max_threads()
-            w.oracle_run(orc, pods[:n // 10], ev[:n // 10], ts[:n // 10], threads=cores)
-            t0 = time.perf_counter()
-            ctot, _ = w.oracle_run(orc, pods[:n], ev[:n], ts[:n], threads=cores)
-            dt = time.perf_counter() - t0
-            out["cpu_baseline"] = {"value": ctot / dt, "unit": "instances/s", "cores": cores, "kind": "port",
-                                   "sample": f"first {n} of {len(pods)} incidents of the same batch, one pass, {dt:.1f} s"}
+            res, cores = cpu_arm(w, pods, ev, ts, 1, 1)
+            v, sec, inst = res["plain"]
+            out["cpu_baseline"] = {"value": v, "unit": "instances/s", "cores": cores, "kind": "port",
+                                   "sample": f"all {len(pods)} incidents of the same batch, one pass, {sec:.1f} s",
+                                   "pruned": {"value": res["pruned"][0], "ms_per_step": 1e3 * res["pruned"][1],
+                                              "what": "the same C restatement with kind-level schema pruning (result-neutral)"},
+                                   "build": "gcc -O3 -march=native -fopenmp, state predicate in C, one call set per step"}
         emit(out)
-    eng.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -247,6 +247,28 @@ int rca_peer_allgather(rca_engine_t *e, int64_t value, int64_t *out_values);
 int rca_peer_wait(rca_engine_t *e, int64_t *out_values);
 int rca_peer_set_timeout(rca_engine_t *e, int64_t milliseconds);
 
+/* ---- Row gather over peer memory ---------------------------------------------------------------------
+ * The payload half of the multi-GPU path (the reference has no counterpart - it is one process): after a
+ * seed-sharded expansion every rank pushes its rows of one level into a window in the destination rank's
+ * device memory, at the offset the exclusive scan of the ranks' counts gives it, so the window holds the rows
+ * of all ranks in rank order (= seed order when the shards are contiguous ranges of a sorted seed list).
+ * Remote 16-byte stores over NVLink / NVSwitch by a kernel on the engine's stream; counts and completion
+ * travel through the count exchange above, which must be set up first (rca_peer_handle / rca_peer_connect).
+ *   rca_gather_window   on the destination rank: allocate (or replace) the window, return its CUDA IPC handle
+ *   rca_gather_connect  on every rank (the destination included): map the destination's window.  The caller
+ *                       carries the handle between the processes, as for rca_peer_connect
+ *   rca_gather_rows     collective: gather `level` of the selected plan of the last submission to word
+ *                       `window_offset_words` of the window (the same on every rank; several levels can
+ *                       share a window).  On the destination *dev_rows points at the rows in the window and
+ *                       *n_rows is the total; rank_rows (nullable, [world]) receives every rank's count;
+ *                       push_ms (nullable) this rank's device time for its push.  Rows that do not fit the
+ *                       window make EVERY rank return RCA_ERR_NOMEM (same totals everywhere): replace the
+ *                       window with a larger one and gather again. */
+int rca_gather_window(rca_engine_t *e, int64_t words, uint8_t *out_handle);
+int rca_gather_connect(rca_engine_t *e, int32_t dst_rank, const uint8_t *handle, int64_t words);
+int rca_gather_rows(rca_engine_t *e, int level, int64_t window_offset_words, const int32_t **dev_rows, int64_t *n_rows,
+                    int64_t *rank_rows, double *push_ms);
+
 /* Limits of rca_expand_static: the fixed scratch holds at most this many seeds and this many
  * partial paths (summed over all hops of one call), in RCA_STATIC_SCRATCH_BYTES of device memory
  * that every GPU which loads the library keeps until the process exits. */

@@ -137,6 +137,14 @@ struct rca_engine {
     unsigned long long peer_seq = 0;
     bool peer_collected = true;           // peer_out holds the values of exchange peer_seq
     unsigned long long peer_timeout_ns = 2000000000ull;
+    // row gather over peer memory (rca_gather_*): the window rows are pushed into
+    int *gather_own = nullptr;            // this rank's window (only a rank that is a destination has one)
+    unsigned long long gather_own_words = 0;
+    int *gather_dst = nullptr;            // the destination rank's window as mapped into this process
+    unsigned long long gather_dst_words = 0;
+    int gather_dst_rank = -1;
+    bool gather_dst_mapped = false;       // gather_dst came from cudaIpcOpenMemHandle (not this rank's own window)
+    cudaEvent_t ev_g0 = nullptr, ev_g1 = nullptr;
     // results of the last submission (one per plan) and the one the accessors address
     std::vector<PlanResult> results;
     int selected = 0;
@@ -328,6 +336,10 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->peer_out) cudaFree(e->peer_out);
     if (e->peer_err) cudaFree(e->peer_err);
     if (e->peer_out_h) cudaFreeHost(e->peer_out_h);
+    if (e->gather_dst_mapped && e->gather_dst) cudaIpcCloseMemHandle(e->gather_dst);
+    if (e->gather_own) cudaFree(e->gather_own);
+    if (e->ev_g0) cudaEventDestroy(e->ev_g0);
+    if (e->ev_g1) cudaEventDestroy(e->ev_g1);
     for (auto ev : e->ev_many) cudaEventDestroy(ev);
     for (auto ev : e->ev_side) cudaEventDestroy(ev);
     for (auto st : e->side) cudaStreamDestroy(st);
@@ -1453,6 +1465,105 @@ extern "C" int rca_peer_wait(rca_engine_t *e, int64_t *out_values) {
                     (double)e->peer_timeout_ns * 1e-9);
     }
     for (int r = 0; r < e->peer_world; r++) out_values[r] = e->peer_out_h[r];
+    return RCA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Row gather over peer memory: see push_rows in rca_kernels.cuh.
+extern "C" int rca_gather_window(rca_engine_t *e, int64_t words, uint8_t *out_handle) {
+    if (!e) return RCA_ERR_ARG;
+    if (words < 1 || !out_handle) return fail(e, RCA_ERR_ARG, "rca_gather_window: words %lld, or null handle", (long long)words);
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    if (e->gather_dst && !e->gather_dst_mapped) { e->gather_dst = nullptr; e->gather_dst_rank = -1; }    // it was the old window
+    if (e->gather_own) { CK(cudaFree(e->gather_own)); e->gather_own = nullptr; e->gather_own_words = 0; }
+    CK(cudaMalloc((void **)&e->gather_own, (size_t)words * sizeof(int)));
+    e->gather_own_words = (unsigned long long)words;
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, e->gather_own));
+    std::memcpy(out_handle, &h, sizeof h);
+    return RCA_OK;
+}
+
+extern "C" int rca_gather_connect(rca_engine_t *e, int32_t dst_rank, const uint8_t *handle, int64_t words) {
+    if (!e) return RCA_ERR_ARG;
+    if (e->peer_rank < 0) return fail(e, RCA_ERR_ARG, "rca_gather_connect: set the count exchange up first (rca_peer_handle, rca_peer_connect)");
+    if (dst_rank < 0 || dst_rank >= e->peer_world || words < 1) return fail(e, RCA_ERR_ARG, "rca_gather_connect: rank %d not in 0..%d, or no words", dst_rank, e->peer_world - 1);
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    if (e->gather_dst_mapped && e->gather_dst) CK(cudaIpcCloseMemHandle(e->gather_dst));
+    e->gather_dst = nullptr; e->gather_dst_mapped = false; e->gather_dst_rank = -1;
+    if (dst_rank == e->peer_rank) {
+        if (!e->gather_own || e->gather_own_words < (unsigned long long)words)
+            return fail(e, RCA_ERR_ARG, "rca_gather_connect: this rank is the destination but holds no window of %lld words (rca_gather_window)", (long long)words);
+        e->gather_dst = e->gather_own;
+    } else {
+        if (!handle) return fail(e, RCA_ERR_ARG, "rca_gather_connect: null handle");
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, sizeof h);
+        void *ptr = nullptr;
+        CK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+        e->gather_dst = (int *)ptr;
+        e->gather_dst_mapped = true;
+    }
+    e->gather_dst_words = (unsigned long long)words;
+    e->gather_dst_rank = dst_rank;
+    if (!e->ev_g0) { CK(cudaEventCreate(&e->ev_g0)); CK(cudaEventCreate(&e->ev_g1)); }
+    return RCA_OK;
+}
+
+extern "C" int rca_gather_rows(rca_engine_t *e, int level, int64_t window_offset_words, const int32_t **dev_rows,
+                               int64_t *n_rows, int64_t *rank_rows, double *push_ms) {
+    if (!e || level < 0 || level > RCA_MAX_HOPS || window_offset_words < 0) return RCA_ERR_ARG;
+    if (e->gather_dst_rank < 0) return fail(e, RCA_ERR_ARG, "rca_gather_rows: no destination window connected (rca_gather_connect)");
+    const PlanResult *r = current_result(e);
+    if (!r) return fail(e, RCA_ERR_ARG, "rca_gather_rows: no result held (call rca_expand first)");
+    CK(cudaSetDevice(e->device));
+    const int world = e->peer_world, rank = e->peer_rank, dst = e->gather_dst_rank;
+    // 1. every rank learns every rank's row count (and that all ranks mean rows of the same width)
+    int64_t counts[8];
+    const long long rl = r->row_len[level];
+    int rc = rca_peer_allgather(e, (int64_t)r->rows[level] | ((int64_t)rl << 48), counts);
+    if (rc) return rc;
+    unsigned long long total = 0, before = 0;
+    for (int k = 0; k < world; k++) {
+        if ((counts[k] >> 48) != rl) return fail(e, RCA_ERR_ARG, "rca_gather_rows: rank %d holds rows of %lld words, this rank of %lld", k, (long long)(counts[k] >> 48), rl);
+        counts[k] &= (1ll << 48) - 1;
+        if (k < rank) before += (unsigned long long)counts[k];
+        total += (unsigned long long)counts[k];
+        if (rank_rows) rank_rows[k] = counts[k];
+    }
+    if (n_rows) *n_rows = (int64_t)total;
+    if (dev_rows) *dev_rows = nullptr;
+    const unsigned long long woff = (unsigned long long)window_offset_words;
+    if (woff + total * (unsigned long long)rl > e->gather_dst_words)       // every rank sees the same totals: all of them refuse
+        return fail(e, RCA_ERR_NOMEM, "rca_gather_rows: %llu rows of %lld words at word %llu do not fit the destination window of %llu words",
+                    total, rl, woff, e->gather_dst_words);
+    // 2. push this rank's rows to their place in the destination window (rank order = seed order for contiguous shards)
+    const unsigned long long words = (unsigned long long)r->rows[level] * (unsigned long long)rl;
+    CK(cudaEventRecord(e->ev_g0, e->stream));
+    if (words) {
+        PushParams pp;
+        pp.src = e->out + r->base[level];
+        pp.dst = e->gather_dst + woff + before * (unsigned long long)rl;
+        pp.words = words;
+        const unsigned long long want = (words / 4 + 255) / 256 + 1;
+        const unsigned grid = (unsigned)std::min<unsigned long long>(want, (unsigned long long)e->sm_count * 8);
+        push_rows<<<grid, 256, 0, e->stream>>>(pp);
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(e->ev_g1, e->stream));
+    // 3. second exchange = completion: its release store follows the push on this stream, so when the destination
+    //    has seen every rank's sequence number, every rank's rows are in its window
+    int64_t done[8];
+    rc = rca_peer_allgather(e, (int64_t)words, done);
+    if (rc) return rc;
+    if (push_ms) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e->ev_g0, e->ev_g1));
+        *push_ms = ms;
+    }
+    if (rank == dst && dev_rows) *dev_rows = total ? e->gather_own + woff : nullptr;
     return RCA_OK;
 }
 

@@ -1566,4 +1566,41 @@ __global__ void peer_exchange(const __grid_constant__ PeerParams p) {
     p.out[t] = src->value;
 }
 
+// ------------------------------------------------------------------------------------------------
+// push_rows: the payload half of the gather ("gather-v of compacted instances").  Every
+// rank's rows of one level are already compact in its own output arena; after the count exchange each rank
+// knows where its rows start in the destination rank's window (exclusive scan over the ranks' counts), and
+// this kernel stores them there over NVLink peer memory - plain 16-byte remote stores, each thread a
+// contiguous run, no staging copy, no host in the data path.  Loads are local and may be unaligned against
+// the destination (the two offsets are unrelated), so the stores are aligned on the DESTINATION and each one
+// is assembled from four word loads of the local arena.  Completion is published by the peer_exchange launch
+// that follows on the same stream (release store after this kernel has finished).
+struct PushParams {
+    const int *src;                   // first word of this rank's rows (local output arena)
+    int *dst;                         // where they go in the destination window (peer or local memory)
+    unsigned long long words;
+};
+
+__global__ void __launch_bounds__(256) push_rows(const __grid_constant__ PushParams p) {
+    const unsigned long long n = p.words;
+    // head: words before the first 16-byte boundary of dst
+    unsigned long long head = ((16u - (unsigned)(reinterpret_cast<uintptr_t>(p.dst) & 15u)) & 15u) >> 2;
+    if (head > n) head = n;
+    const unsigned long long vec = (n - head) >> 2, tail0 = head + (vec << 2);
+    const unsigned long long tid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+    const unsigned long long nthreads = gridDim.x * (unsigned long long)blockDim.x;
+    if (tid < head) p.dst[tid] = __ldg(p.src + tid);
+    if (tid < n - tail0) p.dst[tail0 + tid] = __ldg(p.src + tail0 + tid);
+    int4 *d4 = reinterpret_cast<int4 *>(p.dst + head);
+    const int *s = p.src + head;
+    const bool src_aligned = (reinterpret_cast<uintptr_t>(s) & 15u) == 0;
+    for (unsigned long long j = tid; j < vec; j += nthreads) {
+        int4 v;
+        if (src_aligned) v = __ldg(reinterpret_cast<const int4 *>(s) + j);
+        else v = make_int4(__ldg(s + 4 * j), __ldg(s + 4 * j + 1), __ldg(s + 4 * j + 2), __ldg(s + 4 * j + 3));
+        d4[j] = v;
+    }
+    __threadfence_system();
+}
+
 }  // namespace rca

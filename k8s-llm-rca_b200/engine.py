@@ -25,7 +25,8 @@ EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_set_double_buffer", "rca_result_copy_async", "rca_result_wait", "rca_state_lookup", "rca_state_window", "rca_state_window_kind", "rca_text_load",
            "rca_text_contains", "rca_text_match_pairs", "rca_peer_handle", "rca_peer_connect", "rca_peer_allgather",
-           "rca_peer_wait", "rca_peer_set_timeout", "rca_version")
+           "rca_peer_wait", "rca_peer_set_timeout", "rca_gather_window", "rca_gather_connect", "rca_gather_rows",
+           "rca_version")
 
 
 class RcaError(RuntimeError):
@@ -115,6 +116,10 @@ def load_library(path: str | None = None):
     lib.rca_peer_allgather.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
     lib.rca_peer_wait.argtypes = [C.c_void_p, C.c_void_p]
     lib.rca_peer_set_timeout.argtypes = [C.c_void_p, C.c_int64]
+    lib.rca_gather_window.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    lib.rca_gather_connect.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]
+    lib.rca_gather_rows.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_void_p,
+                                    C.POINTER(C.c_double)]
     lib.rca_text_match_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int64, C.c_void_p]
     lib.rca_text_contains.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
@@ -496,6 +501,26 @@ class Engine:
         out = np.empty(self._peer_world, np.int64)
         self._ck(self.lib.rca_peer_wait(self.h, out.ctypes.data))
         return out
+
+    # -- row gather over peer memory (include/rca_b200.h: rca_gather_*)
+    def gather_window(self, words: int) -> bytes:
+        """On the destination rank: allocate the window the ranks push their rows into; -> its IPC handle."""
+        buf = C.create_string_buffer(self.PEER_HANDLE_BYTES)
+        self._ck(self.lib.rca_gather_window(self.h, int(words), buf))
+        return buf.raw
+
+    def gather_connect(self, dst_rank: int, handle, words: int) -> None:
+        self._ck(self.lib.rca_gather_connect(self.h, int(dst_rank), handle, int(words)))
+
+    def gather_rows(self, result, level: int, offset_words: int = 0):
+        """Collective: rows of `level` of `result` (an ExpandResult of this engine's last submission) from every
+        rank into the destination's window at word `offset_words`.  -> (device pointer or 0, total rows, per-rank rows, this rank's push ms)."""
+        assert result._gen == self._gen, "result was overwritten by a later expand()"
+        self._ck(self.lib.rca_result_select(self.h, result.index))
+        p, n, ms = C.c_void_p(), C.c_int64(), C.c_double()
+        per = np.zeros(self._peer_world, np.int64)
+        self._ck(self.lib.rca_gather_rows(self.h, int(level), int(offset_words), C.byref(p), C.byref(n), per.ctypes.data, C.byref(ms)))
+        return (p.value or 0), int(n.value), per, float(ms.value)
 
     def match_pairs(self, msg_nodes, needles_a, needles_b):
         """The message filter of an instance query for many rows at once (generate_query.py:104-129):

@@ -86,6 +86,31 @@ def connect_peers(engine):
     engine.peer_connect(rank, handles)
 
 
+def connect_gather(engine, words: int, dst: int = 0):
+    """Set up the engine's row gather over peer memory (rca_gather_*): rank `dst` allocates a window of
+    `words` int32 words, its CUDA IPC handle travels through torch.distributed, every rank maps it.
+    connect_peers(engine) must have been called.  Call again with a larger `words` to replace the window."""
+    rank, world = world_info()
+    box = [engine.gather_window(words) if rank == dst else None]
+    if world > 1:
+        _dist().broadcast_object_list(box, src=dst)
+    engine.gather_connect(dst, box[0], words)
+
+
+def gathered_rows(engine, result, level: int, dst: int = 0, offset_words: int = 0):
+    """engine.gather_rows as a torch tensor on the destination (zero-copy view of the window), None elsewhere.
+    -> (tensor or None, per-rank row counts, this rank's push time in ms)."""
+    import torch
+    ptr, n, per, ms = engine.gather_rows(result, level, offset_words)
+    rank, _ = world_info()
+    if rank != dst:
+        return None, per, ms
+    w = result.row_len[level]
+    if n == 0:
+        return torch.empty((0, w), dtype=torch.int32, device=f"cuda:{engine.device}"), per, ms
+    return torch.as_tensor(_CudaView(ptr, n, w), device=f"cuda:{engine.device}"), per, ms
+
+
 def ladder_decision(counts_by_rank):
     """From allgather_counts output: (any rows anywhere?, globally shortest length with rows or -1)."""
     tot = counts_by_rank.sum(dim=0)

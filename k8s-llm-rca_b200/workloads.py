@@ -137,3 +137,81 @@ class Config3:
             out[name] = {len(ets): with_state_cols(rows, len(ets), ev)}
             total += len(rows)
         return total, out
+
+    def oracle_step(self, orc, pods, ev, ts, threads=0, pruned=False, keep_rows=False):
+        """The same step on the CPU oracle as ONE set of C calls (callers: tests and bench.py's cpu_baseline /
+        --impl reference legs only): enumeration + the five instance queries, the state predicate evaluated in C
+        for every node of every row - no array glue in the timed call.  pruned: with the kind-level schema pruning
+        the engine's plans also use (oracle/csr_oracle.c: orc_reach); the table is built once per workload.
+        Returns (instances, {plan name: {length: rows}} or None)."""
+        s = self.snap
+        kw = dict(dest_kind=s.kind_index("Node"), excl_kinds=self.excl, entity_only=True)
+        reach = None
+        if pruned:
+            if not hasattr(self, "_reach"):
+                self._reach = orc.reach("und", self.max_hops, **kw)
+            reach = self._reach
+        t = ts if self.with_states else None
+        out = {} if keep_rows else None
+        lv, _, total = orc.varlen_step(pods, t, "und", self.max_hops, reach=reach, threads=threads, keep_rows=keep_rows, **kw)
+        if keep_rows:
+            out["varlen"] = lv
+        for name, (ets, dirs, _) in self.chains.items():
+            rows, _ = orc.chain_step(ev, t, ets, [{"out": 0, "in": 1}[d] for d in dirs], threads=threads, keep_rows=keep_rows)
+            if keep_rows:
+                out[name] = {len(ets): rows}
+                total += len(rows)
+            else:
+                total += rows
+        return total, out
+
+
+def shared_snapshot(n_objects: int, n_events: int, config_index: int, rank: int = 0, barrier=None, cache_dir="/dev/shm"):
+    """A generated graph built ONCE per box and shared by the ranks through `cache_dir`: rank 0 generates and
+    saves the arrays (Snapshot.save), the others load them after `barrier()`.  Arrays only - no property store:
+    the multi-GPU workloads need ids and adjacency, not strings.  A file left by an earlier run of the same
+    configuration is reused."""
+    import os
+    from .snapshot import Snapshot
+    path = os.path.join(cache_dir, f"rca_b200_snap_{n_objects}_{n_events}_{synth.config_seed(config_index)}")
+    done = path + ".done"
+    snap = None
+    if rank == 0 and not os.path.exists(done):
+        snap = synth.generate(n_objects, n_events, synth.config_seed(config_index))
+        try:
+            snap.save(path)
+            with open(done, "w") as f:
+                f.write("ok\n")
+        except OSError:
+            pass                                   # no room in cache_dir: the other ranks generate their own
+    if barrier is not None:
+        barrier()
+    if snap is None:
+        if os.path.exists(done):
+            snap = Snapshot.load(path)
+        else:
+            snap = synth.generate(n_objects, n_events, synth.config_seed(config_index))
+    return snap
+
+
+class Config4:
+    """BASELINE config 4's shape: a 10M-object graph, undirected Pod -> Node enumeration of up to 5 hops from a
+    sorted seed list that is cut into contiguous, work-balanced shards (parallel.shard_seeds), one per GPU -
+    strong scaling: the whole job is fixed, every added GPU takes a share of it.  Two plans:
+      count5  <= 5 hops, count only (1.7 k instances per seed: the rows of a million seeds would be 300 GB)
+      rows4   <= 4 hops with rows, the rows then gathered to rank 0 (rca_gather_rows) or left where they are."""
+
+    def __init__(self, snap=None, n_objects=10_000_000, n_seeds=1_000_000, rank=0, barrier=None):
+        self.snap = snap if snap is not None else shared_snapshot(n_objects, n_objects // 100, 3, rank, barrier)
+        s = self.snap
+        K = s.kind_index
+        pod, node = K("Pod"), K("Node")
+        self.excl = [K("Event"), K("Namespace")]
+        self.kw = dict(dest_kind=node, excl_kinds=self.excl, entity_only=True)
+        pods = s.nodes_of_kind(pod)
+        step = max(1, len(pods) // max(1, n_seeds))
+        self.seeds = np.ascontiguousarray(pods[::step][:n_seeds], dtype=np.int32)       # sorted ids
+        self.count5 = E.varlen_plan("und", 5, pos_kind=[pod], count_only=True, **self.kw)
+        self.rows4 = E.varlen_plan("und", 4, pos_kind=[pod], **self.kw)
+        self.name = (f"config4 shape: {n_objects / 1e6:g}M-object cluster, {len(self.seeds)} seed Pods in contiguous "
+                     f"work-balanced shards, undirected Pod->Node: <=5 hops counted, <=4 hops with rows")

@@ -15,7 +15,7 @@ def test_sharded_expansion_over_nccl():
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs at least two GPUs")
-    world = min(n, 4)
+    world = n
     env = dict(os.environ, MASTER_ADDR="127.0.0.1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29731", os.path.join(ROOT, "tests", "dist_gpu_worker.py")]

@@ -163,3 +163,63 @@ def test_timestamp_strings_order_like_integers():
     assert ts_to_ms("2020-12-11 06:35:02.011") == 1607668502011          # reference test_check_state.py:41
     with pytest.raises(ValueError):
         ts_to_ms("2020-12-11T06:35:02.011")
+
+
+def _sorted(a, w=None):
+    a = np.asarray(a)
+    return a[np.lexsort(a.T[::-1])] if len(a) else a
+
+
+@pytest.mark.parametrize("pruned", [False, True])
+def test_step_functions_equal_the_plain_oracle_plus_state_lookups(snap_small, csr_oracle_lib, pruned):
+    """orc_varlen_step / orc_chain_step (the timed CPU baseline: state columns in C, optional schema pruning) give
+    the rows of orc_varlen / orc_chain, and their state columns are what orc_states says node by node."""
+    from k8s_llm_rca_b200.synth import T_BASE, DAY
+    snap = snap_small
+    orc = csr_oracle_lib.CsrOracle(snap)
+    K = snap.kind_index
+    rng = np.random.default_rng(3)
+    seeds = snap.nodes_of_kind(K("Pod")).astype(np.int32)
+    ts = (T_BASE + rng.integers(-2 * DAY, 33 * DAY, size=len(seeds))).astype(np.int64)
+    for direction, hops, dest in (("und", 4, "Node"), ("out", 3, "nfs"), ("und", 3, "ConfigMap"), ("in", 2, "Service")):
+        kw = dict(dest_kind=K(dest), excl_kinds=[K("Event"), K("Namespace")], entity_only=True)
+        reach = orc.reach(direction, hops, **kw) if pruned else None
+        assert (reach is not None) == pruned
+        want, sc_plain = orc.varlen(seeds, direction, hops, **kw)
+        got, sc, total = orc.varlen_step(seeds, ts, direction, hops, reach=reach, **kw)
+        assert total == sum(len(r) for r in want.values()) and got.keys() == want.keys()
+        assert sc == sc_plain if not pruned else sc <= sc_plain
+        by_seed = dict(zip(seeds.tolist(), ts.tolist()))
+        for s, rows in got.items():
+            rows = _sorted(rows)
+            assert np.array_equal(rows[:, :2 * s + 1], _sorted(want[s]))
+            t = np.array([by_seed[v] for v in rows[:, 0].tolist()], np.int64)
+            miss = np.zeros(len(rows), np.int64)
+            for d in range(s + 1):
+                first, cnt, _ = orc.states(rows[:, d], t, limit=1)
+                assert np.array_equal(rows[:, 2 * s + 1 + d], first)
+                miss |= (cnt == 0).astype(np.int64) << d
+            assert np.array_equal(rows[:, 3 * s + 2], miss.astype(np.int32))
+        # without timestamps: plain rows
+        got2, _, _ = orc.varlen_step(seeds, None, direction, hops, reach=reach, **kw)
+        for s in want:
+            assert np.array_equal(_sorted(got2[s]), _sorted(want[s]))
+    # a plan pruning does not apply to (no destination)
+    assert orc.reach("und", 3, dest_kind=-1) is None
+    # typed chain with state columns
+    L = snap.label_index
+    ets = [snap.find_etypes("HasEvent", L("Event"), L("EVENT"), "metadata_uid")[0],
+           snap.find_etypes("ReferInternal", L("Event"), L("Pod"), "involvedObject_uid")[0],
+           snap.find_etypes("ReferInternal", L("Pod"), L("Node"), "spec_nodeName")[0]]
+    ev = snap.nodes_of_kind(L("EVENT")).astype(np.int32)
+    ets_ts = (T_BASE + rng.integers(0, 30 * DAY, size=len(ev))).astype(np.int64)
+    want, _ = orc.chain(ev, ets, [1, 0, 0])
+    got, _ = orc.chain_step(ev, ets_ts, ets, [1, 0, 0])
+    assert len(got) == len(want) > 0
+    got = _sorted(got)
+    assert np.array_equal(got[:, :7], _sorted(want))
+    by_seed = dict(zip(ev.tolist(), ets_ts.tolist()))
+    t = np.array([by_seed[v] for v in got[:, 0].tolist()], np.int64)
+    for d in range(4):
+        first, _, _ = orc.states(got[:, d], t, limit=1)
+        assert np.array_equal(got[:, 7 + d], first)
