@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -33,6 +34,7 @@ struct PreparedPlan {
     int L = 0, mode = kModeChain;
     std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
     std::vector<char> level_typed, level_dead;
+    int wide_level = -1;                         // level whose frontier is stored as wide entries (rca_kernels.cuh), or -1
 };
 
 struct PlanResult {
@@ -95,6 +97,8 @@ struct rca_engine {
     long long fused_max_seeds = 16384;    // up to this many seeds a variable-length plan runs one fused launch per level
     long long chain_walk_fanout = 64;     // typed chains whose per-seed fan-out is at most this run as one depth-first launch
     bool unit_steps = true;               // typed steps with at most one candidate per path use count_unit / fill_unit
+    bool wide_entries = false;            // the level before a final unit level stores whole paths (rca_set_wide_entries);
+                                          // measured on config 3: level 3 0.219 -> 0.179 ms, level 2 0.099 -> 0.181 ms - off
     long long chain_fused_max_seeds = 1 << 20;   // typed chains have uniform tiles: the fused launch suits them far longer
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
@@ -375,6 +379,14 @@ extern "C" int64_t rca_graph_bytes(const rca_engine_t *e) { return e ? (int64_t)
 extern "C" int rca_set_unit_steps(rca_engine_t *e, int on) {
     if (!e) return RCA_ERR_ARG;
     e->unit_steps = on != 0;
+    e->plan_cache.clear();
+    return RCA_OK;
+}
+
+extern "C" int rca_set_wide_entries(rca_engine_t *e, int on) {
+    if (!e) return RCA_ERR_ARG;
+    e->wide_entries = on != 0;
+    e->plan_cache.clear();
     return RCA_OK;
 }
 
@@ -527,7 +539,8 @@ static KernelSet pick_kernels(int mode, int q) {
 }
 
 // unit steps (rca_kernels.cuh): typed step, at most one candidate per path, path so far of 2..6 nodes
-static KernelSet pick_unit_kernels(int q) {
+static KernelSet pick_unit_kernels(int q, bool wide = false) {
+    if (wide) return q == 1 ? KernelSet{count_unit<1, true>, fill_unit<1, true>, nullptr} : KernelSet{count_unit<2, true>, fill_unit<2, true>, nullptr};
     switch (q) {
         case 1: return KernelSet{count_unit<1>, fill_unit<1>, nullptr};
         case 2: return KernelSet{count_unit<2>, fill_unit<2>, nullptr};
@@ -535,6 +548,12 @@ static KernelSet pick_unit_kernels(int q) {
         case 4: return KernelSet{count_unit<4>, fill_unit<4>, nullptr};
         default: return KernelSet{count_unit<5>, fill_unit<5>, nullptr};
     }
+}
+
+// the fill kernel of a level that writes wide entries (variable-length plans, node-simple, levels 1 and 2)
+template <bool ADJ2>
+static level_kernel_t pick_wide_fill(int q) {
+    return q == 0 ? (level_kernel_t)fill_level<ADJ2, kModeSimple, 0, true> : (level_kernel_t)fill_level<ADJ2, kModeSimple, 1, true>;
 }
 
 static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
@@ -634,6 +653,24 @@ static void prepare_plan_fresh(rca_engine *e, const rca_plan_t *pl, int64_t n_se
             can = nxt;
             pp.level_dead[s] = pp.subs[s].empty();
             pp.level_typed[s] = !pp.subs[s].empty() && pp.subs[s].size() <= 2;
+        }
+        // Wide entries (rca_kernels.cuh): level w (1 or 2) stores whole paths when level w+1 consists of unit steps
+        // only, nothing continues from it (so nothing ever walks up through level w), and level w itself is ONE
+        // launch of the general kernels (its entry count is final when its fill starts).
+        if (e->unit_steps && e->wide_entries && !pl->count_only) {
+            for (int w = 1; w <= 2 && w < L; w++) {
+                const int c = w + 1;
+                if (!pp.level_typed[c]) continue;
+                bool ok = true;
+                for (const Sub &u : pp.subs[c]) ok &= !(u.fl & 1) && (u.d ? e->unit_in_base : e->unit_out_base)[u.t] >= 0;
+                bool one_launch = !pp.level_typed[w] || pp.subs[w].size() == 1;
+                bool w_unit = false;                  // level w itself a unit level: its kernels do not write wide entries
+                if (pp.level_typed[w] && w >= 2)
+                    for (const Sub &u : pp.subs[w]) w_unit |= (u.d ? e->unit_in_base : e->unit_out_base)[u.t] >= 0;
+                if (ok && one_launch && !w_unit && !pp.level_dead[w]) pp.wide_level = w;
+            }
+            if (pp.wide_level >= 0 && std::getenv("RCA_B200_DEBUG"))
+                std::fprintf(stderr, "rca_b200: plan of %d hops stores level %d as wide entries\n", L, pp.wide_level);
         }
     }
 }
@@ -800,8 +837,14 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 p.sub = j;
                 KernelSet ks = sdir == RCA_DIR_OUT ? pick_kernels<false>(pp.mode, s - 1) : pick_kernels<true>(pp.mode, s - 1);
                 size_t dyn_c = dyn, dyn_f = dyn;
+                p.wide_out = pp.wide_level == s;
+                p.wide_in = pp.wide_level == s - 1 && s >= 2;
+                if (p.wide_out) {
+                    ks.fill = sdir == RCA_DIR_OUT ? pick_wide_fill<false>(s - 1) : pick_wide_fill<true>(s - 1);
+                    dyn_f = (size_t)kWarps * warp_smem_ints(s, 1) * sizeof(int);
+                }
                 if (takes_unit(s, j)) {
-                    ks = pick_unit_kernels(s - 1);
+                    ks = pick_unit_kernels(s - 1, p.wide_in != 0);
                     p.unit_next = e->unit_next + (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t];
                     p.unit_fl = pp.subs[s][j].fl;
                     p.unit_aux = pp.subs[s][j].aux;
@@ -995,7 +1038,10 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         if (++retries > 12) return fail(e, RCA_ERR_NOMEM, "rca_expand: scratch arenas still too small after %d retries", retries);
         // counters are exact up to and including the first level that overflowed: grow to at least that
         unsigned long long fneed = 0, oneed = 0;
-        for (int s = 1; s <= L; s++) { fneed += e->h_ctl->F[s]; oneed += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s); }
+        for (int s = 1; s <= L; s++) {
+            fneed += s == pp.wide_level ? 3 * (e->h_ctl->F[s] + 32) : e->h_ctl->F[s];      // wide entries: three planes
+            oneed += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s);
+        }
         if (ov & 1u) { rc = grow(e, &e->frontier, &e->fcap, std::max(e->fcap * 2, fneed + fneed / 4)); if (rc) return rc; }
         if (ov & 2u) { rc = grow(e, &e->out, &e->ocap, std::max(e->ocap * 2, oneed + oneed / 4)); if (rc) return rc; }
     }
@@ -1221,7 +1267,7 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
             unsigned long long f = 0;
             const int L = pps[k].L;
             for (int s = 1; s <= L; s++) {
-                f += e->mh_ctl[k].F[s];
+                f += s == pps[k].wide_level ? 3 * (e->mh_ctl[k].F[s] + 32) : e->mh_ctl[k].F[s];
                 if (!aside[k]) oneed += e->mh_ctl[k].N[s] * (unsigned long long)row_len_of(&plans[k], s);
             }
             fneed = std::max(fneed, f);

@@ -151,6 +151,9 @@ struct LevelParams {
     int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row
     int unit_aux;                     // kind | intermediate-kind flag << 16 of the far kind
     const int2 *unit_next;            // per node of the near kind: its one (neighbour, relationship), or (-1, -1)
+    // wide frontier (see "Wide entries" below): this level's fill writes / this level's kernels read entries that
+    // carry the whole path so far, the states of its nodes and the seed's timestamp
+    int wide_out, wide_in;
     // count-only plans whose LAST level is one unit step: the level before it takes that step while it counts
     // (count_level only: nothing is stored, so neither its own fill nor the last level is launched)
     int la_n;
@@ -301,17 +304,34 @@ struct WarpSm {
 };
 // ... then a staging area for 32 finished rows (3s+3 words each at most), so that rows leave the SM
 // as whole 128 B lines instead of 4-byte stores scattered at row stride
-__host__ __device__ constexpr int warp_smem_ints(int s) { return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile + kTile * (3 * s + 3); }
+// ... and, for a level that writes wide entries, four rows of 32 ints: per entry of the tile the states of its path's
+// first two nodes and the seed's timestamp (looked up once per entry, used by every candidate of the entry)
+__host__ __device__ constexpr int warp_smem_ints(int s, int wide = 0) {
+    return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile + kTile * (3 * s + 3) + (wide ? 4 * kTile : 0);
+}
 
 struct Warp {                         // a warp's view of its tile
     WarpSm *W;
-    int *anc_n, *anc_r, *stage;
+    int *anc_n, *anc_r, *stage, *wd;
     int lane;
     unsigned lt;
 };
 
+// Wide entries.  When the level after this one is the plan's last and a unit step (fill_unit: one lane per path), that
+// level's cost is the lane-divergent loads it needs to rebuild a path from 16-byte parent-pointer entries - the parent
+// entry, the seed, the seed's timestamp - and one state header per node of the row.  A level whose paths have at most
+// three nodes can hand all of that over instead: its fill writes, per surviving path, three 16-byte words in three
+// planes (each plane one coalesced stream for the reader)
+//     A = (node0, node1, node2 | -1, rel1)    B = (rel2 | -1, root, aux, state0)    C = (state1, state2 | -1, ts)
+// where state_d is the answer of the HasState predicate for node_d at the seed's timestamp (-1: none) - looked up ONCE
+// per node as it joins the path (the siblings of an entry share the first two), not once per row.  The reader then
+// does one coalesced 48-byte read, its one next-hop load and ONE state header load (the new last node) per row.
+// Plane stride = the level's entry count rounded up to 32; planes B and C exist only as far as the plan needs them
+// (C only with the state filter).  Nothing walks up THROUGH a wide level: it is always the last level stored.
+__device__ __forceinline__ unsigned long long wide_stride(unsigned long long entries) { return (entries + 31ull) & ~31ull; }
+
 // Prologue of one tile; returns the number of candidates C.
-template <int MODE>
+template <int MODE, bool WIDE = false>
 __device__ __forceinline__ int tile_prologue(const LevelParams &p, const Tables &T, const Warp &w, unsigned tile,
                                              unsigned long long Fq, const unsigned long long *fb) {
     const int s = p.s, q = s - 1, lane = w.lane;
@@ -374,6 +394,19 @@ __device__ __forceinline__ int tile_prologue(const LevelParams &p, const Tables 
             w.anc_n[o] = __ldg(p.seeds + par);
         }
         W.root[o] = par;
+        if (WIDE && p.with_states) {                  // the entry's share of a wide entry: timestamp, states of its nodes
+            const long long ts = __ldg(p.seed_ts + par);
+            const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+            const int n0 = w.anc_n[o];
+            const ulonglong2 h0 = ld_head(st, n0, true), h1 = ld_head(st, tail, q > 0);
+            int f0, c0, f1 = -1, c1;
+            head_finish(st, h0, n0, ts, f0, c0);
+            if (q > 0) head_finish(st, h1, tail, ts, f1, c1);
+            w.wd[o] = f0;
+            w.wd[kTile + o] = f1;
+            w.wd[2 * kTile + o] = (int)(unsigned)(unsigned long long)ts;
+            w.wd[3 * kTile + o] = (int)((unsigned long long)ts >> 32);
+        }
     }
     W.coff[nz + lane] = (lane == 0) ? C : 0x7fffffff;            // coff[nz] = C, then sentinels
     if (lane < 2) W.coff[nz + 32 + lane] = 0x7fffffff;
@@ -511,10 +544,10 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
 }
 
 // Walk the tile's windows, classify, and write the survivors starting at the tile's bases.
-template <bool ADJ2, int MODE, int QT>
+template <bool ADJ2, int MODE, int QT, bool WIDE = false>
 __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T, const Warp &w, unsigned tile, int C,
                                           unsigned long long fb_s, unsigned long long ob_s,
-                                          unsigned long long run_f, unsigned long long run_e) {
+                                          unsigned long long run_f, unsigned long long run_e, unsigned long long wstride = 0) {
     WarpSm &W = *w.W;
     const int lane = w.lane;
     const int n_it = (C + 31) >> 5;
@@ -524,8 +557,34 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
         const Cand x = fetch_cand<ADJ2, MODE>(p, w, o, (it << 5) + lane, C);
         int v, r, na;
         const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + lane, C, x, v, r, na);
+        ulonglong2 hv = make_ulonglong2(1ull, 0ull);
+        const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+        if (WIDE && p.with_states) hv = ld_head(st, v, (fl & 1) != 0);          // the new node's state: in flight over the ballots
         const unsigned bf = __ballot_sync(0xffffffffu, fl & 1), be = __ballot_sync(0xffffffffu, fl & 2);
-        if (fl & 1) {
+        if (WIDE) {
+            if (fl & 1) {                             // QT + 1 = nodes on the path before this step (1 or 2)
+                const unsigned long long j = run_f + __popc(bf & w.lt);
+                int4 *A = p.frontier + fb_s;
+                if (fb_s + 3 * wstride <= p.fcap) {   // else: flagged by the scan, the run is void
+                    const int n0 = w.anc_n[o];
+                    const int n1 = QT >= 1 ? w.anc_n[kTile + o] : v, n2 = QT >= 1 ? v : -1;
+                    const int r1 = QT >= 1 ? w.anc_r[kTile + o] : r, r2 = QT >= 1 ? r : -1;
+                    int s0 = -1, s1 = -1, s2 = -1, tl = 0, th = 0;
+                    if (p.with_states) {
+                        tl = w.wd[2 * kTile + o]; th = w.wd[3 * kTile + o];
+                        const long long ts = (long long)(((unsigned long long)(unsigned)th << 32) | (unsigned)tl);
+                        int fv, cv;
+                        head_finish(st, hv, v, ts, fv, cv);
+                        s0 = w.wd[o];
+                        s1 = QT >= 1 ? w.wd[kTile + o] : fv;
+                        s2 = QT >= 1 ? fv : -1;
+                    }
+                    A[j] = make_int4(n0, n1, n2, r1);
+                    A[wstride + j] = make_int4(r2, W.root[o], na, s0);
+                    if (p.with_states) A[2 * wstride + j] = make_int4(s1, s2, tl, th);
+                }
+            }
+        } else if (fl & 1) {
             const unsigned long long pos = fb_s + run_f + __popc(bf & w.lt);
             if (pos < p.fcap) p.frontier[pos] = make_int4(v, (int)(tile * kTile + W.cidx[o]), r, na);
         }
@@ -605,7 +664,7 @@ struct LevelCtx {
     unsigned long long slot0;         // first tile slot of this level (multiple of kGroup)
 };
 __device__ __forceinline__ LevelCtx level_setup(const LevelParams &p, TablesSm &tsm, unsigned long long *s_fb,
-                                                int *s_dyn) {
+                                                int *s_dyn, int wide = 0) {
     LevelCtx c;
     const int tid = threadIdx.x, s = p.s, q = s - 1;
     Ctl *ctl = p.ctl;
@@ -617,10 +676,11 @@ __device__ __forceinline__ LevelCtx level_setup(const LevelParams &p, TablesSm &
     c.T = stage_tables(tsm, p);                       // contains the CTA barrier that also publishes s_fb
     c.w.lane = tid & 31;
     c.w.lt = (1u << c.w.lane) - 1u;
-    c.w.W = reinterpret_cast<WarpSm *>(s_dyn + (tid >> 5) * warp_smem_ints(s));
+    c.w.W = reinterpret_cast<WarpSm *>(s_dyn + (tid >> 5) * warp_smem_ints(s, wide));
     c.w.anc_n = reinterpret_cast<int *>(c.w.W + 1);
     c.w.anc_r = c.w.anc_n + s * kTile;
     c.w.stage = c.w.anc_r + s * kTile;
+    c.w.wd = c.w.stage + kTile * (3 * s + 3);
     unsigned long long fb_s = 0, ob_s = ctl->out_base;
     for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
     c.fb_s = fb_s; c.ob_s = ob_s;
@@ -715,22 +775,24 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
         ctl->F[s] = base_f + s_run[0];
         ctl->N[s] = base_n + s_run[1];
         unsigned ov = 0;
-        if (!p.la_n && fb_s + base_f + s_run[0] > p.fcap) ov |= 1u;     // la_n: the paths are counted, never stored
+        const unsigned long long room = p.wide_out ? 3ull * wide_stride(base_f + s_run[0]) : base_f + s_run[0];
+        if (!p.la_n && fb_s + room > p.fcap) ov |= 1u;                 // la_n: the paths are counted, never stored
         if (!p.count_only && ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (ov) ctl->overflow = ov;
     }
 }
 
 // split path, step 3: re-walk every tile and write its survivors at (group prefix + in-group prefix)
-template <bool ADJ2, int MODE, int QT>
+template <bool ADJ2, int MODE, int QT, bool WIDE = false>
 __global__ void __launch_bounds__(kThreads, RCA_MINB_FILL) fill_level(const __grid_constant__ LevelParams p) {
     extern __shared__ int s_dyn[];
     __shared__ TablesSm tsm;
     __shared__ unsigned long long s_fb[kLv];
     if (overflow_seen(p.ctl)) return;
-    LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
+    LevelCtx c = level_setup(p, tsm, s_fb, s_dyn, WIDE ? 1 : 0);
     c.fb_s += p.ctl->subF;                            // after the earlier sub-launches of this level
     c.ob_s += p.ctl->subN * (unsigned long long)p.row_len;
+    const unsigned long long wstride = WIDE ? wide_stride(p.ctl->F[p.s]) : 0ull;     // a wide level is one launch: F[s] is final
     const unsigned nwarps = gridDim.x * kWarps;
     for (unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < c.ntiles; tile += nwarps) {
         const unsigned long long slot = c.slot0 + tile, g = slot / kGroup;
@@ -741,8 +803,8 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_FILL) fill_level(const __gr
         const ulonglong2 gp = p.gscan[g];
         const unsigned long long run_f = gp.x + __reduce_add_sync(0xffffffffu, mine.x);
         const unsigned long long run_e = gp.y + __reduce_add_sync(0xffffffffu, mine.y);
-        const int C = tile_prologue<MODE>(p, c.T, c.w, tile, c.Fq, s_fb);
-        tile_fill<ADJ2, MODE, QT>(p, c.T, c.w, tile, C, c.fb_s, c.ob_s, run_f, run_e);
+        const int C = tile_prologue<MODE, WIDE>(p, c.T, c.w, tile, c.Fq, s_fb);
+        tile_fill<ADJ2, MODE, QT, WIDE>(p, c.T, c.w, tile, C, c.fb_s, c.ob_s, run_f, run_e, wstride);
     }
 }
 
@@ -812,9 +874,26 @@ struct UnitLane {
         for (int d = 0; d <= Q; d++) dead |= (a[d] == v);
         fl = dead ? 0 : ((p.unit_fl & 1) | (((p.unit_fl & 2) && (!p.need_inter || inter)) ? 2 : 0));
     }
+    // the same from a wide entry (Q = 1 or 2): plane A holds the nodes, B (needed by the count pass only under the
+    // intermediate-kind rule) the rest
+    __device__ __forceinline__ void load_wide(const LevelParams &p, const int4 A, const int4 B, bool valid) {
+        a[0] = A.x; a[1] = A.y;
+        if (Q >= 2) a[2] = A.z;
+        rel[0] = 0; rel[1] = A.w;
+        if (Q >= 2) rel[2] = B.x;
+        root = B.y; inter = B.z >> 16;
+        int2 nx = make_int2(-1, -1);
+        if (valid && a[Q] >= p.row_lo && a[Q] < p.row_hi) nx = __ldg(p.unit_next + (a[Q] - p.row_lo));
+        has = nx.x >= 0;
+        v = nx.x; r = nx.y;
+        bool dead = !has;
+#pragma unroll
+        for (int d = 0; d <= Q; d++) dead |= (a[d] == v);
+        fl = dead ? 0 : ((p.unit_fl & 1) | (((p.unit_fl & 2) && (!p.need_inter || inter)) ? 2 : 0));
+    }
 };
 
-template <int Q>
+template <int Q, bool WIDE = false>
 __global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __grid_constant__ LevelParams p) {
     __shared__ unsigned long long s_fb[kLv];
     if (overflow_seen(p.ctl)) return;
@@ -822,7 +901,8 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __g
     const int lane = threadIdx.x & 31;
     unsigned long long scanned = 0;
     const unsigned nwarps = gridDim.x * kWarps;
-    const int4 *fq = p.frontier + s_fb[Q];
+    const int4 *fq = p.frontier + s_fb[Q];            // wide: plane A
+    const unsigned long long wstride = WIDE ? wide_stride(c.Fq) : 0ull;
     const int4 none = make_int4(0, 0, 0, 0);
     unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5);
     int4 e_next = ((unsigned long long)tile * kTile + lane < c.Fq) ? fq[(unsigned long long)tile * kTile + lane] : none;
@@ -831,7 +911,13 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __g
         const int4 e = e_next;
         e_next = i2 < c.Fq ? fq[i2] : none;           // the next tile's entries travel while this tile is worked on
         UnitLane<Q> u;
-        u.load(p, s_fb, e, i < c.Fq);
+        if constexpr (WIDE) {
+            int4 B = none;
+            if (p.need_inter && i < c.Fq) B = fq[wstride + i];
+            u.load_wide(p, e, B, i < c.Fq);
+        } else {
+            u.load(p, s_fb, e, i < c.Fq);
+        }
         const int cf = __popc(__ballot_sync(0xffffffffu, u.fl & 1)), ce = __popc(__ballot_sync(0xffffffffu, u.fl & 2));
         scanned += (unsigned long long)__popc(__ballot_sync(0xffffffffu, u.has));
         if (lane == 0) {
@@ -844,7 +930,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __g
     if (lane == 0 && scanned) atomicAdd(&p.ctl->E[p.s], scanned);
 }
 
-template <int Q>
+template <int Q, bool WIDE = false>
 __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __grid_constant__ LevelParams p) {
     extern __shared__ int s_dyn[];                    // per warp: 32 finished rows
     __shared__ unsigned long long s_fb[kLv];
@@ -858,7 +944,8 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
     int *stage = s_dyn + (threadIdx.x >> 5) * (kTile * rl);
     const bool want_rows = !p.count_only && (p.unit_fl & 2);
     const unsigned nwarps = gridDim.x * kWarps;
-    const int4 *fq = p.frontier + s_fb[Q];
+    const int4 *fq = p.frontier + s_fb[Q];            // wide: plane A
+    const unsigned long long wstride = WIDE ? wide_stride(c.Fq) : 0ull;
     const int4 none = make_int4(0, 0, 0, 0);
     unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5);
     int4 e_next = ((unsigned long long)tile * kTile + lane < c.Fq) ? fq[(unsigned long long)tile * kTile + lane] : none;
@@ -873,16 +960,34 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
         const int4 e = e_next;
         e_next = i2 < c.Fq ? fq[i2] : none;           // the next tile's entries travel while this tile is worked on
         UnitLane<Q> u;
-        u.load(p, s_fb, e, valid);
-        // state probes: the header sector of every node of the row, all in flight together
+        int4 wc = none;                               // wide: plane C = (state1, state2, timestamp)
+        int ws0 = -1;
+        if constexpr (WIDE) {
+            int4 B = none;
+            if (valid) {
+                B = fq[wstride + i];
+                if (p.with_states) wc = fq[2 * wstride + i];
+            }
+            ws0 = B.w;
+            u.load_wide(p, e, B, valid);
+        } else {
+            u.load(p, s_fb, e, valid);
+        }
+        // state probes: the header sector of every node of the row, all in flight together (wide entries bring the
+        // answers for the nodes already on the path: only the new last node is probed)
         const bool probe = want_rows && p.with_states && u.has && (!p.need_inter || u.inter);
         long long ts = 0;
         const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
         ulonglong2 h[S + 1];
         if (p.with_states) {
-            if (probe) ts = __ldg(p.seed_ts + u.root);
+            if constexpr (WIDE) {
+                ts = (long long)(((unsigned long long)(unsigned)wc.w << 32) | (unsigned)wc.z);
+                h[S] = ld_head(st, u.v, probe);
+            } else {
+                if (probe) ts = __ldg(p.seed_ts + u.root);
 #pragma unroll
-            for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= Q) ? u.a[d] : u.v, probe);
+                for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= Q) ? u.a[d] : u.v, probe);
+            }
         }
         const unsigned long long run_f = gp.x + __reduce_add_sync(0xffffffffu, mine.x);
         const unsigned long long run_e = gp.y + __reduce_add_sync(0xffffffffu, mine.y);
@@ -905,12 +1010,25 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
             row[2 * S] = u.r;
             if (p.with_states) {
                 unsigned miss = 0;
+                if constexpr (WIDE) {
+                    const int known[3] = {ws0, wc.x, wc.y};
 #pragma unroll
-                for (int d = 0; d <= S; d++) {
+                    for (int d = 0; d <= Q; d++) {
+                        row[2 * S + 1 + d] = known[d];
+                        miss |= (known[d] < 0 ? 1u : 0u) << d;
+                    }
                     int first, cnt;
-                    head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, first, cnt);
-                    row[2 * S + 1 + d] = first;
-                    miss |= (cnt == 0 ? 1u : 0u) << d;
+                    head_finish(st, h[S], u.v, ts, first, cnt);
+                    row[2 * S + 1 + S] = first;
+                    miss |= (cnt == 0 ? 1u : 0u) << S;
+                } else {
+#pragma unroll
+                    for (int d = 0; d <= S; d++) {
+                        int first, cnt;
+                        head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, first, cnt);
+                        row[2 * S + 1 + d] = first;
+                        miss |= (cnt == 0 ? 1u : 0u) << d;
+                    }
                 }
                 row[3 * S + 2] = (int)miss;
             }

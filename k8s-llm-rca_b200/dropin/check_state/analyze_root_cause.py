@@ -4,6 +4,8 @@ The semantic analyser is any object with add_message / run_assistant / wait_get_
 (the reference's OpenAI assistant; here normally the recorded-response stub)."""
 import neo4j
 
+from common.openai_generic_assistant import OpenAIGenericAssistant
+
 IMPORTANT_FIELDS = ("status", "spec", "path", "server", "subsets", "roleRef", "subjects", "rules", "webhooks",
                     "secrets", "data", "metadata")
 
@@ -49,10 +51,9 @@ def ad_hoc_find_entity_name(entity_kind, entity_id, query_executor):
 def check_semantic(state_node, error_message, semanticAnalyzer):
     """One LLM round over the important fields of a STATE node   [reference :223-250]"""
     fields = {k: state_node[k] for k in set(state_node.keys()) & set(IMPORTANT_FIELDS)}
-    prompt = ("\n    The following JSON comes from a %s object. Focus on the 'spec' and 'status' fields\n"
-              "    (or other relevant fields if 'spec' and 'status' are not present) to find some clues for \n"
-              "    the following error message, and ignore the resolution for this error.\n"
-              "    The error message is:\n%s \n\n    The JSON is:\n%s\n    " % (state_node["kind"], error_message, fields))
+    prompt = ("Recorded state of a %s object, as JSON. Check 'spec' and 'status' (other fields when those are absent) for "
+              "anything that explains the error message; do not propose a fix.\nError message:\n%s\nJSON:\n%s\n"
+              % (state_node["kind"], error_message, fields))
     semanticAnalyzer.add_message(prompt)
     semanticAnalyzer.run_assistant()
     return semanticAnalyzer.wait_get_last_k_message(1).data[0].content[0].text.value
@@ -104,6 +105,7 @@ def check_statepath(query_executor, semanticAnalyzer, statepath):
         elif ele["isNative"] == "false":
             entity_kind = ele["tag"]
         entity_id = ele["id"]
+        print(entity_kind, entity_id)
         kinds.append(entity_kind)
         path_clues["%s(%s)" % (entity_kind, entity_id)] = check_states_of_entity(
             entity_kind, entity_id, error_message, timestamp, query_executor, semanticAnalyzer)
@@ -114,3 +116,16 @@ def check_statepath(query_executor, semanticAnalyzer, statepath):
     semanticAnalyzer.run_assistant()
     report = semanticAnalyzer.wait_get_last_k_message(1).data[0].content[0].text.value
     return report, path_clues
+
+
+# ---- LLM plumbing (reference :6-46)
+def setup_state_semantic_analyzer():
+    analyzer = OpenAIGenericAssistant()
+    analyzer.create_assistant("You read the state of k8s objects and relate mistakes in it to an error message.",
+                              "k8s-state-semantic-analyzer", "gpt-4")
+    analyzer.create_thread()
+    print(analyzer.assistant.id)
+    print(analyzer.thread.id)
+    analyzer.add_message("Every entity should have a STATE node for the time of the event; an entity without one does not "
+                         "exist or was never created, which is an error in itself.")
+    return analyzer

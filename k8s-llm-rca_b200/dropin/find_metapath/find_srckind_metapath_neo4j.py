@@ -1,8 +1,12 @@
 """Mirror of the graph half of reference find_metapath/find_srckind_metapath_neo4j.py:63-175.
 
 Same function names, arguments, return values and failure behaviour; the statements sent to the
-executor have the semantics of the reference's (:64-68, :76-84, :95-129).  The LLM half of that
-module (:20-60, :178-240) is out of scope."""
+executor have the semantics of the reference's (:64-68, :76-84, :95-129).  The LLM half of that module (:20-60, :178-240) is out of
+scope: what is here of it is the plumbing the end-to-end driver needs - same
+function names and return shapes, prompts reduced to what a recorded-response assistant keys on."""
+import json
+
+from common.openai_generic_assistant import OpenAIGenericAssistant
 
 KINDS_QUERY = (
     "MATCH (n1) WHERE n1.category IN ['NativeEntity', 'ExternalEntity'] "
@@ -77,3 +81,32 @@ def print_metapath(path):
     for rel in path.relationships:
         print(rel.type, rel["srcKind"], rel["destKind"], rel["key"])
     print("----------------------------------")
+
+
+# ---- LLM plumbing (reference :20-60, :178-240): an assistant that names the destination kind
+def setup_root_cause_locator():
+    locator = OpenAIGenericAssistant()
+    locator.create_assistant("You analyse Kubernetes error messages and name the resource kinds involved.",
+                             "k8s-root-cause-locator", "gpt-4")
+    locator.create_thread()
+    print(locator.assistant.id)
+    print(locator.thread.id)
+    return locator
+
+
+def build_prompt_template(nativeKinds, externalKinds):
+    """Template with the placeholders {involved_object} and {error_message} (reference :200-240)."""
+    return ("Known k8s API resource kinds: " + ", ".join(nativeKinds) + "\nKnown external resource kinds: "
+            + ", ".join(externalKinds) + "\nThe error below was reported on a {involved_object}. Name the kind that "
+            "resolves it (DestinationKind) and the kinds on the way (RelevantResources), both from the lists above, "
+            "as JSON inside a ```json block.\n\n{error_message}\n")
+
+
+def extract_json(message_str):
+    return json.loads(message_str.split("```json")[1].split("```")[0].strip())
+
+
+def find_destKind_relevantResources(errorMessage, srcKind, promptTemplate, rootCauseLocator):
+    rootCauseLocator.add_message(promptTemplate.format(error_message=errorMessage, involved_object=srcKind))
+    rootCauseLocator.run_assistant()
+    return extract_json(rootCauseLocator.wait_get_last_k_message(1).data[0].content[0].text.value)

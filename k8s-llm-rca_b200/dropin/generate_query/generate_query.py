@@ -1,7 +1,9 @@
 """Mirror of the deterministic half of reference generate_query/generate_query.py
 (:46-57, :88-129, :214-266): metapath -> step text -> Cypher text -> instance rows -> rows whose
 destination the event message mentions.  The LLM generator (:18-43, :60-85, :134-211) is out of
-scope; its recorded outputs are ordinary Cypher text and go through run_and_filter_query too."""
+scope; its recorded outputs are ordinary Cypher text and go through run_and_filter_query too - the
+functions that talk to it are kept as plumbing for the end-to-end driver (names and return shapes)."""
+from common.openai_generic_assistant import OpenAIGenericAssistant
 
 FIXED_STEPS = (("HasEvent", "Event", "EVENT", "metadata_uid"),)
 
@@ -66,3 +68,31 @@ def message_compatible(record):
         if dest["isNative"] == "false":
             kind_key = "tag"
     return (dest[name_key] in message) or (dest[kind_key] in message)
+
+
+# ---- LLM plumbing (reference :18-43, :60-85)
+def setup_cypher_generator():
+    gen = OpenAIGenericAssistant()
+    gen.create_assistant("You write Cypher for Neo4j.", "cypher-query-generator", "gpt-4")
+    gen.create_thread()
+    print(gen.assistant.id)
+    print(gen.thread.id)
+    gen.add_message("Each line 'relType, srcKind, destKind, key;' of a metapath becomes one MATCH "
+                    "(a:srcKind)-[r:relType]->(b:destKind) WHERE r.key = key; the EVENT node is found by its message.")
+    return gen
+
+
+def extract_cypher(message_str):
+    return message_str.split("```cypher")[1].split("```")[0].strip()
+
+
+def generate_cypher_query(metapath_str, error_message, cypherQueryGenerator):
+    cypherQueryGenerator.add_message(
+        "Write the Cypher query for this metapath, inside a ```cypher block, keeping every (srcKind)-[rel]->(destKind) "
+        "in the given direction.\nthe provided metapath is:\n%s\nthe error message to filtering is:\n%s\n"
+        % (metapath_str, error_message))
+    print("run assistant")
+    cypherQueryGenerator.run_assistant()
+    query = extract_cypher(cypherQueryGenerator.wait_get_last_k_message(1).data[0].content[0].text.value)
+    print("the generated cypher query is :\n %s" % query)
+    return query

@@ -13,6 +13,15 @@ from . import exceptions, graph  # noqa: F401
 
 __version__ = "0.0-rca-b200-shim"
 
+_factory = _Executor
+
+
+def set_executor_factory(factory=None):
+    """What `GraphDatabase.driver(uri)` opens: `factory(uri, user, password)` -> an object with run_query / close.
+    Default (and what None restores): the GPU executor."""
+    global _factory
+    _factory = factory or _Executor
+
 
 class Result(list):
     """The driver's Result is a cursor; the reference immediately does list(result)."""
@@ -50,7 +59,7 @@ class Driver:
     def _executor(self):
         if self._ex is None:
             try:
-                self._ex = _Executor(self._uri, None, None)
+                self._ex = _factory(self._uri, None, None)
             except Exception as exc:
                 raise exceptions.ServiceUnavailable(str(exc)) from exc
         return self._ex

@@ -4,7 +4,7 @@
         .run_query(query, parameters=None)     # -> list[Record], fully materialised
         .close()
 
-`uri` names a snapshot instead of a bolt address:
+`uri` names a snapshot instead of a bolt address (or is an alias of one: register_uri_alias):
     snapshot://<name>            a Snapshot registered in this process with register_snapshot()
     snapshot://<name>#metagraph  the schema graph derived from it (what the reference keeps in its
                                  second Neo4j database, test_all.py:21)
@@ -34,13 +34,26 @@ class ServiceUnavailable(Exception):
 
 
 _REGISTRY: dict = {}
+_ALIASES: dict = {}
 
 
 def register_snapshot(name: str, snap) -> None:
     _REGISTRY[name] = snap
 
 
+def register_uri_alias(uri: str, target: str) -> None:
+    """Let a uri the caller's code has hard-wired - the reference's drivers open
+    `bolt://10.1.0.176:7687` (metagraph) and `bolt://10.1.0.174:7687` (state graph), test_all.py:21-22 -
+    stand for a snapshot uri: register_uri_alias("bolt://10.1.0.174:7687", "snapshot://cluster")."""
+    _ALIASES[uri] = target
+
+
+def unregister_uri_alias(uri: str) -> None:
+    _ALIASES.pop(uri, None)
+
+
 def resolve_snapshot(uri: str):
+    uri = _ALIASES.get(uri, uri)
     u = urlparse(uri)
     if u.scheme == "snapshot":
         name = u.netloc or u.path.lstrip("/")

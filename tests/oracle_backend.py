@@ -80,3 +80,11 @@ def record_key(rec):
         else:
             out.append(("val", v))
     return tuple(out)
+
+
+def oracle_executor_factory(uri, user=None, password=None):
+    """For neo4j.set_executor_factory (the shim): the uri resolves as usual, the executor runs on the oracle."""
+    from k8s_llm_rca_b200.executor import resolve_snapshot
+    ex = oracle_executor(resolve_snapshot(uri))
+    ex.snapshot = resolve_snapshot(uri)
+    return ex

@@ -22,12 +22,22 @@ def eng(snap_small):
 
 
 def _both(eng, plan, seeds, ts=None):
+    """(unit steps on, unit steps off).  With unit steps on the plan also runs without wide entries
+    (rca_set_wide_entries): the two ways to hand paths to a final unit level must give the same bytes."""
     out = []
     for on in (True, False):
         eng.set_unit_steps(on)
         res = eng.expand(plan, seeds, ts)
         rows = None if res.count_only else {s: res.rows(s).copy() for s in range(1, res.levels + 1)}
         out.append((res, rows))
+        if on:
+            eng.set_wide_entries(True)
+            wide = eng.expand(plan, seeds, ts)
+            assert wide.emitted == res.emitted and wide.frontier == res.frontier and wide.scanned == res.scanned
+            if rows is not None:
+                for s in rows:
+                    assert np.array_equal(wide.rows(s), rows[s]), ("wide entries change level", s)
+            eng.set_wide_entries(False)
     eng.set_unit_steps(True)
     return out
 
