@@ -547,12 +547,14 @@ def main():
             ms = sum(a.elapsed_time(b) for a, b in evs)
             return ms, inst, launches, per_level
 
-        def timed_e2e_pipelined(steps):
+        def timed_e2e_pipelined(steps, wl=None):
             """End to end with the copy-out of step k travelling while step k+1 runs: the engine alternates between
             two output arenas (rca_set_double_buffer) and the rows leave through rca_result_copy_async.  Every step
             still uploads its seeds from pinned host memory and downloads all of its rows; ONE pair of events
-            brackets all steps (L2 flushes included)."""
-            total_words = sum(r.emitted[s] * r.row_len[s] for _, r in res0 for s in range(1, r.levels + 1))
+            brackets all steps (L2 flushes included).  wl: the workload (default: the headline one)."""
+            wl = wl or w
+            sized = res0 if wl is w else wl.run(eng, d_pods, d_ev, d_ts)[1]
+            total_words = sum(r.emitted[s] * r.row_len[s] for _, r in sized for s in range(1, r.levels + 1))
             h_all = torch.empty(total_words + 64, dtype=torch.int32).pin_memory().numpy()
             cursor = [0]
 
@@ -568,7 +570,7 @@ def main():
                         d2h[0] += n * 4
 
             def one():
-                tot, _ = w.run(eng, h_pods.numpy(), h_ev.numpy(), h_ts.numpy(), fetch=fetch_async)
+                tot, _ = wl.run(eng, h_pods.numpy(), h_ev.numpy(), h_ts.numpy(), fetch=fetch_async)
                 if world > 1:
                     if peer_ok:
                         eng.peer_allgather(tot, wait=False)
@@ -614,6 +616,12 @@ def main():
         ms_serial, inst_serial, _, _ = timed(False, args.steps)     # one step after the other: copy-out, then the next step
         barrier()
         ms_e2e, inst_e2e, wall_e2e = timed_e2e_pipelined(args.steps)
+        d2h_full = d2h[0]
+        barrier()
+        # the same end to end with mask-only rows (RCA_STATES_MASK): the missing-state mask instead of a state id per node
+        w_mask = workloads.Config3(snap=w.snap, with_states="mask")
+        ms_e2e_m, inst_e2e_m, _ = timed_e2e_pipelined(args.steps, w_mask)
+        d2h_mask, d2h[0] = d2h[0], d2h_full
         if peer_ok:                                                              # what the last exchange delivered
             last = last_counts[0]
             assert len(last) == world and (last > 0).all(), f"count exchange returned {last}"
@@ -622,13 +630,13 @@ def main():
         clocks = sampler.stop() if rank == 0 else None
 
     # max over ranks of the device time, sum over ranks of the instances
-    red = torch.tensor([ms_res, ms_e2e, ms_serial], dtype=torch.float64, device=dev)
-    tot = torch.tensor([inst_res, inst_e2e], dtype=torch.int64, device=dev)
+    red = torch.tensor([ms_res, ms_e2e, ms_serial, ms_e2e_m], dtype=torch.float64, device=dev)
+    tot = torch.tensor([inst_res, inst_e2e, inst_e2e_m], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(red, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    ms_res, ms_e2e, ms_serial = red.tolist()
-    inst_res, inst_e2e = tot.tolist()
+    ms_res, ms_e2e, ms_serial, ms_e2e_m = red.tolist()
+    inst_res, inst_e2e, inst_e2e_m = tot.tolist()
 
     # ---- config 5: per-incident RCA graph latency (LLM answers recorded), one by one and batched
     latency = None
@@ -703,7 +711,12 @@ def main():
                     "how": "every step: seeds host->device from pinned memory, rca_expand_many, ALL rows device->host into "
                            "pinned memory; the copy-out of a step overlaps the next step (two output arenas, "
                            "rca_result_copy_async); one pair of CUDA events around all steps, L2 flushes included",
-                    "serial_ms_per_step": ms_serial / args.steps},
+                    "serial_ms_per_step": ms_serial / args.steps,
+                    "mask_rows": {"value": inst_e2e_m / (ms_e2e_m * 1e-3), "unit": "instances/s",
+                                  "ms_per_step": ms_e2e_m / args.steps, "d2h_bytes_per_step": int(d2h_mask // args.steps),
+                                  "d2h_GBps_per_rank": (d2h_mask / args.steps) / (ms_e2e_m / args.steps * 1e-3) / 1e9,
+                                  "what": "the same step with with_states = RCA_STATES_MASK: rows carry the missing-state mask, "
+                                          "not a state id per node (12 -> 8 words per three-hop row); same copies, same timing"}},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "dram_frac": dram_frac, "traffic_source": traffic_note,

@@ -35,6 +35,10 @@ extern "C" {
                                    test_generate_query.py:38                                   */
 #define RCA_DIR_UND 2           /* (a)-[r]-(b)                                                 */
 
+#define RCA_STATES_NONE 0
+#define RCA_STATES_FULL 1
+#define RCA_STATES_MASK 2
+
 #define RCA_PLAN_VARLEN 0       /* find_metapath/find_srckind_metapath_neo4j.py:95-129         */
 #define RCA_PLAN_CHAIN 1        /* generate_query/generate_query.py:241-260                    */
 
@@ -94,7 +98,11 @@ typedef struct {
     uint8_t kind_inter[RCA_MAX_KINDS];  /* 1: kind is in $intermediateKinds                      */
     /* --- both --- */
     int32_t with_states;            /* fuse the HasState predicate (analyze_root_cause.py:70-79)
-                                       into emission: rows grow by (len+1) state ids + 1 mask    */
+                                       into emission.  RCA_STATES_FULL: rows grow by (len+1) state
+                                       ids + 1 mask; RCA_STATES_MASK: by the mask alone - bit d set =
+                                       node d of the row has no state at the seed's time, which is
+                                       what the reference's check branches on (:180) - a third fewer
+                                       bytes to carry to the host                                 */
     int32_t count_only;             /* count path instances per length but do not write rows (no
                                        output arena needed; for very large enumerations)         */
 } rca_plan_t;
@@ -174,7 +182,7 @@ int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t n_plans, c
                     const int64_t *n_seeds, const int64_t *const *seed_ts, int seeds_on_device, rca_stats_t *stats);
 int rca_result_select(rca_engine_t *e, int32_t plan_index);
 /* device pointer / shape of the rows of paths with `level` relationships.
- * Row = (level+1) node ids, level relationship ids [, (level+1) state ids, 1 missing-state mask] */
+ * Row = (level+1) node ids, level relationship ids [, (level+1) state ids][, 1 missing-state mask] */
 int rca_result_level(const rca_engine_t *e, int level, const int32_t **dev_rows, int64_t *n_rows,
                      int32_t *row_len);
 /* replaces records = list(result), neo4j_query_executor.py:21: copy one level's rows to the host */

@@ -495,6 +495,7 @@ static bool arrival_reach(const rca_engine *e, const rca_plan_t *pl, int L, unsi
 }
 
 static int validate_plan(rca_engine *e, const rca_plan_t *pl) {
+    if (pl->with_states < 0 || pl->with_states > RCA_STATES_MASK) return fail(e, RCA_ERR_ARG, "plan: with_states %d not in 0..2", pl->with_states);
     if (pl->kind == RCA_PLAN_CHAIN) {
         if (pl->n_steps < 1 || pl->n_steps > RCA_MAX_HOPS) return fail(e, RCA_ERR_ARG, "chain plan: n_steps %d not in 1..%d", pl->n_steps, RCA_MAX_HOPS);
         int cur = -1;
@@ -518,7 +519,9 @@ static int validate_plan(rca_engine *e, const rca_plan_t *pl) {
     return RCA_OK;
 }
 
-static int row_len_of(const rca_plan_t *pl, int s) { return pl->with_states ? 3 * s + 3 : 2 * s + 1; }
+static int row_len_of(const rca_plan_t *pl, int s) {
+    return pl->with_states == RCA_STATES_FULL ? 3 * s + 3 : pl->with_states == RCA_STATES_MASK ? 2 * s + 2 : 2 * s + 1;
+}
 
 // ---- kernel dispatch: one instantiation per (adjacency format, predicate mode, known depth)
 typedef void (*level_kernel_t)(const LevelParams);

@@ -125,7 +125,7 @@ struct LevelParams {
     int sub;                          // a level may run as several typed sub-launches (0, 1, ..): see rca_b200.cu
     int chain_flag;                   // chain plans: 1 = every candidate continues, 2 = every candidate is a row
     int need_inter;                   // emit only if an interior node so far is of an intermediate kind
-    int with_states;
+    int with_states;                  // 1: rows carry a state id per node and the missing mask, 2: the mask alone
     int count_only;                   // rows are counted, never written
     int row_len;                      // words per emitted row at this level
     int row_len_lv[RCA_MAX_HOPS + 1]; // ... and at every level (arena bases are sums over earlier levels)
@@ -515,7 +515,7 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
                 int first, cnt;
                 head_finish(st, h[d], (d <= q) ? w.anc_n[d * kTile + o] : v, ts, first, cnt);
                 if (active) {
-                    row[2 * s + 1 + d] = first;
+                    if (p.with_states == 1) row[2 * s + 1 + d] = first;
                     miss |= (cnt == 0 ? 1u : 0u) << d;
                 }
             }
@@ -530,12 +530,12 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
                 first = __shfl_sync(0xffffffffu, first, leader);
                 cnt = __shfl_sync(0xffffffffu, cnt, leader);
                 if (active) {
-                    row[2 * s + 1 + d] = first;
+                    if (p.with_states == 1) row[2 * s + 1 + d] = first;
                     miss |= (cnt == 0 ? 1u : 0u) << d;
                 }
             }
         }
-        if (active) row[3 * s + 2] = (int)miss;
+        if (active) row[p.with_states == 1 ? 3 * s + 2 : 2 * s + 1] = (int)miss;        // compact rows: the mask alone
     }
     __syncwarp();
     int *dst = p.out + w0;
@@ -1014,23 +1014,23 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
                     const int known[3] = {ws0, wc.x, wc.y};
 #pragma unroll
                     for (int d = 0; d <= Q; d++) {
-                        row[2 * S + 1 + d] = known[d];
+                        if (p.with_states == 1) row[2 * S + 1 + d] = known[d];
                         miss |= (known[d] < 0 ? 1u : 0u) << d;
                     }
                     int first, cnt;
                     head_finish(st, h[S], u.v, ts, first, cnt);
-                    row[2 * S + 1 + S] = first;
+                    if (p.with_states == 1) row[2 * S + 1 + S] = first;
                     miss |= (cnt == 0 ? 1u : 0u) << S;
                 } else {
 #pragma unroll
                     for (int d = 0; d <= S; d++) {
                         int first, cnt;
                         head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, first, cnt);
-                        row[2 * S + 1 + d] = first;
+                        if (p.with_states == 1) row[2 * S + 1 + d] = first;
                         miss |= (cnt == 0 ? 1u : 0u) << d;
                     }
                 }
-                row[3 * S + 2] = (int)miss;
+                row[p.with_states == 1 ? 3 * S + 2 : 2 * S + 1] = (int)miss;
             }
         }
         __syncwarp();
@@ -1227,10 +1227,10 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
                         if (k > L) continue;
                         int first, cnt;
                         head_finish(st, h[k], node[k], ts, first, cnt);
-                        row[2 * L + 1 + k] = first;
+                        if (p.with_states == 1) row[2 * L + 1 + k] = first;
                         miss |= (cnt == 0 ? 1u : 0u) << k;
                     }
-                    row[3 * L + 2] = (int)miss;
+                    row[p.with_states == 1 ? 3 * L + 2 : 2 * L + 1] = (int)miss;
                 }
             }
             rows++;
@@ -1434,15 +1434,15 @@ __device__ __forceinline__ void chain_line_body(const ChainParams &p) {
                 if (k >= L) continue;
                 row[k] = node[k];
                 if (k < L - 1) row[L + 1 + k] = rel[k];
-                if (probe) row[2 * L + 1 + k] = first[k];
+                if (probe && p.with_states == 1) row[2 * L + 1 + k] = first[k];
             }
             row[L] = v;
             row[2 * L] = r;
             if (probe) {
                 int fv, cnt;
                 state_probe(st, v, ts, fv, cnt);
-                row[3 * L + 1] = fv;
-                row[3 * L + 2] = (int)(miss0 | ((cnt == 0 ? 1u : 0u) << L));
+                if (p.with_states == 1) row[3 * L + 1] = fv;
+                row[p.with_states == 1 ? 3 * L + 2 : 2 * L + 1] = (int)(miss0 | ((cnt == 0 ? 1u : 0u) << L));
             }
         }
     }

@@ -151,7 +151,7 @@ def varlen_plan(direction, max_hops, min_hops=1, dest_kind=-1, excl_kinds=(), in
         p.kind_excl[int(k)] = 1
     for k in inter_kinds:
         p.kind_inter[int(k)] = 1
-    p.with_states = int(bool(with_states))
+    p.with_states = _states_mode(with_states)
     p.count_only = int(bool(count_only))
     return p
 
@@ -169,9 +169,20 @@ def chain_plan(etypes, dirs, with_states=False, count_only=False) -> PlanDesc:
     for i in range(MAX_HOPS + 1):
         p.pos_kind[i] = -1
     p.dest_kind = -1
-    p.with_states = int(bool(with_states))
+    p.with_states = _states_mode(with_states)
     p.count_only = int(bool(count_only))
     return p
+
+
+STATES_NONE, STATES_FULL, STATES_MASK = 0, 1, 2
+
+
+def _states_mode(with_states) -> int:
+    """False / True / "mask" (or the RCA_STATES_* numbers): no state columns, a state id per node plus the missing
+    mask, the mask alone."""
+    if with_states in ("mask", STATES_MASK) and with_states is not True:
+        return STATES_MASK
+    return STATES_FULL if with_states else STATES_NONE
 
 
 def _dev_ptr(x):
@@ -260,8 +271,10 @@ class ExpandResult:
         12 F_{s-1} + 4 E_s + 4 (2s+1) N_s, plus, with the fused state filter,
         (s+1) N_s (8 + 16 I + 5) with I = 1 interval inspected per node."""
         b = 12 * self.frontier[s - 1] + 4 * self.scanned[s] + 4 * (2 * s + 1) * self.emitted[s]
-        if self.row_len[s] > 2 * s + 1:
+        if self.row_len[s] == 3 * s + 3:
             b += (s + 1) * self.emitted[s] * (8 + 16 + 5)
+        elif self.row_len[s] == 2 * s + 2:               # mask-only rows: no state id written, one mask word per row
+            b += (s + 1) * self.emitted[s] * (8 + 16) + 4 * self.emitted[s]
         return b
 
     def algorithmic_bytes(self) -> int:
