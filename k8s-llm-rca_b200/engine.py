@@ -488,6 +488,46 @@ class Engine:
                 hits[i] = by_u[u]
         return first[idx], hits
 
+    def contains_first(self, patterns):
+        """Batched `message CONTAINS pattern`, the canonical 'LIMIT 1' answer only: the lowest node id whose message
+        contains each pattern, or -1 (no list of all matches is built or copied)."""
+        uniq = {}
+        idx = np.fromiter((uniq.setdefault(t, len(uniq)) for t in patterns), dtype=np.int64, count=len(patterns))
+        enc = [t.encode("utf-8") for t in uniq]
+        off = np.zeros(len(enc) + 1, dtype=np.int64)
+        np.cumsum(np.fromiter(map(len, enc), dtype=np.int64, count=len(enc)), out=off[1:])
+        blob = np.frombuffer(b"".join(enc), dtype=np.uint8) if off[-1] else np.zeros(1, np.uint8)
+        first = np.empty(len(enc), np.int32)
+        n = C.c_int64(0)
+        if len(enc):
+            self._ck(self.lib.rca_text_contains(self.h, blob.ctypes.data, off.ctypes.data, len(enc), first.ctypes.data,
+                                                None, 0, C.byref(n)))
+        return first[idx]
+
+    def message_index(self, nodes):
+        """Index in the loaded message arena of the messages of `nodes` (node ids given to text_load)."""
+        nodes = np.asarray(nodes, dtype=np.int32)
+        idx = np.searchsorted(self._text_nodes, nodes)
+        if len(nodes) and ((idx >= len(self._text_nodes)).any() or (self._text_nodes[np.minimum(idx, len(self._text_nodes) - 1)] != nodes).any()):
+            raise ValueError("a node has no message in the loaded arena")
+        return np.ascontiguousarray(idx, dtype=np.int32)
+
+    def match_pairs_idx(self, msg_index, needle_a, needle_b, needle_blob, needle_off):
+        """rca_text_match_pairs on prepared arrays: message indices (message_index), two needle indices per pair
+        (-1: none) into an arena given as (uint8 bytes, int64 offsets).  -> bool array."""
+        n = len(msg_index)
+        if n == 0:
+            return np.zeros(0, dtype=bool)
+        mi = np.ascontiguousarray(msg_index, dtype=np.int32)
+        na = np.ascontiguousarray(needle_a, dtype=np.int32)
+        nb = np.ascontiguousarray(needle_b, dtype=np.int32)
+        blob = np.ascontiguousarray(needle_blob, dtype=np.uint8)
+        off = np.ascontiguousarray(needle_off, dtype=np.int64)
+        out = np.empty(n, np.uint8)
+        self._ck(self.lib.rca_text_match_pairs(self.h, blob.ctypes.data, off.ctypes.data, len(off) - 1, mi.ctypes.data,
+                                               na.ctypes.data, nb.ctypes.data, n, out.ctypes.data))
+        return out.astype(bool)
+
     # -- count exchange over peer memory (include/rca_b200.h: rca_peer_*)
     PEER_HANDLE_BYTES = 64
 

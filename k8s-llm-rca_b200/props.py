@@ -73,6 +73,15 @@ class BaseProps:
         lo, hi = self.snap.kind_range(kind_idx)
         return [v for v in range(lo, hi) if self.node_props(v).get("id") == id_str]
 
+    def column(self, kind_idx, key):
+        """The property `key` of every node of kind `kind_idx`, in node order (None where a node lacks it)."""
+        lo, hi = self.snap.kind_range(kind_idx)
+        return [self.node_props(v).get(key) for v in range(lo, hi)]
+
+    def event_times_ms(self, nodes):
+        """`timestamp` of the given EVENT nodes as int64 milliseconds."""
+        return np.array([ts_to_ms(self.node_props(int(v))["timestamp"]) for v in np.asarray(nodes).tolist()], dtype=np.int64)
+
     def messages(self):
         """(node ids, list of message strings) over every node that has a `message`."""
         ids, msgs = [], []

@@ -58,6 +58,7 @@ class IncidentReplayer:
         self.eng = state_executor.backend.engine
         self.dest_fn = dest_fn
         self._mp_cache = {}
+        self._needle_cache, self._chain_cache = {}, {}
         s = self.snap
         L = s.label_index
         self._et_has_event = s.find_etypes("HasEvent", L("Event"), L("EVENT"), "metadata_uid")[0]
@@ -112,87 +113,179 @@ class IncidentReplayer:
         return self._mp_cache[key]
 
     def run_batch(self, messages):
+        """The batch as a list of per-incident dictionaries (the form run_one returns)."""
+        return self.run_batch_arrays(messages).as_dicts([k.name for k in self.snap.kinds])
+
+    # per kind: the arena of the names the message filter looks for (generate_query.py:104-129), built once
+    def _needles(self, k):
+        hit = self._needle_cache.get(k)
+        if hit is None:
+            s = self.snap
+            nk, kk = _name_key(s.props.kind_const_props(k))
+            names = s.props.column(k, nk)
+            kind_text = s.props.kind_const_props(k).get(kk)
+            if kind_text is None:
+                kinds = s.props.column(k, kk)
+                kind_text = kinds[0] if kinds and all(x == kinds[0] for x in kinds) else None
+            none = np.fromiter((x is None for x in names), dtype=bool, count=len(names))
+            enc = [(x or "").encode("utf-8") for x in names] + [(kind_text or "").encode("utf-8")]
+            off = np.zeros(len(enc) + 1, dtype=np.int64)
+            np.cumsum(np.fromiter(map(len, enc), dtype=np.int64, count=len(enc)), out=off[1:])
+            blob = np.frombuffer(b"".join(enc), dtype=np.uint8).copy() if off[-1] else np.zeros(1, np.uint8)
+            hit = self._needle_cache[k] = (blob, off, none, kind_text is None)
+        return hit
+
+    def _chain_of(self, src, mp):
+        """(edge types, directions) of the instance query of metapath `mp` from source kind `src`: the two event steps,
+        then one step per metagraph relationship in the direction the walk crosses it."""
+        key = (src, mp.key())
+        hit = self._chain_cache.get(key)
+        if hit is None:
+            s = self.snap
+            ets = [self._et_has_event, s.find_etypes("ReferInternal", s.label_index("Event"), s.label_index(src),
+                                                      "involvedObject_uid")[0]]
+            dirs = ["in", "out"]
+            cur = s.label_index(src)
+            for rel in mp.relationships:                          # metagraph relationship -> state-graph edge type
+                a, b = s.label_index(rel["srcKind"]), s.label_index(rel["destKind"])
+                ets.append(s.find_etypes(rel.type, a, b, rel["key"])[0])
+                dirs.append("out" if a == cur else "in")
+                cur = b if a == cur else a
+            hit = self._chain_cache[key] = (ets, dirs, cur)
+        return hit
+
+    def run_batch_arrays(self, messages):
+        """The same work for many incidents at once, kept in arrays end to end: one CONTAINS scan for all messages, the
+        source kinds from one submission of two-step chains, then per (source, destination) group ONE submission of
+        its metapaths' instance queries over the group's events with the state predicate fused in (mask rows), and
+        the message filter of the group's rows as one launch over a per-kind name arena built once per snapshot.
+        No per-row Python.  -> BatchResult."""
         s, eng = self.snap, self.eng
         n = len(messages)
+        t_start = time.perf_counter()
         if not self.sx.backend._text_loaded:
             self.sx.backend.contains([])
-        first, _ = eng.contains(list(messages))                     # lowest EVENT node per message ('LIMIT 1')
-        evt = first.astype(np.int32)
-        results = [{"srcKind": None, "metapaths": [], "rows": [], "missing": []} for _ in range(n)]
+        evt = eng.contains_first(messages).astype(np.int32)             # lowest EVENT node per message ('LIMIT 1')
+        res = BatchResult(n, evt)
         ok = np.nonzero(evt >= 0)[0]
-        useeds = np.unique(evt[ok])
-        # S2 for the whole batch: EVENT <-HasEvent- Event -involvedObject-> X, one chain per edge type
-        obj_of, kind_of = {}, {}
-        for t in self._et_involved:
-            rows = eng.expand(E.chain_plan([self._et_has_event, t], ["in", "out"]), useeds).rows(2)
-            kname = s.kinds[s.etypes[t].dst_kind].name
-            for e_, o in zip(rows[:, 0].tolist(), rows[:, 2].tolist()):
-                if e_ not in obj_of:                               # first edge type wins, like records[0] of S2
-                    obj_of[e_], kind_of[e_] = o, kname
-        groups = {}
-        for i in ok.tolist():
-            e_ = int(evt[i])
-            if e_ not in kind_of:
+        if len(ok) == 0:
+            return res
+        uev = np.unique(evt[ok])                                        # everything below is per distinct event
+        # S2 for the whole batch: EVENT <-HasEvent- Event -involvedObject-> X, one chain per edge type, one submission
+        plans = [E.chain_plan([self._et_has_event, t], ["in", "out"]) for t in self._et_involved]
+        src_kind = np.full(len(uev), -1, np.int32)
+        for t, r in zip(self._et_involved, eng.expand_many(plans, [uev] * len(plans))):
+            rows = r.rows(2)
+            if len(rows) == 0:
                 continue
-            src = kind_of[e_]
-            dest, inter = self.dest_fn(messages[i], src)
-            results[i]["srcKind"] = src
-            groups.setdefault((src, dest, tuple(inter)), []).append(i)
-        cand = []                                                   # (incident, row, destination name, destination kind)
-        for (src, dest, inter), members in groups.items():
+            first = np.unique(rows[:, 0], return_index=True)[0]         # one row per event is enough: the kind is the type's
+            at = np.searchsorted(uev, first)
+            free = src_kind[at] < 0                                     # first edge type wins, like records[0] of S2
+            src_kind[at[free]] = s.etypes[t].dst_kind
+        # destination kind per distinct event (recorded answer), groups of events by (source, destination, waypoints)
+        pos = np.searchsorted(uev, evt[ok])
+        k_inc = src_kind[pos]                                           # source kind of every incident with an event
+        res.src_kind[ok] = k_inc
+        have = k_inc >= 0
+        ev_first, first_at = np.unique(evt[ok][have], return_index=True)
+        inc_first = ok[have][first_at]                                  # one incident (its message) per distinct event
+        names = [k.name for k in s.kinds]
+        ev_group, group_ids = {}, {}
+        gid_of_uev = np.full(len(uev), -1, np.int32)
+        for e_, i, k in zip(ev_first.tolist(), inc_first.tolist(), src_kind[np.searchsorted(uev, ev_first)].tolist()):
+            dest, inter = self.dest_fn(messages[i], names[k])
+            g = (names[k], dest, tuple(inter))
+            gid = group_ids.setdefault(g, len(group_ids))
+            ev_group.setdefault(g, []).append(e_)
+        for g, evs in ev_group.items():
+            gid_of_uev[np.searchsorted(uev, np.asarray(evs, dtype=np.int32))] = group_ids[g]
+        res.groups = list(group_ids)
+        res.gid = np.full(n, -1, np.int32)
+        res.gid[ok] = gid_of_uev[pos]
+        for group, evs in ev_group.items():
+            src, dest, inter = group
             mps = self._metapaths(src, dest, list(inter))
-            seeds = np.unique(evt[members])
-            ts_ms = np.array([ts_to_ms(s.props.node_props(int(v))["timestamp"]) for v in seeds.tolist()], dtype=np.int64)
-            by_evt = {}
-            for mp in mps:
-                ets = [self._et_has_event, s.find_etypes("ReferInternal", s.label_index("Event"), s.label_index(src),
-                                                          "involvedObject_uid")[0]]
-                dirs = ["in", "out"]
-                cur = s.label_index(src)
-                for rel in mp.relationships:                      # metagraph relationship -> state-graph edge type
-                    a, b = s.label_index(rel["srcKind"]), s.label_index(rel["destKind"])
-                    t = s.find_etypes(rel.type, a, b, rel["key"])[0]
-                    ets.append(t)
-                    dirs.append("out" if a == cur else "in")
-                    cur = b if a == cur else a
+            res.metapaths[group] = [p.key() for p in mps]
+            seeds = np.array(sorted(evs), dtype=np.int32)
+            ts_ms = s.props.event_times_ms(seeds)
+            chains = [self._chain_of(src, mp) for mp in mps]
+            plans = [E.chain_plan(ets, dirs, with_states="mask") for ets, dirs, _ in chains]
+            outs = eng.expand_many(plans, [seeds] * len(plans), [ts_ms] * len(plans)) if plans else []
+            for mp, (ets, dirs, dk), r in zip(mps, chains, outs):
                 L = len(ets)
-                rows = eng.expand(E.chain_plan(ets, dirs, with_states=True), seeds, ts_ms).rows(L)
-                # message filter (generate_query.py:104-129): destination named in the message
-                dprops = {}
-                for r in rows.tolist():
-                    e_, d = r[0], r[L]
-                    if d not in dprops:
-                        p = s.props.node_props(d)
-                        nk, kk = _name_key(p)
-                        dprops[d] = (p[nk], p[kk])
-                    by_evt.setdefault(e_, []).append((mp.key(), r, dprops[d]))
-            for i in members:
-                results[i]["metapaths"] = [p.key() for p in mps]
-                for mpk, r, (dname, dkind) in by_evt.get(int(evt[i]), []):
-                    if dname is None or dkind is None:       # the reference's `None in message`
-                        raise TypeError("'in <string>' requires string as left operand, not NoneType")
-                    cand.append((i, r, dname, dkind))
-        # message filter (generate_query.py:104-129) for every row of every incident in one launch: the
-        # destination's name or kind must occur in the EVENT's message
-        keep = eng.match_pairs([int(evt[c[0]]) for c in cand], [c[2] for c in cand], [c[3] for c in cand])
-        for (i, r, _, _), ok in zip(cand, keep.tolist()):
-            if not ok:
-                continue
-            res = results[i]
-            L = (len(r) - 2) // 3
-            # column order of the instance query's RETURN: evt, r1, n1, r2, n2, ... (aliases by kind)
-            cols = [r[0]]
-            for k in range(1, L + 1):
-                cols += [r[L + k], r[k]]
-            miss_mask = r[3 * L + 2]
-            missing = tuple(r[k] for k in range(2, L + 1) if (miss_mask >> k) & 1)
-            res["rows"].append(tuple(cols))
-            res["missing"].append(missing)
-        for res in results:
-            order = sorted(range(len(res["rows"])), key=lambda k: res["rows"][k])
-            res["rows"] = [res["rows"][k] for k in order]
-            res["missing"] = [res["missing"][k] for k in order]
-        return results
+                rows = r.rows(L)
+                if len(rows) == 0:
+                    continue
+                # message filter (generate_query.py:104-129): the destination's name, or its kind, occurs in the message
+                blob, off, none, no_kind = self._needles(dk)
+                d_local = rows[:, L] - int(s.kind_start[dk])
+                if no_kind or none[d_local].any():                      # the reference's `None in message`
+                    raise TypeError("'in <string>' requires string as left operand, not NoneType")
+                keep = eng.match_pairs_idx(eng.message_index(rows[:, 0]), d_local, np.full(len(rows), len(off) - 2, np.int32),
+                                           blob, off)
+                rows = rows[keep]
+                if len(rows) == 0:
+                    continue
+                # column order of the instance query's RETURN: evt, r1, n1, r2, n2, ... (aliases by kind)
+                perm = [0] + [c for k in range(1, L + 1) for c in (L + k, k)]
+                res.blocks.append(Block(group, mp.key(), L, rows[:, 0].copy(), np.ascontiguousarray(rows[:, perm]),
+                                        rows[:, 2 * L + 1].copy()))
+            res.group_done_ms[group] = (time.perf_counter() - t_start) * 1e3
+        res.finish()
+        return res
+
+
+class Block:
+    """Filtered instance rows of one (group, metapath): `evt` the seed EVENT of each row, `rows` in the RETURN order of
+    the instance query (evt, r1, n1, r2, n2, ...), `miss` the missing-state mask over path positions."""
+    __slots__ = ("group", "mp_key", "L", "evt", "rows", "miss")
+
+    def __init__(self, group, mp_key, L, evt, rows, miss):
+        self.group, self.mp_key, self.L, self.evt, self.rows, self.miss = group, mp_key, L, evt, rows, miss
+
+
+class BatchResult:
+    def __init__(self, n, evt):
+        self.n, self.evt = n, evt
+        self.src_kind = np.full(n, -1, np.int32)      # kind index of the involved object, -1: no such event / object
+        self.groups = []                  # (source kind, destination kind, waypoints), by group id
+        self.gid = np.full(n, -1, np.int32)
+        self.metapaths = {}               # group -> metapath keys
+        self.group_done_ms = {}
+        self.blocks = []
+        self.done_ms = np.zeros(n)
+        self.kind_names = None
+
+    def finish(self):
+        """Per-incident completion time: when the group its event belongs to was finished."""
+        t = np.array([self.group_done_ms.get(g, 0.0) for g in self.groups] + [0.0])
+        self.done_ms = t[self.gid]
+
+    @property
+    def n_rows(self):
+        """Instance rows over all incidents (an event several incidents share counts once per incident)."""
+        if not (self.evt >= 0).any():
+            return 0
+        cnt = np.bincount(self.evt[self.evt >= 0])
+        return int(sum(cnt[b.evt].sum() for b in self.blocks))
+
+    def as_dicts(self, kind_names):
+        """[{srcKind, metapaths, rows, missing}] per incident - the form IncidentReplayer.run_one returns."""
+        by_evt = {}
+        for b in self.blocks:
+            L = b.L
+            for e_, r, m in zip(b.evt.tolist(), b.rows.tolist(), b.miss.tolist()):
+                nodes = [r[0]] + r[2::2]                          # path positions 0..L in walk order
+                missing = tuple(nodes[k] for k in range(2, L + 1) if (m >> k) & 1)
+                by_evt.setdefault(e_, []).append((tuple(r), missing))
+        out = []
+        for i in range(self.n):
+            g = self.groups[self.gid[i]] if self.gid[i] >= 0 else None
+            pairs = sorted(by_evt.get(int(self.evt[i]), []), key=lambda t: t[0])
+            out.append({"srcKind": kind_names[self.src_kind[i]] if self.src_kind[i] >= 0 else None,
+                        "metapaths": list(self.metapaths.get(g, [])) if g else [],
+                        "rows": [p[0] for p in pairs], "missing": [p[1] for p in pairs]})
+        return out
 
 
 def latency_profile(replayer, messages, n_single=200):
@@ -202,8 +295,9 @@ def latency_profile(replayer, messages, n_single=200):
         t0 = time.perf_counter()
         replayer.run_one(m)
         lat.append((time.perf_counter() - t0) * 1e3)
+    replayer.run_batch_arrays(messages)          # caches (name arenas, metapaths) are part of a loaded snapshot
     t0 = time.perf_counter()
-    replayer.run_batch(messages)
+    replayer.run_batch_arrays(messages)
     batch_ms = (time.perf_counter() - t0) * 1e3
     lat = np.array(lat)
     return {"single_p50_ms": float(np.percentile(lat, 50)), "single_p99_ms": float(np.percentile(lat, 99)),

@@ -316,6 +316,26 @@ class SynthProps(BaseProps):
             p["imageName"] = f"registry.local/app-{j}:v1"
         return p
 
+    def column(self, kind_idx, key):
+        kind = self.snap.kinds[kind_idx]
+        lo, hi = self.snap.kind_range(kind_idx)
+        n = hi - lo
+        if not kind.is_state:                         # the formulas of _entity, a whole kind at a time
+            if key == "name2" and kind.category == "NativeEntity":
+                prefix = kind.name.lower()
+                return [f"{prefix}-{j}" for j in range(n)]
+            if key == "path" and kind.name == "nfs":
+                return [f"/exports/vol-{j}" for j in range(n)]
+            if key == "containerName" and kind.name == "container":
+                return [f"container-{j}" for j in range(n)]
+            if key == "imageName" and kind.name == "image":
+                return [f"registry.local/app-{j}:v1" for j in range(n)]
+        return super().column(kind_idx, key)
+
+    def event_times_ms(self, nodes):
+        lo, _ = self.snap.kind_range(len(self.snap.kinds) - 1)
+        return np.asarray(self.ev_ts, dtype=np.int64)[np.asarray(nodes, dtype=np.int64) - lo]
+
     def rel_props(self, r):
         p = super().rel_props(r)
         s = self.snap
