@@ -108,7 +108,8 @@ struct Ctl {                          // device control block, one per engine
     unsigned long long out_base;      // first output word of this plan (plans of one submission share the arena)
     unsigned int ticket[kLv];         // fused path: tile tickets
     unsigned int overflow;            // bit0 frontier arena, bit1 output arena
-    unsigned int pad;
+    unsigned int epoch;               // tile-state tag of this run, read when the launch parameters carry none (epoch 0):
+                                      // a replayed CUDA graph has fixed parameters, the tag must change with every run
 };
 
 struct LevelParams {
@@ -1106,6 +1107,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
     const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
     const int s = p.s, lane = c.w.lane;
     ulonglong2 *tstate = p.tstate + c.slot0;
+    const unsigned epoch = p.epoch ? p.epoch : ctl->epoch;
     unsigned long long scanned = 0;
     unsigned ov = 0;
     while (true) {
@@ -1121,7 +1123,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
         int cf, ce, c2, s2;
         tile_count<ADJ2, MODE, QT>(p, c.T, c.w, C, cf, ce, c2, s2);
         unsigned long long run_f, run_e;
-        tile_lookback(tstate, tile, p.epoch, (unsigned long long)cf, (unsigned long long)ce, run_f, run_e);
+        tile_lookback(tstate, tile, epoch, (unsigned long long)cf, (unsigned long long)ce, run_f, run_e);
         if (run_f + cf > 0xffffffffull) ov |= 1u;     // the 32-bit count field of the state word
         if (c.fb_s + run_f + cf > p.fcap) ov |= 1u;
         if (!p.count_only && c.ob_s + (run_e + ce) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
@@ -1250,6 +1252,7 @@ __device__ __forceinline__ void chain_walk_body(const ChainParams &p) {
     __shared__ unsigned long long s_wsum[kWarps], s_pre;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     Ctl *ctl = p.ctl;
+    const unsigned epoch = p.epoch ? p.epoch : ctl->epoch;
     const unsigned ntiles = (unsigned)((p.n_seeds + kThreads - 1) / kThreads);
     const int L = p.L;
     unsigned long long sc[RCA_MAX_HOPS + 1], al[RCA_MAX_HOPS + 1];
@@ -1287,7 +1290,7 @@ __device__ __forceinline__ void chain_walk_body(const ChainParams &p) {
         }
         if (wid == 0) {
             unsigned long long pre_f, pre_e;
-            tile_lookback(p.tstate, tile, p.epoch, 0ull, tile_rows, pre_f, pre_e);
+            tile_lookback(p.tstate, tile, epoch, 0ull, tile_rows, pre_f, pre_e);
             if (lane == 0) {
                 s_pre = pre_e;
                 if (tile == ntiles - 1) ctl->N[L] = pre_e + tile_rows;
@@ -1323,6 +1326,7 @@ __device__ __forceinline__ void chain_line_body(const ChainParams &p) {
     __shared__ unsigned long long s_wsum[kWarps], s_pre;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     Ctl *ctl = p.ctl;
+    const unsigned epoch = p.epoch ? p.epoch : ctl->epoch;
     const unsigned ntiles = (unsigned)((p.n_seeds + kThreads - 1) / kThreads);
     const int L = p.L;
     const bool probe = p.with_states && !p.count_only;
@@ -1393,7 +1397,7 @@ __device__ __forceinline__ void chain_line_body(const ChainParams &p) {
         }
         if (wid == 0) {
             unsigned long long pre_f, pre_e;
-            tile_lookback(p.tstate, tile, p.epoch, 0ull, tile_rows, pre_f, pre_e);
+            tile_lookback(p.tstate, tile, epoch, 0ull, tile_rows, pre_f, pre_e);
             if (lane == 0) {
                 s_pre = pre_e;
                 if (tile == ntiles - 1) ctl->N[L] = pre_e + tile_rows;

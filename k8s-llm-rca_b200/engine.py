@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "librca_b200.so")
 
 EXPORTS = ("rca_open", "rca_close", "rca_last_error", "rca_set_stream", "rca_set_fused_threshold",
-           "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_set_wide_entries", "rca_graph_bytes", "rca_reserve",
+           "rca_set_chain_walk_fanout", "rca_set_unit_steps", "rca_set_wide_entries", "rca_set_graphs", "rca_graph_bytes", "rca_reserve",
            "rca_expand", "rca_expand_many", "rca_result_select", "rca_expand_static",
            "rca_result_level", "rca_result_copy", "rca_set_double_buffer", "rca_result_copy_async", "rca_result_wait", "rca_state_lookup", "rca_state_window", "rca_state_window_kind", "rca_text_load",
            "rca_text_contains", "rca_text_match_pairs", "rca_peer_handle", "rca_peer_connect", "rca_peer_allgather",
@@ -90,6 +90,7 @@ def load_library(path: str | None = None):
     lib.rca_set_chain_walk_fanout.argtypes = [C.c_void_p, C.c_int64]
     lib.rca_set_unit_steps.argtypes = [C.c_void_p, C.c_int]
     lib.rca_set_wide_entries.argtypes = [C.c_void_p, C.c_int]
+    lib.rca_set_graphs.argtypes = [C.c_void_p, C.c_int]
     lib.rca_graph_bytes.argtypes = [C.c_void_p]
     lib.rca_graph_bytes.restype = C.c_int64
     lib.rca_expand.argtypes = [C.c_void_p, C.POINTER(PlanDesc), C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
@@ -340,6 +341,10 @@ class Engine:
         """The level before a final unit level stores whole paths (48-byte wide entries) instead of parent-pointer
         entries (default off; include/rca_b200.h)."""
         self._ck(self.lib.rca_set_wide_entries(self.h, 1 if on else 0))
+
+    def set_graphs(self, on: bool):
+        """Repeated submissions of expand_many are replayed as CUDA graphs (default on; include/rca_b200.h)."""
+        self._ck(self.lib.rca_set_graphs(self.h, 1 if on else 0))
 
     def set_double_buffer(self, on: bool):
         """Submissions alternate between two output arenas, so ExpandResult.rows_async() copies can overlap the
