@@ -160,7 +160,9 @@ struct rca_engine {
     std::vector<ManyGraph> many_graphs;
     std::vector<std::vector<unsigned char>> many_seen;   // keys of the last few eager submissions: one seen again is captured
     unsigned long long many_stamp = 0;
-    bool use_graphs = true;
+    bool use_graphs = false;              // measured on config 3: a replay is 4 % (one GPU) to 7 % (eight processes on one
+                                          // host) SLOWER than the eager enqueue - the step is bound by its kernels' dependent
+                                          // chain, not by the host, and the graph's event / memcpy nodes cost more than they save
     bool capturing = false;               // stream operations are being captured: timing events are recorded as external
     // results of the last submission (one per plan) and the one the accessors address
     std::vector<PlanResult> results;

@@ -343,7 +343,7 @@ class Engine:
         self._ck(self.lib.rca_set_wide_entries(self.h, 1 if on else 0))
 
     def set_graphs(self, on: bool):
-        """Repeated submissions of expand_many are replayed as CUDA graphs (default on; include/rca_b200.h)."""
+        """Repeated submissions of expand_many are replayed as CUDA graphs (default off; include/rca_b200.h)."""
         self._ck(self.lib.rca_set_graphs(self.h, 1 if on else 0))
 
     def set_double_buffer(self, on: bool):

@@ -43,6 +43,7 @@ def test_replay_equals_eager(snap_10k):
     ref.set_graphs(False)
     ref.set_fused_threshold(0)                     # the enumeration through count / scan / fill, like the headline workload
     eng = engine.Engine(snap)
+    eng.set_graphs(True)
     eng.set_fused_threshold(0)
     stream = torch.cuda.Stream()
     eng.set_stream(stream.cuda_stream)
