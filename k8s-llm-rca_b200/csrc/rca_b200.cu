@@ -64,6 +64,7 @@ struct rca_engine {
     int *out_dst = nullptr, *st_off = nullptr;
     StRec *st_rec = nullptr;              // HasState intervals, one 32 B record each
     StHead *st_head = nullptr;            // first interval + count + offset per node that can have one (rca_kernels.cuh)
+    StMore *st_more = nullptr;            // second and third interval of the nodes that have them
     int n_head = 0;
     unsigned char *rel_et = nullptr;      // edge type per relationship = per out_dst slot (only when there are <= 256 edge types)
     unsigned char *in_et = nullptr, *und_et = nullptr;   // ... and per in_adj / und_adj slot
@@ -282,6 +283,18 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
             head[v] = StHead{t44(s->st_tmin[b]) | (node & 0xfffffull) << 44, t44(s->st_tmax[b]) | (node >> 20) << 44 | more << 56};
         }
         OCK(upload(&g->st_head, head.data(), head.size()));
+        std::vector<StMore> more((size_t)g->n_head, StMore{1ull, 0ull, 1ull, 0ull});
+        for (int v = 0; v < g->n_head; v++) {
+            const int b = s->st_off[v], c = s->st_off[v + 1] - b;
+            auto pack = [&](int j, unsigned long long &a_, unsigned long long &b_) {
+                const unsigned long long node = (unsigned)s->st_node[j];
+                a_ = t44(s->st_tmin[j]) | (node & 0xfffffull) << 44;
+                b_ = t44(s->st_tmax[j]) | (node >> 20) << 44;
+            };
+            if (c >= 2) pack(b + 1, more[v].a1, more[v].b1);
+            if (c >= 3) pack(b + 2, more[v].a2, more[v].b2);
+        }
+        OCK(upload(&g->st_more, more.data(), more.size()));
     }
     if (s->n_etypes <= 256 && s->rel_et) {
         std::vector<unsigned char> et((size_t)s->n_rels);
@@ -326,7 +339,7 @@ extern "C" int rca_open(const rca_snapshot_t *s, int device, rca_engine_t **out)
         g->graph_bytes = 3 * V1 * sizeof(int2) + (size_t)s->n_rels * (sizeof(int) + sizeof(int2)) + (size_t)s->n_und * sizeof(int2) +
                          ((size_t)s->n_typed_out + (size_t)s->n_typed_in) * sizeof(int2) + V1 * sizeof(int) +
                          (size_t)s->n_states * sizeof(StRec) + (g->rel_et ? 2 * (size_t)s->n_rels + (size_t)s->n_und : 0) +
-                         (size_t)g->n_head * sizeof(StHead) + nx.size() * sizeof(int2);
+                         (size_t)g->n_head * (sizeof(StHead) + sizeof(StMore)) + nx.size() * sizeof(int2);
     }
     OCK(cudaMalloc((void **)&g->ctl, sizeof(Ctl)));
     OCK(cudaMallocHost((void **)&g->h_ctl, sizeof(Ctl)));
@@ -343,7 +356,7 @@ extern "C" int rca_close(rca_engine_t *e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     for (auto &g : e->many_graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
     void *dev[] = {e->out_rng, e->in_rng, e->und_rng, e->in_adj, e->und_adj, e->typed_out, e->typed_in, e->out_dst,
-                   e->st_off, e->st_rec, e->st_head, e->unit_next, e->rel_et, e->in_et, e->und_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
+                   e->st_off, e->st_rec, e->st_head, e->st_more, e->unit_next, e->rel_et, e->in_et, e->und_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off, e->m_ptab, e->m_ctl};
     for (void *p : dev) if (p) cudaFree(p);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
@@ -759,7 +772,7 @@ static void chain_params(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
     c.with_states = pl->with_states; c.count_only = pl->count_only; c.row_len = row_len_of(pl, L);
     c.epoch = b.epoch; c.seeds = b.seeds; c.seed_ts = b.ts; c.n_seeds = b.n_seeds;
     c.out = e->out; c.ocap = b.ocap ? b.ocap : e->ocap; c.ctl = b.ctl; c.tstate = e->tstate + b.tstate_at;
-    c.st_head = e->st_head; c.n_head = e->n_head; c.st_off = e->st_off; c.st_rec = e->st_rec;
+    c.st_head = e->st_head; c.st_more = e->st_more; c.n_head = e->n_head; c.st_off = e->st_off; c.st_rec = e->st_rec;
     line = true;                                      // all steps before the last are unit steps: no search needed
     for (int i = 0; i + 1 < L; i++) line &= c.unit[i] != nullptr;
 }
@@ -828,7 +841,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.ptab = b.ptab;
         p.rel_et = dir == RCA_DIR_OUT ? e->rel_et : dir == RCA_DIR_IN ? e->in_et : e->und_et;   // per slot of the array walked
         p.arr_prune = pp.arr_prune;
-        p.st_head = e->st_head; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
+        p.st_head = e->st_head; p.st_more = e->st_more; p.n_head = e->n_head; p.st_off = e->st_off; p.st_rec = e->st_rec;
         const size_t dyn = (size_t)kWarps * warp_smem_ints(s) * sizeof(int);
         const long long first = std::max<long long>(1, (b.n_seeds + kTile * kWarps - 1) / (kTile * kWarps));
         // count-only plan whose last level is one unit step that emits: level L-1 takes that step while it counts

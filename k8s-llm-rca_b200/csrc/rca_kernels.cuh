@@ -99,6 +99,15 @@ struct StHead {
     unsigned long long a, b;          // no interval: tmin 1, tmax 0 - matches no timestamp
 };
 constexpr unsigned long long kT44 = (1ull << 44) - 1;
+// ... and, for the nodes that have more than one interval, their SECOND and THIRD interval in the same packing, 32 bytes
+// per node at an address that follows from the node id alone: a node with up to three intervals is answered by the
+// header and, one round trip later, this record - where the full records need three dependent round trips (offsets,
+// interval bounds, then the state node of the interval that matched).  A warp waits for its slowest lane, and among
+// the 128 nodes a tile of rows probes there is always one with several intervals: the chain of fill_unit is what
+// bounds it.  Nodes with four or more intervals continue in the full records from the fourth on.
+struct StMore {
+    unsigned long long a1, b1, a2, b2;    // no such interval: tmin 1, tmax 0
+};
 
 struct Ctl {                          // device control block, one per engine
     unsigned long long F[kLv];        // frontier size per level (level s occupies arena entries sum F[1..s-1] ..)
@@ -162,6 +171,7 @@ struct LevelParams {
     const int2 *la_next;              // its next-hop table
     // HasState intervals
     const StHead *st_head;            // [n_head]: nodes at or above n_head have no intervals
+    const StMore *st_more;            // [n_head] second and third interval (null: answer from the full records)
     int n_head;
     const int *st_off;                // [V+1]: a node's records are st_rec[st_off[v] .. st_off[v+1])
     const StRec *st_rec;
@@ -269,7 +279,14 @@ struct States {
     int n_head;
     const int *off;
     const StRec *rec;
+    const StMore *more = nullptr;
 };
+__device__ __forceinline__ void packed_interval(unsigned long long a, unsigned long long b, long long ts, int &first, int &cnt) {
+    if ((long long)(a & kT44) <= ts && (long long)(b & kT44) > ts) {
+        if (cnt == 0) first = (int)((a >> 44) | (((b >> 44) & 0xfffull) << 20));
+        cnt++;
+    }
+}
 __device__ __forceinline__ ulonglong2 ld_head(const States &st, int v, bool on) {
     ulonglong2 h = make_ulonglong2(1ull, 0ull);
     if (on && (unsigned)v < (unsigned)st.n_head) h = __ldg(reinterpret_cast<const ulonglong2 *>(st.head + v));
@@ -286,7 +303,14 @@ __device__ __forceinline__ void head_finish(const States &st, const ulonglong2 h
         first = (int)((h.x >> 44) | (((h.y >> 44) & 0xfffull) << 20));
         cnt = 1;
     }
-    if (h.y >> 56) state_probe_full(st.off, st.rec, v, ts, 1, first, cnt);
+    const int further = (int)(h.y >> 56);
+    if (!further) return;
+    if (!st.more) { state_probe_full(st.off, st.rec, v, ts, 1, first, cnt); return; }
+    const ulonglong2 *m = reinterpret_cast<const ulonglong2 *>(st.more + v);
+    const ulonglong2 x = __ldg(m), y = __ldg(m + 1);          // one sector, both halves requested at once
+    packed_interval(x.x, x.y, ts, first, cnt);
+    packed_interval(y.x, y.y, ts, first, cnt);
+    if (further > 2) state_probe_full(st.off, st.rec, v, ts, 3, first, cnt);
 }
 __device__ __forceinline__ void state_probe(const States &st, int v, long long ts, int &first, int &cnt) {
     head_finish(st, ld_head(st, v, true), v, ts, first, cnt);
@@ -397,7 +421,7 @@ __device__ __forceinline__ int tile_prologue(const LevelParams &p, const Tables 
         W.root[o] = par;
         if (WIDE && p.with_states) {                  // the entry's share of a wide entry: timestamp, states of its nodes
             const long long ts = __ldg(p.seed_ts + par);
-            const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+            const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
             const int n0 = w.anc_n[o];
             const ulonglong2 h0 = ld_head(st, n0, true), h1 = ld_head(st, tail, q > 0);
             int f0, c0, f1 = -1, c1;
@@ -507,7 +531,7 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
         if constexpr (S >= 0) {
             // the kernel is latency-bound here: issue every column's offset loads, then every column's
             // record loads, back to back - two memory round trips per row instead of 2(S+1)
-            const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+            const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
             ulonglong2 h[S + 1];
 #pragma unroll
             for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= q) ? w.anc_n[d * kTile + o] : v, active);
@@ -527,7 +551,7 @@ __device__ __forceinline__ void flush_rows(const LevelParams &p, const Warp &w, 
                 const unsigned same = __match_any_sync(0xffffffffu, nd) & __match_any_sync(0xffffffffu, ts);
                 const int leader = __ffs(same) - 1;
                 int first = -1, cnt = 0;
-                if (w.lane == leader && nd >= 0) state_probe(States{p.st_head, p.n_head, p.st_off, p.st_rec}, nd, ts, first, cnt);
+                if (w.lane == leader && nd >= 0) state_probe(States{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more}, nd, ts, first, cnt);
                 first = __shfl_sync(0xffffffffu, first, leader);
                 cnt = __shfl_sync(0xffffffffu, cnt, leader);
                 if (active) {
@@ -559,7 +583,7 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
         int v, r, na;
         const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + lane, C, x, v, r, na);
         ulonglong2 hv = make_ulonglong2(1ull, 0ull);
-        const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+        const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
         if (WIDE && p.with_states) hv = ld_head(st, v, (fl & 1) != 0);          // the new node's state: in flight over the ballots
         const unsigned bf = __ballot_sync(0xffffffffu, fl & 1), be = __ballot_sync(0xffffffffu, fl & 2);
         if (WIDE) {
@@ -978,7 +1002,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
         // answers for the nodes already on the path: only the new last node is probed)
         const bool probe = want_rows && p.with_states && u.has && (!p.need_inter || u.inter);
         long long ts = 0;
-        const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+        const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
         ulonglong2 h[S + 1];
         if (p.with_states) {
             if constexpr (WIDE) {
@@ -1168,6 +1192,7 @@ struct ChainParams {
     Ctl *ctl;
     ulonglong2 *tstate;
     const StHead *st_head;
+    const StMore *st_more;
     int n_head;
     const int *st_off;
     const StRec *st_rec;
@@ -1219,7 +1244,7 @@ __device__ __forceinline__ unsigned long long chain_dfs(const ChainParams &p, in
                 for (int k = 0; k < L; k++) row[L + 1 + k] = rel[k];
                 if (p.with_states) {
                     // every node's header load goes out before the first one is looked at
-                    const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+                    const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
                     ulonglong2 h[RCA_MAX_HOPS + 1];
 #pragma unroll
                     for (int k = 0; k <= RCA_MAX_HOPS; k++) h[k] = ld_head(st, k <= L ? node[k] : 0, k <= L);
@@ -1330,7 +1355,7 @@ __device__ __forceinline__ void chain_line_body(const ChainParams &p) {
     const unsigned ntiles = (unsigned)((p.n_seeds + kThreads - 1) / kThreads);
     const int L = p.L;
     const bool probe = p.with_states && !p.count_only;
-    const States st{p.st_head, p.n_head, p.st_off, p.st_rec};
+    const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
     unsigned sc[RCA_MAX_HOPS + 1], al[RCA_MAX_HOPS + 1];
 #pragma unroll
     for (int k = 0; k <= RCA_MAX_HOPS; k++) { sc[k] = 0; al[k] = 0; }
