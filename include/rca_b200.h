@@ -149,13 +149,12 @@ int rca_set_chain_walk_fanout(rca_engine_t *e, int64_t max_rows_per_seed);
  * on = 0 sends such levels through the general kernels (default on).  No counterpart in the reference. */
 int rca_set_unit_steps(rca_engine_t *e, int on);
 /* When the last level of a large variable-length plan consists of such unit steps and the paths before it have at
- * most three nodes, the level before it stores every surviving path whole - its nodes, relationships, the answers
- * of the state predicate for them and the seed's timestamp, 48 bytes in three coalesced planes - instead of a
- * 16-byte parent-pointer entry: the last level then reads one contiguous record per row and probes ONE state
- * header, where it used to chase the parent entry, the seed, the timestamp and a header per node.  Same rows,
- * same order, same counters.  Default OFF: on BASELINE's config 3 the last level gains less (0.22 -> 0.18 ms)
- * than the level before it loses (0.10 -> 0.18 ms: three times the bytes written, and a state probe inside its
- * window loop); it pays where the level before is small against the last one.  No counterpart in the reference. */
+ * most three nodes, the level before it can store every surviving path whole - nodes, relationships, seed index,
+ * 32 bytes in two coalesced planes - instead of a 16-byte parent-pointer entry: the last level then knows all nodes
+ * of a row after one contiguous read, where it chases the parent entry and the seed.  Same rows, same order, same
+ * counters.  Default OFF: on BASELINE's config 3 the last level gains less (0.189 -> 0.187 ms) than the level
+ * before it loses to the wider writes (0.095 -> 0.102 ms); a first version that also carried the state answers lost
+ * more (level 2: 0.10 -> 0.18 ms).  No counterpart in the reference. */
 int rca_set_wide_entries(rca_engine_t *e, int on);
 /* device memory the snapshot occupies on this engine's GPU (adjacency, typed tables, intervals and the
  * tables rca_open derives from them), in bytes.  No counterpart in the reference. */

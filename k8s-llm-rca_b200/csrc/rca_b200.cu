@@ -99,7 +99,7 @@ struct rca_engine {
     long long chain_walk_fanout = 64;     // typed chains whose per-seed fan-out is at most this run as one depth-first launch
     bool unit_steps = true;               // typed steps with at most one candidate per path use count_unit / fill_unit
     bool wide_entries = false;            // the level before a final unit level stores whole paths (rca_set_wide_entries);
-                                          // measured on config 3: level 3 0.219 -> 0.179 ms, level 2 0.099 -> 0.181 ms - off
+                                          // measured on config 3: level 2 0.095 -> 0.102 ms, level 3 0.189 -> 0.187 ms - off
     long long chain_fused_max_seeds = 1 << 20;   // typed chains have uniform tiles: the fused launch suits them far longer
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr;                 // pinned
@@ -1096,7 +1096,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         // counters are exact up to and including the first level that overflowed: grow to at least that
         unsigned long long fneed = 0, oneed = 0;
         for (int s = 1; s <= L; s++) {
-            fneed += s == pp.wide_level ? 3 * (e->h_ctl->F[s] + 32) : e->h_ctl->F[s];      // wide entries: three planes
+            fneed += s == pp.wide_level ? 2 * (e->h_ctl->F[s] + 32) : e->h_ctl->F[s];      // wide entries: two planes
             oneed += e->h_ctl->N[s] * (unsigned long long)row_len_of(pl, s);
         }
         if (ov & 1u) { rc = grow(e, &e->frontier, &e->fcap, std::max(e->fcap * 2, fneed + fneed / 4)); if (rc) return rc; }
@@ -1413,7 +1413,7 @@ extern "C" int rca_expand_many(rca_engine_t *e, const rca_plan_t *plans, int32_t
             unsigned long long f = 0;
             const int L = pps[k].L;
             for (int s = 1; s <= L; s++) {
-                f += s == pps[k].wide_level ? 3 * (e->mh_ctl[k].F[s] + 32) : e->mh_ctl[k].F[s];
+                f += s == pps[k].wide_level ? 2 * (e->mh_ctl[k].F[s] + 32) : e->mh_ctl[k].F[s];
                 if (!aside[k]) oneed += e->mh_ctl[k].N[s] * (unsigned long long)row_len_of(&plans[k], s);
             }
             fneed = std::max(fneed, f);

@@ -329,30 +329,28 @@ struct WarpSm {
 };
 // ... then a staging area for 32 finished rows (3s+3 words each at most), so that rows leave the SM
 // as whole 128 B lines instead of 4-byte stores scattered at row stride
-// ... and, for a level that writes wide entries, four rows of 32 ints: per entry of the tile the states of its path's
-// first two nodes and the seed's timestamp (looked up once per entry, used by every candidate of the entry)
 __host__ __device__ constexpr int warp_smem_ints(int s, int wide = 0) {
-    return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile + kTile * (3 * s + 3) + (wide ? 4 * kTile : 0);
+    return (int)(sizeof(WarpSm) / 4) + 2 * s * kTile + kTile * (3 * s + 3) + 0 * wide;
 }
 
 struct Warp {                         // a warp's view of its tile
     WarpSm *W;
-    int *anc_n, *anc_r, *stage, *wd;
+    int *anc_n, *anc_r, *stage;
     int lane;
     unsigned lt;
 };
 
 // Wide entries.  When the level after this one is the plan's last and a unit step (fill_unit: one lane per path), that
-// level's cost is the lane-divergent loads it needs to rebuild a path from 16-byte parent-pointer entries - the parent
-// entry, the seed, the seed's timestamp - and one state header per node of the row.  A level whose paths have at most
-// three nodes can hand all of that over instead: its fill writes, per surviving path, three 16-byte words in three
-// planes (each plane one coalesced stream for the reader)
-//     A = (node0, node1, node2 | -1, rel1)    B = (rel2 | -1, root, aux, state0)    C = (state1, state2 | -1, ts)
-// where state_d is the answer of the HasState predicate for node_d at the seed's timestamp (-1: none) - looked up ONCE
-// per node as it joins the path (the siblings of an entry share the first two), not once per row.  The reader then
-// does one coalesced 48-byte read, its one next-hop load and ONE state header load (the new last node) per row.
-// Plane stride = the level's entry count rounded up to 32; planes B and C exist only as far as the plan needs them
-// (C only with the state filter).  Nothing walks up THROUGH a wide level: it is always the last level stored.
+// level is bound by its chain of dependent loads: entry -> parent entry -> seed -> state header of the seed -> its
+// further intervals.  A level whose paths have at most three nodes can hand the whole path over instead: its fill
+// writes, per surviving path, two 16-byte words in two planes (each plane one coalesced stream for the reader)
+//     A = (node0, node1, node2 | -1, rel1)    B = (rel2 | -1, root, aux, 0)
+// so that the reader knows every node of the row after ONE coalesced read and can request the next hop, the seed's
+// timestamp and all state headers at once - one round trip less, and no lane-divergent parent / seed loads.
+// (A first version also carried the answers of the state predicate for the nodes already on the path - looked up
+// per entry and, for the new node, per candidate in the writer's window loop; measured, the writer lost twice what
+// the reader gained.)  Plane stride = the level's entry count rounded up to 32.  Nothing walks up THROUGH a wide
+// level: it is always the last level stored.
 __device__ __forceinline__ unsigned long long wide_stride(unsigned long long entries) { return (entries + 31ull) & ~31ull; }
 
 // Prologue of one tile; returns the number of candidates C.
@@ -419,19 +417,6 @@ __device__ __forceinline__ int tile_prologue(const LevelParams &p, const Tables 
             w.anc_n[o] = __ldg(p.seeds + par);
         }
         W.root[o] = par;
-        if (WIDE && p.with_states) {                  // the entry's share of a wide entry: timestamp, states of its nodes
-            const long long ts = __ldg(p.seed_ts + par);
-            const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
-            const int n0 = w.anc_n[o];
-            const ulonglong2 h0 = ld_head(st, n0, true), h1 = ld_head(st, tail, q > 0);
-            int f0, c0, f1 = -1, c1;
-            head_finish(st, h0, n0, ts, f0, c0);
-            if (q > 0) head_finish(st, h1, tail, ts, f1, c1);
-            w.wd[o] = f0;
-            w.wd[kTile + o] = f1;
-            w.wd[2 * kTile + o] = (int)(unsigned)(unsigned long long)ts;
-            w.wd[3 * kTile + o] = (int)((unsigned long long)ts >> 32);
-        }
     }
     W.coff[nz + lane] = (lane == 0) ? C : 0x7fffffff;            // coff[nz] = C, then sentinels
     if (lane < 2) W.coff[nz + 32 + lane] = 0x7fffffff;
@@ -582,31 +567,17 @@ __device__ __forceinline__ void tile_fill(const LevelParams &p, const Tables &T,
         const Cand x = fetch_cand<ADJ2, MODE>(p, w, o, (it << 5) + lane, C);
         int v, r, na;
         const int fl = classify<ADJ2, MODE, QT>(p, T, w, o, (it << 5) + lane, C, x, v, r, na);
-        ulonglong2 hv = make_ulonglong2(1ull, 0ull);
-        const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
-        if (WIDE && p.with_states) hv = ld_head(st, v, (fl & 1) != 0);          // the new node's state: in flight over the ballots
         const unsigned bf = __ballot_sync(0xffffffffu, fl & 1), be = __ballot_sync(0xffffffffu, fl & 2);
         if (WIDE) {
             if (fl & 1) {                             // QT + 1 = nodes on the path before this step (1 or 2)
                 const unsigned long long j = run_f + __popc(bf & w.lt);
                 int4 *A = p.frontier + fb_s;
-                if (fb_s + 3 * wstride <= p.fcap) {   // else: flagged by the scan, the run is void
+                if (fb_s + 2 * wstride <= p.fcap) {   // else: flagged by the scan, the run is void
                     const int n0 = w.anc_n[o];
                     const int n1 = QT >= 1 ? w.anc_n[kTile + o] : v, n2 = QT >= 1 ? v : -1;
                     const int r1 = QT >= 1 ? w.anc_r[kTile + o] : r, r2 = QT >= 1 ? r : -1;
-                    int s0 = -1, s1 = -1, s2 = -1, tl = 0, th = 0;
-                    if (p.with_states) {
-                        tl = w.wd[2 * kTile + o]; th = w.wd[3 * kTile + o];
-                        const long long ts = (long long)(((unsigned long long)(unsigned)th << 32) | (unsigned)tl);
-                        int fv, cv;
-                        head_finish(st, hv, v, ts, fv, cv);
-                        s0 = w.wd[o];
-                        s1 = QT >= 1 ? w.wd[kTile + o] : fv;
-                        s2 = QT >= 1 ? fv : -1;
-                    }
                     A[j] = make_int4(n0, n1, n2, r1);
-                    A[wstride + j] = make_int4(r2, W.root[o], na, s0);
-                    if (p.with_states) A[2 * wstride + j] = make_int4(s1, s2, tl, th);
+                    A[wstride + j] = make_int4(r2, W.root[o], na, 0);
                 }
             }
         } else if (fl & 1) {
@@ -705,7 +676,6 @@ __device__ __forceinline__ LevelCtx level_setup(const LevelParams &p, TablesSm &
     c.w.anc_n = reinterpret_cast<int *>(c.w.W + 1);
     c.w.anc_r = c.w.anc_n + s * kTile;
     c.w.stage = c.w.anc_r + s * kTile;
-    c.w.wd = c.w.stage + kTile * (3 * s + 3);
     unsigned long long fb_s = 0, ob_s = ctl->out_base;
     for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
     c.fb_s = fb_s; c.ob_s = ob_s;
@@ -800,7 +770,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
         ctl->F[s] = base_f + s_run[0];
         ctl->N[s] = base_n + s_run[1];
         unsigned ov = 0;
-        const unsigned long long room = p.wide_out ? 3ull * wide_stride(base_f + s_run[0]) : base_f + s_run[0];
+        const unsigned long long room = p.wide_out ? 2ull * wide_stride(base_f + s_run[0]) : base_f + s_run[0];
         if (!p.la_n && fb_s + room > p.fcap) ov |= 1u;                 // la_n: the paths are counted, never stored
         if (!p.count_only && ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (ov) ctl->overflow = ov;
@@ -974,6 +944,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
     const int4 none = make_int4(0, 0, 0, 0);
     unsigned tile = blockIdx.x * kWarps + (threadIdx.x >> 5);
     int4 e_next = ((unsigned long long)tile * kTile + lane < c.Fq) ? fq[(unsigned long long)tile * kTile + lane] : none;
+    int4 b_next = (WIDE && (unsigned long long)tile * kTile + lane < c.Fq) ? fq[wstride + (unsigned long long)tile * kTile + lane] : none;
     for (; tile < c.ntiles; tile += nwarps) {
         const unsigned long long slot = c.slot0 + tile, g = slot / kGroup;
         const unsigned in_g = (unsigned)(slot % kGroup);
@@ -985,34 +956,23 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
         const int4 e = e_next;
         e_next = i2 < c.Fq ? fq[i2] : none;           // the next tile's entries travel while this tile is worked on
         UnitLane<Q> u;
-        int4 wc = none;                               // wide: plane C = (state1, state2, timestamp)
-        int ws0 = -1;
         if constexpr (WIDE) {
-            int4 B = none;
-            if (valid) {
-                B = fq[wstride + i];
-                if (p.with_states) wc = fq[2 * wstride + i];
-            }
-            ws0 = B.w;
+            const int4 B = b_next;
+            b_next = i2 < c.Fq ? fq[wstride + i2] : none;
             u.load_wide(p, e, B, valid);
         } else {
             u.load(p, s_fb, e, valid);
         }
-        // state probes: the header sector of every node of the row, all in flight together (wide entries bring the
-        // answers for the nodes already on the path: only the new last node is probed)
+        // state probes: the header sector of every node of the row, all in flight together (a wide entry names all the
+        // nodes at once: the headers leave in the same round trip as the next-hop load)
         const bool probe = want_rows && p.with_states && u.has && (!p.need_inter || u.inter);
         long long ts = 0;
         const States st{p.st_head, p.n_head, p.st_off, p.st_rec, p.st_more};
         ulonglong2 h[S + 1];
         if (p.with_states) {
-            if constexpr (WIDE) {
-                ts = (long long)(((unsigned long long)(unsigned)wc.w << 32) | (unsigned)wc.z);
-                h[S] = ld_head(st, u.v, probe);
-            } else {
-                if (probe) ts = __ldg(p.seed_ts + u.root);
+            if (probe) ts = __ldg(p.seed_ts + u.root);
 #pragma unroll
-                for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= Q) ? u.a[d] : u.v, probe);
-            }
+            for (int d = 0; d <= S; d++) h[d] = ld_head(st, (d <= Q) ? u.a[d] : u.v, probe);
         }
         const unsigned long long run_f = gp.x + __reduce_add_sync(0xffffffffu, mine.x);
         const unsigned long long run_e = gp.y + __reduce_add_sync(0xffffffffu, mine.y);
@@ -1025,6 +985,34 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
         const int n = __popc(be);
         const unsigned long long w0 = c.ob_s + run_e * (unsigned long long)rl;
         if (w0 + (unsigned long long)n * rl > p.ocap) continue;      // flagged with the counts: the run is void
+        if constexpr (S == 3) {
+            // Three-hop rows with state columns are 12 words (8 with the mask alone): whole 16-byte words.  When the
+            // level's rows start on a 16-byte boundary every lane stores its row straight from registers with two or
+            // three vector stores - no staging through shared memory (12 stores with 4-way bank conflicts, 12 loads, 12
+            // coalesced stores and a loop per tile; the L1 data pipe, which all of those go through, is what bounds
+            // this kernel).
+            if (p.with_states && ((w0 & 3ull) == 0)) {
+                if (u.fl & 2) {
+                    int sid[4];
+                    unsigned miss = 0;
+#pragma unroll
+                    for (int d = 0; d <= S; d++) {
+                        int cnt;
+                        head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, sid[d], cnt);
+                        miss |= (cnt == 0 ? 1u : 0u) << d;
+                    }
+                    int4 *dst4 = reinterpret_cast<int4 *>(p.out + w0 + (unsigned long long)__popc(be & lt) * rl);
+                    dst4[0] = make_int4(u.a[0], u.a[1], u.a[2], u.v);
+                    if (p.with_states == 1) {
+                        dst4[1] = make_int4(u.rel[1], u.rel[2], u.r, sid[0]);
+                        dst4[2] = make_int4(sid[1], sid[2], sid[3], (int)miss);
+                    } else {
+                        dst4[1] = make_int4(u.rel[1], u.rel[2], u.r, (int)miss);
+                    }
+                }
+                continue;
+            }
+        }
         if (u.fl & 2) {
             int *row = stage + __popc(be & lt) * rl;
 #pragma unroll
@@ -1035,25 +1023,12 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __gri
             row[2 * S] = u.r;
             if (p.with_states) {
                 unsigned miss = 0;
-                if constexpr (WIDE) {
-                    const int known[3] = {ws0, wc.x, wc.y};
 #pragma unroll
-                    for (int d = 0; d <= Q; d++) {
-                        if (p.with_states == 1) row[2 * S + 1 + d] = known[d];
-                        miss |= (known[d] < 0 ? 1u : 0u) << d;
-                    }
+                for (int d = 0; d <= S; d++) {
                     int first, cnt;
-                    head_finish(st, h[S], u.v, ts, first, cnt);
-                    if (p.with_states == 1) row[2 * S + 1 + S] = first;
-                    miss |= (cnt == 0 ? 1u : 0u) << S;
-                } else {
-#pragma unroll
-                    for (int d = 0; d <= S; d++) {
-                        int first, cnt;
-                        head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, first, cnt);
-                        if (p.with_states == 1) row[2 * S + 1 + d] = first;
-                        miss |= (cnt == 0 ? 1u : 0u) << d;
-                    }
+                    head_finish(st, h[d], (d <= Q) ? u.a[d] : u.v, ts, first, cnt);
+                    if (p.with_states == 1) row[2 * S + 1 + d] = first;
+                    miss |= (cnt == 0 ? 1u : 0u) << d;
                 }
                 row[p.with_states == 1 ? 3 * S + 2 : 2 * S + 1] = (int)miss;
             }
