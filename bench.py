@@ -21,6 +21,8 @@ Beside the headline the line carries
   sharded       BASELINE config 4's shape as a strong-scaling measurement: one fixed job (10M-object
                 graph, a million sorted seed Pods) cut over the ranks, with and without the payload
                 gather to rank 0.
+  config2       BASELINE config 2: 10k objects, every source kind -> Node, <= 4 hops, metapath ladder and instance
+                expansion with kernel time and HBM fraction (rank 0).
   latency       BASELINE config 5: per-incident RCA graph latency.
 """
 import argparse
@@ -291,6 +293,53 @@ def parity_leg(w, eng, rank, world, dev, peer_ok, oracle_sample):
     return info
 
 
+def config2_leg(local_rank, peak):
+    """BASELINE config 2: a 10k-object cluster, every source kind -> Node, <= 4 hops, the full ladder of
+    find_metapath (directed, undirected, one hop, via Namespace; shortest length kept) - on the metagraph, as the
+    reference runs it, through run_query; and the same statement shape over the INSTANCE graph (all nodes of the kind
+    as seeds, directed then undirected), which is where the kernels have work.  Small and latency-bound by nature:
+    reported for completeness, with its kernel time and the HBM fraction its algorithmic bytes amount to."""
+    import contextlib
+    import io
+    from k8s_llm_rca_b200 import dropin, engine as E, executor, synth
+    snap = synth.generate(10_000, 1000, synth.config_seed(1))
+    executor.register_snapshot("config2", snap)
+    mx = executor.GpuQueryExecutor("snapshot://config2#metagraph", device=local_rank)
+    dropin.install()
+    from find_metapath.find_srckind_metapath_neo4j import find_metapath
+    eng = E.Engine(snap, device=local_rank)
+    K = snap.kind_index
+    node, excl = K("Node"), [K("Event"), K("Namespace")]
+    out = {"objects": 10_000, "max_hops": 4, "dest": "Node", "metapaths": {}, "instances": {}}
+    kernel_ms = bytes_alg = total = 0
+    t0 = time.perf_counter()
+    for k, kind in enumerate(snap.kinds):
+        if kind.is_state or kind.name in ("Event", "Namespace", "Node"):
+            continue
+        with contextlib.redirect_stdout(io.StringIO()):
+            try:
+                mps = find_metapath(mx, kind.name, "Node", [])
+            except ValueError:                                     # no rung of the ladder finds a path (reference :153)
+                mps = []
+        out["metapaths"][kind.name] = {"count": len(mps), "length": len(mps[0]) if mps else None}
+        seeds = snap.nodes_of_kind(k)
+        n_kind = 0
+        for direction in ("out", "und"):
+            r = eng.expand(E.varlen_plan(direction, 4, dest_kind=node, excl_kinds=excl, entity_only=True, pos_kind=[k]), seeds)
+            kernel_ms += r.kernel_ms
+            bytes_alg += r.algorithmic_bytes()
+            n_kind += r.total
+        out["instances"][kind.name] = n_kind
+        total += n_kind
+    out.update({"wall_ms": (time.perf_counter() - t0) * 1e3, "kernel_ms": kernel_ms, "instances_total": total,
+                "algorithmic_GBps": bytes_alg / (kernel_ms * 1e-3) / 1e9 if kernel_ms else None,
+                "hbm_frac": bytes_alg / (kernel_ms * 1e-3) / 1e9 / peak if kernel_ms else None,
+                "note": "launch- and latency-bound: a few thousand seeds per launch; the metapath sets equal the oracle's (tests)"})
+    eng.close()
+    mx.close()
+    return out
+
+
 def sharded_leg(args, rank, world, local_rank, dev, barrier):
     """BASELINE config 4's shape, strong scaling: one fixed job over `world` GPUs."""
     import torch
@@ -421,6 +470,7 @@ def main():
     ap.add_argument("--sharded-objects", type=int, default=10_000_000, help="config 4 shape, strong scaling; 0 skips the leg")
     ap.add_argument("--sharded-seeds", type=int, default=1_000_000)
     ap.add_argument("--sharded-steps", type=int, default=10)
+    ap.add_argument("--config2", type=int, default=1, help="0 skips the config-2 leg (10k objects, every source kind -> Node)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -712,6 +762,7 @@ def main():
 
     if rank == 0:
         peak, peak_src = peaks()
+        config2 = config2_leg(local_rank, peak) if args.config2 else None
         # dominant kernel = the level launch with the largest share of the step
         (kname, ks), (kms, kbytes, kcalls) = max(per_level.items(), key=lambda kv: kv[1][0])
         achieved = (kbytes / kcalls) / (kms / kcalls * 1e-3) / 1e9
@@ -752,6 +803,7 @@ def main():
                          "frac_is": "SURVEY 8(d)'s algorithmic bytes / time / peak; dram_frac = ncu DRAM bytes / time / peak"},
             "clocks": clocks,
             "parity_check": parity,
+            "config2": config2,
             "sharded": sharded,
             "latency": latency,
         }
