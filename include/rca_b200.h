@@ -105,6 +105,13 @@ typedef struct {
                                        bytes to carry to the host                                 */
     int32_t count_only;             /* count path instances per length but do not write rows (no
                                        output arena needed; for very large enumerations)         */
+    int32_t shortest_only;          /* VARLEN: keep only the rows of the shortest length that has any - the
+                                       rule find_metapath applies to what its statement returned
+                                       (find_srckind_metapath_neo4j.py:153-154).  The launches of every
+                                       longer length return at once: their rows are never made, let
+                                       alone carried to the host.  Over several GPUs each rank stops at
+                                       ITS shortest length; the caller takes the minimum over the ranks
+                                       (parallel.ladder_decision) and drops the longer ranks' rows      */
 } rca_plan_t;
 
 /* Counters of the last rca_expand, all exact (they come from the kernels' own count pass). */

@@ -828,6 +828,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
         p.chain_flag = s < L ? 1 : 2;
         p.need_inter = pp.varlen && pl->has_inter;
         p.with_states = pl->with_states;
+        p.shortest_only = pp.varlen && pl->shortest_only;
         p.count_only = pl->count_only;
         p.row_len = row_len_of(pl, s);
         for (int j = 0; j <= RCA_MAX_HOPS; j++) p.row_len_lv[j] = row_len_of(pl, j);
@@ -851,7 +852,7 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
             return !pp.fused && pp.level_typed[lv] && e->unit_steps && pp.mode == kModeSimple && lv >= 2 && lv <= 6 &&
                    (pp.subs[lv][j].d ? e->unit_in_base : e->unit_out_base)[pp.subs[lv][j].t] >= 0;
         };
-        bool merged_last = !pp.fused && pl->count_only && e->unit_steps && pp.mode == kModeSimple && L >= 2 &&
+        bool merged_last = !pp.fused && pl->count_only && !pl->shortest_only && e->unit_steps && pp.mode == kModeSimple && L >= 2 &&
                            pp.level_typed[L] && pp.subs[L].size() == 1 && (pp.subs[L][0].fl & 2) &&
                            (pp.subs[L][0].d ? e->unit_in_base : e->unit_out_base)[pp.subs[L][0].t] >= 0;
         if (merged_last && pp.level_typed[L - 1])     // ... unless level L-1 is itself a unit step (no fan-out to save on)

@@ -119,6 +119,8 @@ struct Ctl {                          // device control block, one per engine
     unsigned int overflow;            // bit0 frontier arena, bit1 output arena
     unsigned int epoch;               // tile-state tag of this run, read when the launch parameters carry none (epoch 0):
                                       // a replayed CUDA graph has fixed parameters, the tag must change with every run
+    unsigned int stop_level;          // shortest_only plans: the first level that emitted rows (0: none yet); the launches
+    unsigned int pad;                 // of every later level return at once
 };
 
 struct LevelParams {
@@ -135,6 +137,7 @@ struct LevelParams {
     int sub;                          // a level may run as several typed sub-launches (0, 1, ..): see rca_b200.cu
     int chain_flag;                   // chain plans: 1 = every candidate continues, 2 = every candidate is a row
     int need_inter;                   // emit only if an interior node so far is of an intermediate kind
+    int shortest_only;                // keep only the rows of the shortest length that has any (find_metapath's rule)
     int with_states;                  // 1: rows carry a state id per node and the missing mask, 2: the mask alone
     int count_only;                   // rows are counted, never written
     int row_len;                      // words per emitted row at this level
@@ -650,6 +653,17 @@ __device__ __forceinline__ bool overflow_seen(const Ctl *ctl) {
     __syncthreads();
     return s_ov != 0;
 }
+// ... and of "a shorter level already has rows" (shortest_only plans: this level's launches have nothing to do)
+__device__ __forceinline__ bool launch_void(const LevelParams &p) {
+    __shared__ unsigned s_void;
+    if (threadIdx.x == 0) {
+        const volatile Ctl *c = p.ctl;
+        const unsigned stop = c->stop_level;
+        s_void = c->overflow != 0 || (stop != 0 && (unsigned)p.s > stop);
+    }
+    __syncthreads();
+    return s_void != 0;
+}
 
 // Common set-up of the three level kernels: tables, per-warp shared memory, arena bases.
 struct LevelCtx {
@@ -695,7 +709,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) count_level(const __grid_c
     extern __shared__ int s_dyn[];
     __shared__ TablesSm tsm;
     __shared__ unsigned long long s_fb[kLv];
-    if (overflow_seen(p.ctl)) return;
+    if (launch_void(p)) return;
     const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
     unsigned long long scanned = 0, rows2 = 0, scanned2 = 0;
     const unsigned nwarps = gridDim.x * kWarps;
@@ -725,7 +739,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
     __shared__ unsigned long long s_w[2][32];
     __shared__ unsigned long long s_run[2];
     Ctl *ctl = p.ctl;
-    if (ctl->overflow) return;
+    if (ctl->overflow || (ctl->stop_level != 0 && (unsigned)p.s > ctl->stop_level)) return;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, s = p.s, q = s - 1;
     unsigned long long fb_s = 0, ob_s = ctl->out_base;
     for (int j = 1; j < s; j++) { fb_s += ctl->F[j]; ob_s += ctl->N[j] * (unsigned long long)p.row_len_lv[j]; }
@@ -774,6 +788,7 @@ __global__ void __launch_bounds__(1024) scan_groups(const __grid_constant__ Leve
         if (!p.la_n && fb_s + room > p.fcap) ov |= 1u;                 // la_n: the paths are counted, never stored
         if (!p.count_only && ob_s + (base_n + s_run[1]) * (unsigned long long)p.row_len > p.ocap) ov |= 2u;
         if (ov) ctl->overflow = ov;
+        if (p.shortest_only && base_n + s_run[1] > 0 && !ctl->stop_level) ctl->stop_level = (unsigned)s;
     }
 }
 
@@ -783,7 +798,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_FILL) fill_level(const __gr
     extern __shared__ int s_dyn[];
     __shared__ TablesSm tsm;
     __shared__ unsigned long long s_fb[kLv];
-    if (overflow_seen(p.ctl)) return;
+    if (launch_void(p)) return;
     LevelCtx c = level_setup(p, tsm, s_fb, s_dyn, WIDE ? 1 : 0);
     c.fb_s += p.ctl->subF;                            // after the earlier sub-launches of this level
     c.ob_s += p.ctl->subN * (unsigned long long)p.row_len;
@@ -891,7 +906,7 @@ struct UnitLane {
 template <int Q, bool WIDE = false>
 __global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __grid_constant__ LevelParams p) {
     __shared__ unsigned long long s_fb[kLv];
-    if (overflow_seen(p.ctl)) return;
+    if (launch_void(p)) return;
     const UnitCtx c = unit_setup(p, s_fb);
     const int lane = threadIdx.x & 31;
     unsigned long long scanned = 0;
@@ -929,7 +944,7 @@ template <int Q, bool WIDE = false>
 __global__ void __launch_bounds__(kThreads, RCA_MINB_UNIT) fill_unit(const __grid_constant__ LevelParams p) {
     extern __shared__ int s_dyn[];                    // per warp: 32 finished rows
     __shared__ unsigned long long s_fb[kLv];
-    if (overflow_seen(p.ctl)) return;
+    if (launch_void(p)) return;
     UnitCtx c = unit_setup(p, s_fb);
     c.fb_s += p.ctl->subF;
     c.ob_s += p.ctl->subN * (unsigned long long)p.row_len;
@@ -1102,7 +1117,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
     Ctl *ctl = p.ctl;
     // an arena overflowed at an earlier level: entries past its end were never written, the host
     // will grow the arena and run the plan again (checked before any ticket is taken)
-    if (overflow_seen(ctl)) return;
+    if (launch_void(p)) return;
     const LevelCtx c = level_setup(p, tsm, s_fb, s_dyn);
     const int s = p.s, lane = c.w.lane;
     ulonglong2 *tstate = p.tstate + c.slot0;
@@ -1129,6 +1144,7 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB) fused_level(const __grid_c
         if (tile == c.ntiles - 1 && lane == 0) {      // the last tile knows the level totals
             ctl->F[s] = run_f + cf;
             ctl->N[s] = run_e + ce;
+            if (p.shortest_only && run_e + ce > 0) ctl->stop_level = (unsigned)s;
         }
         __syncwarp();
         tile_fill<ADJ2, MODE, QT>(p, c.T, c.w, tile, C, c.fb_s, c.ob_s, run_f, run_e);

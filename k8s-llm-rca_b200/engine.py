@@ -56,7 +56,7 @@ class PlanDesc(C.Structure):
                 ("has_inter", C.c_int32), ("prune", C.c_int32),
                 ("pos_kind", C.c_int32 * (MAX_HOPS + 1)),
                 ("kind_excl", C.c_uint8 * MAX_KINDS), ("kind_inter", C.c_uint8 * MAX_KINDS),
-                ("with_states", C.c_int32), ("count_only", C.c_int32)]
+                ("with_states", C.c_int32), ("count_only", C.c_int32), ("shortest_only", C.c_int32)]
 
 
 class StatsDesc(C.Structure):
@@ -132,7 +132,8 @@ def load_library(path: str | None = None):
 
 
 def varlen_plan(direction, max_hops, min_hops=1, dest_kind=-1, excl_kinds=(), inter_kinds=(), entity_only=False,
-                node_simple=True, pos_kind=None, prune=True, with_states=False, count_only=False) -> PlanDesc:
+                node_simple=True, pos_kind=None, prune=True, with_states=False, count_only=False,
+                shortest_only=False) -> PlanDesc:
     """Variable-length path plan - the reference's metapath statements,
     find_metapath/find_srckind_metapath_neo4j.py:95-129."""
     p = PlanDesc()
@@ -154,6 +155,7 @@ def varlen_plan(direction, max_hops, min_hops=1, dest_kind=-1, excl_kinds=(), in
         p.kind_inter[int(k)] = 1
     p.with_states = _states_mode(with_states)
     p.count_only = int(bool(count_only))
+    p.shortest_only = int(bool(shortest_only))
     return p
 
 
