@@ -1,5 +1,12 @@
-import sys, time, cProfile, pstats
-sys.path.insert(0, '/root/repo')
+"""Where the time of a batched incident replay goes (10 k incidents of the config-3 graph): three timed runs, then a
+cProfile of one.  python tools/latency_batch_profile.py"""
+import cProfile
+import os
+import pstats
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from k8s_llm_rca_b200 import executor, replay, workloads
 w = workloads.Config3()
