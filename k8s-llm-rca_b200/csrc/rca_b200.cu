@@ -34,6 +34,7 @@ struct PreparedPlan {
     int L = 0, mode = kModeChain;
     std::vector<std::vector<Sub>> subs;          // typed sub-launches per level (split path)
     std::vector<char> level_typed, level_dead;
+    std::vector<std::vector<char>> cont_kind;    // [level][kind]: a path may CONTINUE through a node of this kind at this level
     int wide_level = -1;                         // level whose frontier is stored as wide entries (rca_kernels.cuh), or -1
 };
 
@@ -683,6 +684,7 @@ static void prepare_plan_fresh(rca_engine *e, const rca_plan_t *pl, int64_t n_se
             if (!m.allowed(a)) continue;
             can[a] = !(act[0 * RCA_MAX_KINDS + m.tail(a)] & kActDead);     // row 0 holds the seed rules
         }
+        pp.cont_kind.assign(L + 1, std::vector<char>(e->n_kinds, 0));
         for (int s = 1; s <= L; s++) {
             std::fill(nxt.begin(), nxt.end(), 0);
             for (int a = 0; a < A; a++) {
@@ -691,6 +693,7 @@ static void prepare_plan_fresh(rca_engine *e, const rca_plan_t *pl, int64_t n_se
                 if (k & kActDead) continue;
                 const bool emit = (k & kActEmit) != 0;
                 const bool cont = (k & kActCont) && arr[(size_t)s * kArrBytes + a];
+                if (cont) pp.cont_kind[s][m.head(a)] = 1;
                 if (emit || cont)
                     pp.subs[s].push_back(Sub{a >> 1, a & 1, (cont ? 1 : 0) | (emit ? 2 : 0), m.head(a) | ((k & kActInter) ? 1 << 16 : 0)});
                 if (cont)
@@ -906,6 +909,13 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                     p.unit_next = e->unit_next + (sdir == RCA_DIR_OUT ? e->unit_out_base : e->unit_in_base)[pp.subs[s][j].t];
                     p.unit_fl = pp.subs[s][j].fl;
                     p.unit_aux = pp.subs[s][j].aux;
+                    {   // can a node at positions 0 .. s-2 be of the step's far kind ?  Position 0 is the seed (its kind must
+                        // be declared), positions 1 .. s-2 are nodes paths continued through at those levels.
+                        const int far = pp.subs[s][j].aux & 0xffff;
+                        bool clear = pl->pos_kind[0] >= 0 && pl->pos_kind[0] != far && !pp.cont_kind.empty();
+                        for (int d = 1; d <= s - 2 && clear; d++) clear = !pp.cont_kind[d][far];
+                        if (clear) p.unit_fl |= 4;
+                    }
                     dyn_c = 0;
                     dyn_f = (size_t)kWarps * kTile * p.row_len * sizeof(int);
                 }

@@ -161,7 +161,8 @@ struct LevelParams {
                                       // types): the load needs the slot only, so it travels beside the adjacency load
     int arr_prune;                    // refine 'continue' by the arrival table (edge type, direction)
     // unit steps (count_unit / fill_unit): the far kind of the typed step is fixed, so its tests are per launch
-    int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row
+    int unit_fl;                      // bit0: a surviving candidate continues, bit1: it is a row, bit2: no node of the path
+                                      // before its tail can be of the far kind (the count pass skips the parent walk)
     int unit_aux;                     // kind | intermediate-kind flag << 16 of the far kind
     const int2 *unit_next;            // per node of the near kind: its one (neighbour, relationship), or (-1, -1)
     // wide frontier (see "Wide entries" below): this level's fill writes / this level's kernels read entries that
@@ -309,10 +310,10 @@ __device__ __forceinline__ void head_finish(const States &st, const ulonglong2 h
     const int further = (int)(h.y >> 56);
     if (!further) return;
     if (!st.more) { state_probe_full(st.off, st.rec, v, ts, 1, first, cnt); return; }
-    const ulonglong2 *m = reinterpret_cast<const ulonglong2 *>(st.more + v);
-    const ulonglong2 x = __ldg(m), y = __ldg(m + 1);          // one sector, both halves requested at once
-    packed_interval(x.x, x.y, ts, first, cnt);
-    packed_interval(y.x, y.y, ts, first, cnt);
+    unsigned long long a1, b1, a2, b2;                        // one sector, ONE 256-bit request (one pass of the L1 data pipe)
+    asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(a1), "=l"(b1), "=l"(a2), "=l"(b2) : "l"(st.more + v));
+    packed_interval(a1, b1, ts, first, cnt);
+    packed_interval(a2, b2, ts, first, cnt);
     if (further > 2) state_probe_full(st.off, st.rec, v, ts, 3, first, cnt);
 }
 __device__ __forceinline__ void state_probe(const States &st, int v, long long ts, int &first, int &cnt) {
@@ -884,6 +885,17 @@ struct UnitLane {
         for (int d = 0; d <= Q; d++) dead |= (a[d] == v);
         fl = dead ? 0 : ((p.unit_fl & 1) | (((p.unit_fl & 2) && (!p.need_inter || inter)) ? 2 : 0));
     }
+    // the count pass when the host has shown that no node before the tail can be of the step's far kind (unit_fl bit 2):
+    // the candidate can only collide with the tail itself, so the parent walk and the seed load are not needed
+    __device__ __forceinline__ void load_tail_only(const LevelParams &p, const int4 e, bool valid) {
+        a[Q] = e.x; inter = e.w >> 16;
+        int2 nx = make_int2(-1, -1);
+        if (valid && e.x >= p.row_lo && e.x < p.row_hi) nx = __ldg(p.unit_next + (e.x - p.row_lo));
+        has = nx.x >= 0;
+        v = nx.x; r = nx.y;
+        const bool dead = !has || v == e.x;
+        fl = dead ? 0 : ((p.unit_fl & 1) | (((p.unit_fl & 2) && (!p.need_inter || inter)) ? 2 : 0));
+    }
     // the same from a wide entry (Q = 1 or 2): plane A holds the nodes, B (needed by the count pass only under the
     // intermediate-kind rule) the rest
     __device__ __forceinline__ void load_wide(const LevelParams &p, const int4 A, const int4 B, bool valid) {
@@ -925,6 +937,8 @@ __global__ void __launch_bounds__(kThreads, RCA_MINB_UNITC) count_unit(const __g
             int4 B = none;
             if (p.need_inter && i < c.Fq) B = fq[wstride + i];
             u.load_wide(p, e, B, i < c.Fq);
+        } else if (p.unit_fl & 4) {
+            u.load_tail_only(p, e, i < c.Fq);
         } else {
             u.load(p, s_fb, e, i < c.Fq);
         }

@@ -63,6 +63,15 @@ def test_every_kind_pair_same_bytes_as_general_kernels(eng, snap_small, csr_orac
                         ref, _ = orc.varlen(seeds, direction, hops, **kw)
                         assert rows_to_set(rows_on) == rows_to_set(ref), tag
                         checked += 1
+                    if hops in (3, 4):
+                        # the seed kind declared: the count pass of a unit level may then skip the walk up the path
+                        # (it has been shown that nothing before the tail can be of the step's far kind)
+                        declared = engine.varlen_plan(direction, hops, pos_kind=[snap_small.kind_index(src)], **kw)
+                        (d_on, d_rows_on), (d_off, d_rows_off) = _both(eng, declared, seeds)
+                        assert d_on.emitted == d_off.emitted == on.emitted and d_on.frontier == d_off.frontier, tag
+                        for s in d_rows_on:
+                            assert np.array_equal(d_rows_on[s], d_rows_off[s]), tag + (s, "declared seed kind")
+                            assert np.array_equal(np.sort(d_rows_on[s], axis=0), np.sort(rows_on[s], axis=0)), tag + (s,)
     assert checked >= 10
 
 
