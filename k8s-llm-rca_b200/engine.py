@@ -387,6 +387,16 @@ class Engine:
         """Several plans in one submission (rca_expand_many): one synchronisation for the whole set.
         seeds_list[k] / ts_list[k]: numpy arrays, or CUDA tensors for all plans.  -> [ExpandResult]."""
         n = len(plans)
+        # a submission that comes again with the very same plan and buffer objects (a benchmark loop, a service replaying
+        # a prepared batch) reuses its marshalled descriptor: building it is a third of the host side of a small step
+        ck = (tuple(map(id, plans)), tuple(map(id, seeds_list)), tuple(map(id, ts_list)) if ts_list is not None else None)
+        hit = self._many_cache.get(ck) if hasattr(self, "_many_cache") else None
+        if hit is not None and all(p == q for p, q in zip(hit["ptrs"], self._live_ptrs(seeds_list, ts_list))):
+            st = (StatsDesc * n)()
+            self._gen += 1
+            arr = (PlanDesc * n)(*plans)             # the plans themselves are copied afresh: they may have been edited in place
+            self._ck(self.lib.rca_expand_many(self.h, arr, n, hit["sp"], hit["ns"], hit["tp"], hit["dev"], st))
+            return self._many_results(plans, st, [p.max_hops if p.kind == PLAN_VARLEN else p.n_steps for p in plans])
         arr = (PlanDesc * n)(*plans)
         keep, sp, tp, ns, devs = [], (C.c_void_p * n)(), (C.c_void_p * n)(), (C.c_int64 * n)(), set()
         seen = {}                       # plans of one submission usually share their seed / timestamp buffers
@@ -412,11 +422,31 @@ class Engine:
             raise ValueError("all seed / timestamp buffers must be host arrays or all device tensors")
         st = (StatsDesc * n)()
         self._gen += 1
-        self._ck(self.lib.rca_expand_many(self.h, arr, n, sp, ns, tp, devs.pop() if devs else 0, st))
+        dev = devs.pop() if devs else 0
+        self._ck(self.lib.rca_expand_many(self.h, arr, n, sp, ns, tp, dev, st))
+        levels = [p.max_hops if p.kind == PLAN_VARLEN else p.n_steps for p in plans]
+        if all(hasattr(x, "data_ptr") for x in seeds_list):          # tensors only: their identity and address can be re-checked cheaply
+            if not hasattr(self, "_many_cache"):
+                self._many_cache = {}
+            if len(self._many_cache) >= 4:
+                self._many_cache.pop(next(iter(self._many_cache)))
+            self._many_cache[ck] = {"sp": sp, "tp": tp, "ns": ns, "dev": dev, "levels": levels,
+                                    "keep": (keep, list(plans), list(seeds_list), list(ts_list) if ts_list is not None else None),
+                                    "ptrs": self._live_ptrs(seeds_list, ts_list)}
+        return self._many_results(plans, st, levels)
+
+    @staticmethod
+    def _live_ptrs(seeds_list, ts_list):
+        """(address, length) of every buffer as it is NOW - what a cached descriptor is re-validated against."""
+        out = [(x.data_ptr(), x.numel()) if hasattr(x, "data_ptr") else None for x in seeds_list]
+        if ts_list is not None:
+            out += [(x.data_ptr(), x.numel()) if hasattr(x, "data_ptr") else None for x in ts_list]
+        return out
+
+    def _many_results(self, plans, st, levels):
         out = []
-        for k in range(n):
-            levels = plans[k].max_hops if plans[k].kind == PLAN_VARLEN else plans[k].n_steps
-            r = ExpandResult(self, st[k], levels)
+        for k in range(len(plans)):
+            r = ExpandResult(self, st[k], levels[k])
             r.count_only = bool(plans[k].count_only)
             r.index = k
             out.append(r)
