@@ -66,7 +66,27 @@ def main():
     none = parallel.ShardedExpander(snap, lambda p, s, t: orc.varlen(s, "out", 2, dest_kind=K("image"), excl_kinds=[ev, ns], entity_only=True)[0], "cpu")
     o2 = none.run(2, None, snap.nodes_of_kind(node))
     assert o2["total"] == 0 and not o2["any_rows"] and o2["shortest"] == -1
+    # a graph built once per box and shared through a directory (workloads.shared_snapshot: what bench.py's strong-scaling
+    # leg does with /dev/shm): rank 0 generates and saves, the others load after the barrier - every rank holds the same arrays
+    import tempfile
+    from k8s_llm_rca_b200 import workloads
+    box = [tempfile.mkdtemp(prefix="rca_shared_") if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    shared = workloads.shared_snapshot(1500, 150, 3, rank=rank, barrier=dist.barrier, cache_dir=box[0])
+    local = synth.generate(1500, 150, synth.config_seed(3))
+    for name in ("kind_start", "out_rng", "out_dst", "in_adj", "und_adj", "st_off", "st_tmin", "st_tmax", "st_node", "rel_et"):
+        assert np.array_equal(getattr(shared, name), getattr(local, name)), name
+    assert [k.label for k in shared.kinds] == [k.label for k in local.kinds]
+    w4 = workloads.Config4(snap=shared, n_seeds=200)
+    mine, _, (lo, hi) = parallel.shard_seeds(shared, w4.seeds, rank, world, "und", True)
+    spans = [None] * world
+    dist.all_gather_object(spans, (lo, hi))
+    assert spans[0][0] == 0 and spans[-1][1] == len(w4.seeds) and all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+    assert np.all(np.diff(w4.seeds) > 0)                       # sorted seed list: rank order is seed order
     dist.barrier()
+    if rank == 0:
+        import shutil
+        shutil.rmtree(box[0], ignore_errors=True)
     dist.destroy_process_group()
     print(f"rank {rank} ok")
 
