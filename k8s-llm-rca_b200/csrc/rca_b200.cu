@@ -603,13 +603,31 @@ static level_kernel_t pick_wide_fill(int q) {
 
 static int max_grid(rca_engine *e, level_kernel_t kernel, size_t dyn_smem) {
     for (const auto &c : e->occ_cache) if (c.kernel == (const void *)kernel && c.dyn == dyn_smem) return c.grid;
-    // levels 6 to 8 need more than the 48 KB of shared memory (static tables included) a kernel gets without asking
+    // levels 6 to 8 need more than the 48 KB of shared memory (static tables included) a kernel gets without asking.
+    // The opt-in belongs to the kernel, not to this engine or this (kernel, size) pair: one kernel serves several levels
+    // with different sizes, and a later, SMALLER request must not lower what an earlier level was granted (it did: a plan
+    // that used the kernel at level 6, then one that first used it at level 5, then level 6 again - found by the
+    // randomised parity test).  The largest size ever asked for is kept per device and kernel.
     if (dyn_smem + 8192u > 48u * 1024u) {
-        const cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem);
-        if (rc != cudaSuccess) std::fprintf(stderr, "rca_b200: cudaFuncSetAttribute(%zu) failed: %s\n", dyn_smem, cudaGetErrorString(rc));
+        static std::mutex mu;
+        static std::vector<std::pair<std::pair<int, const void *>, size_t>> granted;
+        std::lock_guard<std::mutex> lock(mu);
+        size_t *have = nullptr;
+        for (auto &g : granted) if (g.first.first == e->device && g.first.second == (const void *)kernel) have = &g.second;
+        if (!have) { granted.push_back({{e->device, (const void *)kernel}, 0}); have = &granted.back().second; }
+        if (dyn_smem > *have) {
+            const cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem);
+            if (rc != cudaSuccess) std::fprintf(stderr, "rca_b200: cudaFuncSetAttribute(%zu) failed: %s\n", dyn_smem, cudaGetErrorString(rc));
+            else *have = dyn_smem;
+        }
     }
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    const cudaError_t oc = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem);
+    if (oc != cudaSuccess || per_sm < 1) {
+        if (std::getenv("RCA_B200_DEBUG")) std::fprintf(stderr, "rca_b200: occupancy query (%zu B) -> %s, %d per SM\n", dyn_smem, cudaGetErrorString(oc), per_sm);
+        cudaGetLastError();
+        per_sm = 1;
+    }
     e->occ_cache.push_back({(const void *)kernel, dyn_smem, e->sm_count * per_sm});    // asked once per (kernel, shared memory)
     return e->sm_count * per_sm;
 }
@@ -934,7 +952,12 @@ static int launch_levels(rca_engine *e, const PreparedPlan &pp, const RunBufs &b
                 *launches += 3;
             }
         }
-        CK(cudaGetLastError());
+        {
+            const cudaError_t le = cudaGetLastError();
+            if (le != cudaSuccess)
+                return fail(e, RCA_ERR_CUDA, "launch of level %d of %d failed: %s (%s, %d dynamic shared bytes per CTA)", s, L,
+                            cudaGetErrorString(le), pp.fused ? "fused" : "count/scan/fill", (int)dyn);
+        }
         if (ev_lv) CK(record_timing(e, ev_lv[s], e->stream));
     }
     return RCA_OK;

@@ -68,6 +68,9 @@ def test_random_graphs_and_plans_against_the_oracle(csr_oracle_lib):
         eng = engine.Engine(snap)
         for fam in (0, 1 << 40):
             eng.set_fused_threshold(fam)
+            unit_on, wide_on = bool(rng.random() < 0.8), bool(rng.random() < 0.5)
+            eng.set_unit_steps(unit_on)                         # the result-neutral switches, in every combination
+            eng.set_wide_entries(wide_on)
             for _ in range(6):
                 direction = ["out", "in", "und"][int(rng.integers(0, 3))]
                 hops = int(rng.integers(1, 7))
@@ -87,7 +90,12 @@ def test_random_graphs_and_plans_against_the_oracle(csr_oracle_lib):
                 ts = (T0 + rng.integers(-2, 30, size=len(seeds)) * H).astype(np.int64)
                 want, _, _ = orc.varlen_step(ok, ts[(seeds >= 0) & (seeds < snap.n_nodes)], direction, hops, **kw)
                 for mode in (False, True):
-                    res = eng.expand(engine.varlen_plan(direction, hops, with_states=mode, prune=bool(rng.random() < 0.7), **kw), seeds, ts)
+                    prune = bool(rng.random() < 0.7)
+                    try:
+                        res = eng.expand(engine.varlen_plan(direction, hops, with_states=mode, prune=prune, **kw), seeds, ts)
+                    except engine.RcaError as ex:
+                        raise AssertionError(f"{ex}: graph {g}, {direction} {hops} hops, {kw}, states {mode}, prune {prune}, "
+                                             f"fused {fam != 0}, unit {unit_on}, wide {wide_on}, {len(seeds)} seeds") from None
                     got = res.all_rows()
                     assert sorted(got) == sorted(want), (g, direction, hops, kw)
                     for s in want:
@@ -150,6 +158,8 @@ def test_random_typed_chains_against_the_oracle(csr_oracle_lib):
                 rows_seen += len(want)
         # all chains of one source kind in one submission
         eng.set_chain_walk_fanout(64)
+        eng.set_graphs(bool(rng.random() < 0.5))
+        eng.set_unit_steps(bool(rng.random() < 0.8))
         by_kind = {}
         for c in chains:
             by_kind.setdefault(c[0], []).append(c)
