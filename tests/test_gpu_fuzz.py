@@ -1,6 +1,6 @@
 """Randomised parity: small random multigraphs - parallel relationships, self-loops, kinds with no nodes, edge types
 that are functional on one side and not on the other, HasState intervals of every count - and random plans
-(direction, 1..6 hops, destination or none, excluded and intermediate kinds, node-simple or relationship-unique
+(direction, 1..8 hops, destination or none, excluded and intermediate kinds, node-simple or relationship-unique
 patterns, a declared seed kind, state columns, shortest-only, count-only) through every kernel family, against the C
 oracle.  The generated cluster graphs of the other tests share one schema; these graphs have none."""
 import numpy as np
@@ -60,7 +60,7 @@ def test_random_graphs_and_plans_against_the_oracle(csr_oracle_lib):
     from k8s_llm_rca_b200 import engine
     rng = np.random.default_rng(20240)
     compared = rows_seen = 0
-    for g in range(150):
+    for g in range(200):
         snap, counts = random_graph(rng)
         if snap.n_rels == 0:
             continue
@@ -73,7 +73,7 @@ def test_random_graphs_and_plans_against_the_oracle(csr_oracle_lib):
             eng.set_wide_entries(wide_on)
             for _ in range(6):
                 direction = ["out", "in", "und"][int(rng.integers(0, 3))]
-                hops = int(rng.integers(1, 7))
+                hops = int(rng.integers(1, 9))
                 src = int(rng.choice([k for k in range(4) if counts[k]]))
                 dest = int(rng.integers(-1, 4))
                 node_simple = bool(rng.random() < 0.8)
@@ -83,6 +83,8 @@ def test_random_graphs_and_plans_against_the_oracle(csr_oracle_lib):
                     kw["inter_kinds"] = [int(x) for x in rng.choice(4, size=int(rng.integers(1, 3)), replace=False)]
                 if rng.random() < 0.5:
                     kw["pos_kind"] = [src] + [-1] * hops
+                    if rng.random() < 0.3:                      # a kind required somewhere inside the path as well
+                        kw["pos_kind"][int(rng.integers(1, hops + 1))] = int(rng.integers(0, 4))
                 seeds = snap.nodes_of_kind(src).astype(np.int32)
                 if rng.random() < 0.3:
                     seeds = np.concatenate([seeds, seeds[:1], [-1, snap.n_nodes + 3]]).astype(np.int32)     # repeated and invalid seeds
@@ -109,7 +111,7 @@ def test_random_graphs_and_plans_against_the_oracle(csr_oracle_lib):
                     assert short.emitted[m] == len(want[m])
                 compared += 1
         eng.close()
-    assert compared > 1200 and rows_seen > 12000
+    assert compared > 1600 and rows_seen > 16000
 
 
 def test_random_typed_chains_against_the_oracle(csr_oracle_lib):
