@@ -176,3 +176,107 @@ def test_random_typed_chains_against_the_oracle(csr_oracle_lib):
                 assert np.array_equal(sort_rows(got), sort_rows(want)), (g, ets, dirs, "batched")
         eng.close()
     assert compared > 1000 and rows_seen > 3000
+
+
+def test_random_submissions_state_queries_and_the_static_entry(csr_oracle_lib):
+    """The other entry points on the same random graphs: several plans of every sort in ONE submission (rca_expand_many:
+    main-stream plans one after the other from the bottom of the output arena, one-launch chains at fixed places at its
+    top) against the same plans run one by one; the stand-alone state queries against the oracle; the entry point that
+    allocates nothing against rca_expand."""
+    import torch
+    from k8s_llm_rca_b200 import engine
+    rng = np.random.default_rng(4242)
+    subs = probes = statics = 0
+    for g in range(80):
+        snap, counts = random_graph(rng)
+        if snap.n_rels == 0:
+            continue
+        orc = csr_oracle_lib.CsrOracle(snap)
+        eng = engine.Engine(snap)
+        eng.set_graphs(bool(rng.random() < 0.5))
+        kinds = [k for k in range(4) if counts[k]]
+        # ---- a random submission
+        plans, seeds_l, ts_l = [], [], []
+        for _ in range(int(rng.integers(2, 12))):
+            k0 = int(rng.choice(kinds))
+            seeds = snap.nodes_of_kind(k0).astype(np.int32)
+            ts = (T0 + rng.integers(-2, 30, size=len(seeds)) * H).astype(np.int64)
+            states = [False, True, "mask"][int(rng.integers(0, 3))]
+            if rng.random() < 0.5:
+                cur, ets, dirs = k0, [], []
+                for _step in range(int(rng.integers(1, 5))):
+                    opts = [(t, "out", e.dst_kind) for t, e in enumerate(snap.etypes) if e.src_kind == cur] + \
+                           [(t, "in", e.src_kind) for t, e in enumerate(snap.etypes) if e.dst_kind == cur]
+                    if not opts:
+                        break
+                    t, d, cur = opts[int(rng.integers(0, len(opts)))]
+                    ets.append(t); dirs.append(d)
+                if not ets:
+                    continue
+                plans.append(engine.chain_plan(ets, dirs, with_states=states, count_only=bool(rng.random() < 0.2)))
+            else:
+                plans.append(engine.varlen_plan(["out", "in", "und"][int(rng.integers(0, 3))], int(rng.integers(1, 5)),
+                                                dest_kind=int(rng.integers(-1, 4)), excl_kinds=[4, 5], entity_only=True,
+                                                with_states=states, count_only=bool(rng.random() < 0.2),
+                                                shortest_only=bool(rng.random() < 0.2)))
+            seeds_l.append(seeds); ts_l.append(ts)
+        if len(plans) >= 2:
+            eng.set_fused_threshold(0 if rng.random() < 0.5 else 1 << 40)
+            for rep in range(3):                               # repeated: the second and third run may be graph replays
+                many = eng.expand_many(plans, seeds_l, ts_l)
+                got = [(list(r.emitted), None if r.count_only else {s: r.rows(s).copy() for s in range(1, r.levels + 1)}) for r in many]
+                for (emitted, rows), plan, sd, t in zip(got, plans, seeds_l, ts_l):
+                    one = eng.expand(plan, sd, t)
+                    assert list(one.emitted) == emitted, (g, rep)
+                    if rows is not None:
+                        for s in rows:
+                            assert np.array_equal(rows[s], one.rows(s)), (g, rep, s)     # same rows in the same order
+            subs += 1
+        # ---- stand-alone state queries: strict and loose, with and without the label of the state node
+        ent = np.concatenate([snap.nodes_of_kind(k) for k in kinds]).astype(np.int32)
+        q = ent[rng.integers(0, len(ent), size=64)]
+        lo = (T0 + rng.integers(-3, 32, size=64) * H).astype(np.int64)
+        hi = lo + rng.integers(0, 4, size=64) * H
+        f, c, ids = eng.state_lookup(q, lo)
+        wf, wc, wids = orc.states(q, lo)
+        assert np.array_equal(f, wf) and np.array_equal(c, wc) and np.array_equal(ids, wids)
+        f, c, ids = eng.state_lookup(q, hi, ts_hi=lo)                                    # loose: tmin <= hi and tmax > lo
+        wf, wc, wids = orc.states(q, hi, ts_hi=lo)
+        assert np.array_equal(f, wf) and np.array_equal(c, wc) and np.array_equal(ids, wids)
+        sk = int(rng.integers(6, 10))
+        f, c, ids = eng.state_lookup(q, lo, state_kind=sk)
+        klo, khi = snap.kind_range(sk)
+        _, _, allids = orc.states(q, lo, limit=64)
+        for i in range(64):
+            keep = [v for v in allids[i].tolist() if klo <= v < khi]
+            assert c[i] == len(keep) and ids[i].tolist()[:len(keep[:10])] == keep[:10] and f[i] == (keep[0] if keep else -1)
+        probes += 1
+        # ---- the entry point that allocates nothing
+        k0 = int(rng.choice(kinds))
+        seeds = snap.nodes_of_kind(k0).astype(np.int32)
+        ts = (T0 + rng.integers(0, 25, size=len(seeds)) * H).astype(np.int64)
+        hops = int(rng.integers(1, 6))
+        states = [False, True, "mask"][int(rng.integers(0, 3))]
+        plan = engine.varlen_plan(["out", "und"][int(rng.integers(0, 2))], hops, dest_kind=int(rng.integers(-1, 4)), excl_kinds=[4, 5],
+                                  entity_only=bool(rng.random() < 0.7), with_states=states)
+        eng.set_fused_threshold(1 << 40)
+        eng.set_stream(torch.cuda.current_stream().cuda_stream)
+        d_rows = torch.full((2_000_000,), -9, dtype=torch.int32, device="cuda")
+        try:
+            st = eng.expand_static(plan, torch.from_numpy(seeds).cuda(), torch.from_numpy(ts).cuda() if states else None, d_rows)
+        except engine.RcaError as ex:                          # more partial paths than the fixed scratch holds: refused, never wrong
+            assert "RCA_STATIC_MAX_FRONTIER" in str(ex) or "row buffer" in str(ex)
+        else:
+            ref = eng.expand(plan, seeds, ts if states else None)
+            host, off = d_rows.cpu().numpy(), 0
+            for s in range(1, hops + 1):
+                n, wd = int(st.emitted[s]), int(st.row_len[s])
+                assert n == ref.emitted[s]
+                if n:
+                    assert np.array_equal(host[off:off + n * wd].reshape(n, wd), ref.rows(s))
+                off += n * wd
+            assert (host[off:off + 32] == -9).all()
+            statics += 1
+        eng.set_stream(0)
+        eng.close()
+    assert subs > 50 and probes > 50 and statics > 40
