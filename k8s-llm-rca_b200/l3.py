@@ -72,9 +72,12 @@ def _purge():
 
 
 def run_driver(tree: str, snapshot, recorded: dict, script: str = "test_all.py", main_kwargs=None, executor_factory=None,
-               name: str = "l3"):
+               name: str = "l3", workdir: str | None = None, pauses: bool = False):
     """Import `script` from `tree` and run its main() against `snapshot` with recorded assistant answers.
     recorded: {assistant name: {key: answer or [answers...]}} (dropin/common/openai_generic_assistant.py).
+    workdir: directory to run in (test_with_file.py reads ./data/... and appends to ./output/...: with_file_workdir
+    prepares one).  pauses=False turns the script's own time.sleep calls (test_with_file.py:208 waits ten seconds
+    between messages) into no-ops for the run.
     Returns (stdout text, main()'s return value)."""
     executor.register_snapshot(name, snapshot)
     executor.register_uri_alias(META_URI, f"snapshot://{name}#metagraph")
@@ -103,9 +106,19 @@ def run_driver(tree: str, snapshot, recorded: dict, script: str = "test_all.py",
         mod = importlib.util.module_from_spec(spec)
         sys.modules[spec.name] = mod
         sink = io.StringIO()
-        with contextlib.redirect_stdout(sink):
-            spec.loader.exec_module(mod)
-            ret = mod.main(**(main_kwargs or {}))
+        import time as _time
+        real_sleep, here = _time.sleep, os.getcwd()
+        try:
+            if not pauses:
+                _time.sleep = lambda *_a, **_k: None
+            if workdir:
+                os.chdir(workdir)
+            with contextlib.redirect_stdout(sink):
+                spec.loader.exec_module(mod)
+                ret = mod.main(**(main_kwargs or {}))
+        finally:
+            _time.sleep = real_sleep
+            os.chdir(here)
         return sink.getvalue(), ret
     finally:
         sys.path.remove(tree)
@@ -113,6 +126,20 @@ def run_driver(tree: str, snapshot, recorded: dict, script: str = "test_all.py",
         executor.unregister_uri_alias(META_URI)
         executor.unregister_uri_alias(STATE_URI)
         _purge()
+
+
+def with_file_workdir(root: str, messages, input_name: str = "mixed-example-10-3.csv"):
+    """The directory layout reference test_with_file.py expects (:42-43): ./data/<csv with a header row and one message
+    per row> and ./output/.  Returns the path of the result file the script appends to."""
+    import csv
+    os.makedirs(os.path.join(root, "data"), exist_ok=True)
+    os.makedirs(os.path.join(root, "output"), exist_ok=True)
+    with open(os.path.join(root, "data", input_name), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["message"])
+        for m in messages:
+            w.writerow([m])
+    return os.path.join(root, "output", "mixed-example-10-3c-result.json")
 
 
 # Progress lines both drivers print, in the order they appear: the shape of a transcript

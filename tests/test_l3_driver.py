@@ -46,6 +46,27 @@ def test_reference_driver_runs_unmodified_to_completion(trace):
     assert "The code started at" in text                              # the reference's own closing lines were reached
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference tree is only in the build container")
+def test_reference_file_driver_runs_unmodified_and_writes_its_result(trace, tmp_path):
+    """The reference's second driver, test_with_file.py:20-225: messages from ./data/*.csv (it runs the second row), one
+    JSON result per message appended to ./output/*.json with attempt counts, queries, reports and token usage."""
+    from k8s_llm_rca_b200 import l3
+    from oracle_backend import oracle_executor_factory
+    snap, _ = l3.incident_snapshot(trace["message"])
+    out_file = l3.with_file_workdir(str(tmp_path), ["a message no event of this graph carries", trace["message"], "a third row"])
+    text, _ = l3.run_driver("/root/reference", snap, trace["recorded"], script="test_with_file.py",
+                            executor_factory=oracle_executor_factory, workdir=str(tmp_path))
+    shape = [s for s in l3.transcript_shape(text)]
+    assert shape == trace["shape"]                            # the same ladders as test_all.py on the same incident
+    result = json.loads(open(out_file).read())
+    assert result["error_message"] == trace["message"] and result["locator_attempts"] == 2
+    (analysis,) = result["analysis"]
+    assert analysis["cypher_attempts"] == 3 and "human_cypher_query" in analysis and "MATCH (evt:EVENT)" in analysis["human_cypher_query"]
+    assert len(analysis["statepath"]) == 1 and json.loads(analysis["statepath"][0]["report"])["conclusion"] == "recorded"
+    assert set(analysis["statepath"][0]["clue"]) == {s.split(" ", 1)[1].replace(" ", "(") + ")" for s in trace["shape"] if s.startswith("entity")}
+    assert set(result["token_usage"]) == {"prompt_tokens", "completion_tokens", "total_tokens"} and result["time_cost"] >= 0
+
+
 def test_mirror_driver_over_oracle_backend_matches_the_reference_transcript(trace):
     from k8s_llm_rca_b200 import l3
     from oracle_backend import oracle_executor_factory
