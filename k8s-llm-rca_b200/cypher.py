@@ -46,6 +46,8 @@ _ESC = {"n": "\n", "t": "\t", "r": "\r", "\\": "\\", "'": "'", '"': '"', "b": "\
 
 
 def _unquote(s):
+    if "\\" not in s:                                 # nothing to unescape: the usual case (ids, timestamps, keys, messages)
+        return s[1:-1]
     out, i, body = [], 0, s[1:-1]
     while i < len(body):
         c = body[i]

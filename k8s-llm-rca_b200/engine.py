@@ -512,9 +512,8 @@ class Engine:
             if n.value <= cap:
                 break
             cap = int(n.value) + 16
-        pairs = np.unique(pairs[:n.value], axis=0) if n.value else np.zeros((0, 2), np.int32)
         by_u = {}
-        for u, node in pairs.tolist():
+        for u, node in sorted(set(map(tuple, pairs[:n.value].tolist()))):      # few pairs per call: plain Python beats np.unique
             by_u.setdefault(u, []).append(node)
         idx = [uniq[b] for b in enc]
         hits = {}

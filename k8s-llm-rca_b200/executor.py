@@ -134,6 +134,7 @@ class QueryRunner:
         self.backend = backend
         self._label = {k.label: i for i, k in enumerate(snap.kinds)}
         self._kconst = [snap.props.kind_const_props(k) for k in range(snap.n_kinds)]
+        self._varlen_cache = {}
 
     # -- public
     def run(self, query, parameters=None):
@@ -142,7 +143,22 @@ class QueryRunner:
         if isinstance(plan, cy.NodeScanPlan):
             return self._node_scan(plan, params)
         if isinstance(plan, cy.VarLenPlan):
-            return self._varlen(plan, params)
+            # A snapshot never changes, so the answer to a metapath statement is a function of its text and parameters:
+            # the ladder of find_metapath asks the same few (srcKind, destKind, intermediateKinds) questions for incident
+            # after incident.  The rows are kept (entities are immutable views of the snapshot); every call still gets
+            # its own list.
+            try:
+                key = (query, tuple(sorted((k, tuple(v) if isinstance(v, list) else v) for k, v in params.items())))
+                hit = self._varlen_cache.get(key)
+            except TypeError:
+                key, hit = None, None
+            if hit is None:
+                hit = self._varlen(plan, params)
+                if key is not None:
+                    if len(self._varlen_cache) >= 256:
+                        self._varlen_cache.pop(next(iter(self._varlen_cache)))
+                    self._varlen_cache[key] = hit
+            return list(hit)
         if isinstance(plan, cy.ChainPlan):
             return self._chain(plan, params)
         if isinstance(plan, cy.StatePlan):
