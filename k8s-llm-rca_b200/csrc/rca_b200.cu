@@ -113,8 +113,13 @@ struct rca_engine {
     long long *msg_off = nullptr;
     std::vector<int> msg_node;            // message index -> node id (host)
     long long n_msgs = 0;
-    void *io_buf = nullptr;               // staging for rca_state_lookup with host buffers
+    void *io_buf = nullptr;               // staging for the state and text queries with host buffers
     size_t io_cap = 0;
+    // rca_expand with few host seeds (the per-incident statements): plan table, control block, timestamps and seeds lie side by
+    // side in one device block with a pinned mirror, so that a call uploads ONCE
+    unsigned char *small_dev = nullptr, *small_host = nullptr;
+    void *io_host = nullptr;              // ... and its pinned mirror: a call's inputs go up in ONE copy and its outputs come down
+    size_t io_host_cap = 0;               // in ONE (every small copy is a DMA of its own, 5-8 us each, and they queue up)
     // rca_expand_many: per-plan tables and control blocks
     unsigned char *m_ptab = nullptr, *mh_ptab = nullptr;
     Ctl *m_ctl = nullptr, *mh_ctl = nullptr;
@@ -360,6 +365,9 @@ extern "C" int rca_close(rca_engine_t *e) {
                    e->st_off, e->st_rec, e->st_head, e->st_more, e->unit_next, e->rel_et, e->in_et, e->und_et, e->frontier, e->out, e->tstate, e->tcount, e->gsum, e->gscan, e->ctl, e->ptab,
                    e->seeds_buf, e->ts_buf, e->io_buf, e->msg_bytes, e->msg_off, e->m_ptab, e->m_ctl};
     for (void *p : dev) if (p) cudaFree(p);
+    if (e->io_host) cudaFreeHost(e->io_host);
+    if (e->small_host) cudaFreeHost(e->small_host);
+    if (e->small_dev) cudaFree(e->small_dev);
     if (e->h_ctl) cudaFreeHost(e->h_ctl);
     if (e->h_ptab) cudaFreeHost(e->h_ptab);
     if (e->mh_ptab) cudaFreeHost(e->mh_ptab);
@@ -1085,19 +1093,43 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     if (rc) return rc;
     e->results.assign(1, PlanResult());
     e->selected = 0;
+    // few host seeds: everything the kernels read from the host goes up in one copy (layout: table | control block |
+    // timestamps | seeds); otherwise table, control block and seed buffers travel separately as before
+    constexpr long long kSmallSeeds = 4096;
+    constexpr size_t kSmallCtl = ((size_t)kPtBytes + 255) & ~(size_t)255, kSmallTs = kSmallCtl + 512;
+    static_assert(sizeof(Ctl) <= 512, "control block does not fit its slot");
+    const bool small = !seeds_on_device && n_seeds <= kSmallSeeds;
+    if (small && !e->small_dev) {
+        CK(cudaMalloc((void **)&e->small_dev, kSmallTs + (size_t)kSmallSeeds * 12));
+        CK(cudaMallocHost((void **)&e->small_host, kSmallTs + (size_t)kSmallSeeds * 12));
+    }
     PreparedPlan pp;
-    prepare_plan(e, pl, n_seeds, e->h_ptab, pp);
+    prepare_plan(e, pl, n_seeds, small ? e->small_host : e->h_ptab, pp);
     const int L = pp.L;
 
     const int *d_seeds = seeds;
     const long long *d_ts = (const long long *)seed_ts;
-    if (!seeds_on_device && n_seeds) {
-        rc = stage_seeds(e, seeds, seed_ts, n_seeds, pl->with_states != 0, 0, n_seeds);
-        if (rc) return rc;
-        d_seeds = e->seeds_buf;
-        if (pl->with_states) d_ts = e->ts_buf;
+    Ctl *d_ctl = e->ctl;
+    const unsigned char *d_ptab = e->ptab;
+    size_t small_bytes = 0;
+    if (small) {
+        const size_t off_seeds = kSmallTs + (size_t)n_seeds * 8;
+        if (pl->with_states && n_seeds) std::memcpy(e->small_host + kSmallTs, seed_ts, (size_t)n_seeds * 8);
+        if (n_seeds) std::memcpy(e->small_host + off_seeds, seeds, (size_t)n_seeds * 4);
+        d_ts = pl->with_states ? (const long long *)(e->small_dev + kSmallTs) : nullptr;
+        d_seeds = (const int *)(e->small_dev + off_seeds);
+        d_ctl = (Ctl *)(e->small_dev + kSmallCtl);
+        d_ptab = e->small_dev;
+        small_bytes = off_seeds + (size_t)n_seeds * 4;
+    } else {
+        if (!seeds_on_device && n_seeds) {
+            rc = stage_seeds(e, seeds, seed_ts, n_seeds, pl->with_states != 0, 0, n_seeds);
+            if (rc) return rc;
+            d_seeds = e->seeds_buf;
+            if (pl->with_states) d_ts = e->ts_buf;
+        }
+        CK(cudaMemcpyAsync(e->ptab, e->h_ptab, kPtBytes, cudaMemcpyHostToDevice, e->stream));
     }
-    CK(cudaMemcpyAsync(e->ptab, e->h_ptab, kPtBytes, cudaMemcpyHostToDevice, e->stream));
 
     // scratch arenas: keep what earlier calls grew to, else a guess from the seed count
     if (!e->frontier) { rc = grow(e, &e->frontier, &e->fcap, std::max<unsigned long long>(8ull * n_seeds, 1ull << 20)); if (rc) return rc; }
@@ -1107,7 +1139,7 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
     float ms = 0.f;
     while (true) {
         RunBufs b;
-        b.seeds = d_seeds; b.ts = d_ts; b.n_seeds = n_seeds; b.ctl = e->ctl; b.ptab = e->ptab; b.epoch = 0;
+        b.seeds = d_seeds; b.ts = d_ts; b.n_seeds = n_seeds; b.ctl = d_ctl; b.ptab = d_ptab; b.epoch = 0;
         rc = ensure_tile_arrays(e, n_seeds, pp.fused, !pp.fused, &b.groups);
         if (rc) return rc;
         if (pp.fused) { rc = next_epoch(e, &b.epoch); if (rc) return rc; }
@@ -1115,13 +1147,18 @@ extern "C" int rca_expand(rca_engine_t *e, const rca_plan_t *pl, const int32_t *
         std::memset(e->h_ctl, 0, sizeof(Ctl));
         e->h_ctl->F[0] = (unsigned long long)n_seeds;
         CK(cudaEventRecord(e->ev0, e->stream));
-        CK(cudaMemcpyAsync(e->ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+        if (small && retries == 0) {                   // table, control block, timestamps and seeds: one copy
+            std::memcpy(e->small_host + kSmallCtl, e->h_ctl, sizeof(Ctl));
+            CK(cudaMemcpyAsync(e->small_dev, e->small_host, small_bytes, cudaMemcpyHostToDevice, e->stream));
+        } else {
+            CK(cudaMemcpyAsync(d_ctl, e->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, e->stream));
+        }
         if (!pp.fused) CK(cudaMemsetAsync(e->gsum, 0, b.groups * sizeof(ulonglong2), e->stream));
         CK(cudaEventRecord(e->ev_lv[0], e->stream));
         rc = launch_levels(e, pp, b, e->ev_lv, &launches);
         if (rc) return rc;
         CK(cudaEventRecord(e->ev1, e->stream));
-        CK(cudaMemcpyAsync(e->h_ctl, e->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaMemcpyAsync(e->h_ctl, d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
         CK(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
         const unsigned ov = e->h_ctl->overflow;
@@ -1534,6 +1571,25 @@ extern "C" int rca_result_wait(rca_engine_t *e) {
     return RCA_OK;
 }
 
+// device staging of at least `need` bytes and a pinned host mirror of the same size
+static int io_staging(rca_engine *e, size_t need) {
+    if (need > e->io_cap) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->io_buf) CK(cudaFree(e->io_buf));
+        e->io_buf = nullptr; e->io_cap = 0;
+        CK(cudaMalloc(&e->io_buf, need));
+        e->io_cap = need;
+    }
+    if (need > e->io_host_cap) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->io_host) CK(cudaFreeHost(e->io_host));
+        e->io_host = nullptr; e->io_host_cap = 0;
+        CK(cudaMallocHost(&e->io_host, need));
+        e->io_host_cap = need;
+    }
+    return RCA_OK;
+}
+
 static int state_query(rca_engine_t *e, const char *who, const int32_t *nodes, const int64_t *ta, const int64_t *tb, int64_t n,
                        int on_device, int32_t *out_first, int32_t *out_cnt, int32_t *out_ids, int st_lo = 0,
                        int st_hi = 0x7fffffff) {
@@ -1547,31 +1603,32 @@ static int state_query(rca_engine_t *e, const char *who, const int32_t *nodes, c
     if (!on_device) {
         // staging layout: ta[n] | tb[n] (8 B each) | nodes[n] | first[n] | cnt[n] | ids[n][LIMIT]
         const size_t need = (size_t)n * (16 + 4 + 4 + 4 + 4 * RCA_STATE_LIMIT);
-        if (need > e->io_cap) {
-            CK(cudaStreamSynchronize(e->stream));
-            if (e->io_buf) CK(cudaFree(e->io_buf));
-            e->io_buf = nullptr; e->io_cap = 0;
-            CK(cudaMalloc(&e->io_buf, need));
-            e->io_cap = need;
-        }
-        char *b = (char *)e->io_buf;
+        int rc = io_staging(e, need);
+        if (rc) return rc;
+        char *b = (char *)e->io_buf, *h = (char *)e->io_host;
         d_ta = (long long *)b;
         d_tb = (long long *)(b + 8 * (size_t)n);
         d_nodes = (int *)(b + 16 * (size_t)n);
         d_first = (int *)(b + 20 * (size_t)n);
         d_cnt = (int *)(b + 24 * (size_t)n);
         d_ids = out_ids ? (int *)(b + 28 * (size_t)n) : nullptr;
-        CK(cudaMemcpyAsync((void *)d_ta, ta, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
-        CK(cudaMemcpyAsync((void *)d_tb, tb, 8 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
-        CK(cudaMemcpyAsync((void *)d_nodes, nodes, 4 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+        std::memcpy(h, ta, 8 * (size_t)n);                     // the three inputs side by side: one copy up
+        std::memcpy(h + 8 * (size_t)n, tb, 8 * (size_t)n);
+        std::memcpy(h + 16 * (size_t)n, nodes, 4 * (size_t)n);
+        CK(cudaMemcpyAsync(b, h, 20 * (size_t)n, cudaMemcpyHostToDevice, e->stream));
     }
     state_lookup<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(e->st_off, e->st_rec, e->n_nodes, d_nodes, d_ta, d_tb, n,
                                                                     st_lo, st_hi, d_first, d_cnt, d_ids);
     CK(cudaGetLastError());
-    if (!on_device) {
-        CK(cudaMemcpyAsync(out_first, d_first, 4 * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
-        CK(cudaMemcpyAsync(out_cnt, d_cnt, 4 * (size_t)n, cudaMemcpyDeviceToHost, e->stream));
-        if (out_ids) CK(cudaMemcpyAsync(out_ids, d_ids, 4 * (size_t)n * RCA_STATE_LIMIT, cudaMemcpyDeviceToHost, e->stream));
+    if (!on_device) {                                         // the three outputs side by side: one copy down
+        char *b = (char *)e->io_buf, *h = (char *)e->io_host;
+        const size_t out_bytes = (size_t)n * (out_ids ? 8 + 4 * RCA_STATE_LIMIT : 8);
+        CK(cudaMemcpyAsync(h + 20 * (size_t)n, b + 20 * (size_t)n, out_bytes, cudaMemcpyDeviceToHost, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+        std::memcpy(out_first, h + 20 * (size_t)n, 4 * (size_t)n);
+        std::memcpy(out_cnt, h + 24 * (size_t)n, 4 * (size_t)n);
+        if (out_ids) std::memcpy(out_ids, h + 28 * (size_t)n, 4 * (size_t)n * RCA_STATE_LIMIT);
+        return RCA_OK;
     }
     CK(cudaStreamSynchronize(e->stream));
     return RCA_OK;
@@ -1861,24 +1918,23 @@ extern "C" int rca_text_contains(rca_engine_t *e, const uint8_t *pat_bytes, cons
     size_t o_pat = 0, o_poff = al(pbytes), o_lens = o_poff + al((n_pat + 1) * 8), o_pow = o_lens + al(lens.size() * 4 + 4),
            o_th = o_pow + al(lens.size() * 8 + 8), o_tp = o_th + al((size_t)tsize * 8), o_first = o_tp + al((size_t)tsize * 4),
            o_np = o_first + al((size_t)n_pat * 4), o_pairs = o_np + 256, need = o_pairs + al((size_t)pairs_cap * 8);
-    if (need > e->io_cap) {
-        CK(cudaStreamSynchronize(e->stream));
-        if (e->io_buf) CK(cudaFree(e->io_buf));
-        e->io_buf = nullptr; e->io_cap = 0;
-        CK(cudaMalloc(&e->io_buf, need));
-        e->io_cap = need;
+    {
+        int rc = io_staging(e, need);
+        if (rc) return rc;
     }
-    char *b = (char *)e->io_buf;
-    CK(cudaMemcpyAsync(b + o_pat, pat_bytes, pbytes, cudaMemcpyHostToDevice, e->stream));
-    CK(cudaMemcpyAsync(b + o_poff, pat_off, (n_pat + 1) * 8, cudaMemcpyHostToDevice, e->stream));
+    char *b = (char *)e->io_buf, *h = (char *)e->io_host;
+    // everything the kernel reads, laid out in the pinned mirror as it lies on the device: ONE copy up
+    std::memcpy(h + o_pat, pat_bytes, pbytes);
+    std::memcpy(h + o_poff, pat_off, (size_t)(n_pat + 1) * 8);
     if (!lens.empty()) {
-        CK(cudaMemcpyAsync(b + o_lens, lens.data(), lens.size() * 4, cudaMemcpyHostToDevice, e->stream));
-        CK(cudaMemcpyAsync(b + o_pow, pow_top.data(), lens.size() * 8, cudaMemcpyHostToDevice, e->stream));
+        std::memcpy(h + o_lens, lens.data(), lens.size() * 4);
+        std::memcpy(h + o_pow, pow_top.data(), lens.size() * 8);
     }
-    CK(cudaMemcpyAsync(b + o_th, tab_hash.data(), (size_t)tsize * 8, cudaMemcpyHostToDevice, e->stream));
-    CK(cudaMemcpyAsync(b + o_tp, tab_pat.data(), (size_t)tsize * 4, cudaMemcpyHostToDevice, e->stream));
-    CK(cudaMemcpyAsync(b + o_first, first.data(), (size_t)n_pat * 4, cudaMemcpyHostToDevice, e->stream));
-    CK(cudaMemsetAsync(b + o_np, 0, 8, e->stream));
+    std::memcpy(h + o_th, tab_hash.data(), (size_t)tsize * 8);
+    std::memcpy(h + o_tp, tab_pat.data(), (size_t)tsize * 4);
+    std::memcpy(h + o_first, first.data(), (size_t)n_pat * 4);
+    std::memset(h + o_np, 0, 8);
+    CK(cudaMemcpyAsync(b, h, o_np + 8, cudaMemcpyHostToDevice, e->stream));
     unsigned long long found = 0;
     if (!lens.empty() && e->n_msgs > 0) {
         TextParams tp;
@@ -1891,13 +1947,20 @@ extern "C" int rca_text_contains(rca_engine_t *e, const uint8_t *pat_bytes, cons
         const long long threads = e->n_msgs * (long long)lens.size();
         contains_scan<<<(unsigned)((threads + 255) / 256), 256, 0, e->stream>>>(tp);
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(first.data(), b + o_first, (size_t)n_pat * 4, cudaMemcpyDeviceToHost, e->stream));
-        CK(cudaMemcpyAsync(&found, b + o_np, 8, cudaMemcpyDeviceToHost, e->stream));
+        // the answers - first match per pattern, number of pairs - and the first few pairs come down in ONE copy; only a
+        // longer pair list needs a second one
+        const unsigned long long eager = std::min<unsigned long long>((unsigned long long)pairs_cap, 64);
+        CK(cudaMemcpyAsync(h + o_first, b + o_first, (o_pairs - o_first) + eager * 8, cudaMemcpyDeviceToHost, e->stream));
         CK(cudaStreamSynchronize(e->stream));
+        std::memcpy(first.data(), h + o_first, (size_t)n_pat * 4);
+        std::memcpy(&found, h + o_np, 8);
         const unsigned long long got = std::min<unsigned long long>(found, (unsigned long long)pairs_cap);
         if (got) {
-            CK(cudaMemcpyAsync(out_pairs, b + o_pairs, got * 8, cudaMemcpyDeviceToHost, e->stream));
-            CK(cudaStreamSynchronize(e->stream));
+            if (got > eager) {
+                CK(cudaMemcpyAsync(h + o_pairs, b + o_pairs, got * 8, cudaMemcpyDeviceToHost, e->stream));
+                CK(cudaStreamSynchronize(e->stream));
+            }
+            std::memcpy(out_pairs, h + o_pairs, got * 8);
             for (unsigned long long k = 0; k < got; k++) out_pairs[2 * k + 1] = e->msg_node[out_pairs[2 * k + 1]];   // message index -> node id
         }
     } else {
