@@ -9,6 +9,7 @@
     snapshot://<name>#metagraph  the schema graph derived from it (what the reference keeps in its
                                  second Neo4j database, test_all.py:21)
     synth://?objects=N&events=M&seed=S[#metagraph]   a generated graph (synth.generate)
+    dump:///abs/path[#metagraph] a node / relationship dump on disk (ingest.load_path: JSON lines, CSV file or CSV directory)
 
 `QueryRunner` is the host logic between Cypher text and the engine: it compiles the text
 (cypher.py), resolves labels / kinds / edge types against the snapshot, asks a backend for paths,
@@ -69,8 +70,18 @@ def resolve_snapshot(uri: str):
                                             int(q["events"][0]) if "events" in q else None,
                                             int(q.get("seed", ["20240001"])[0]))
         snap = _REGISTRY[key]
+    elif u.scheme == "dump":
+        path = (u.netloc + u.path) if u.netloc else u.path
+        key = ("dump", path)
+        if key not in _REGISTRY:
+            from . import ingest
+            try:
+                _REGISTRY[key] = ingest.load_path(path)
+            except (OSError, ValueError, KeyError) as exc:
+                raise ServiceUnavailable(f"cannot load the dump at {path!r}: {exc}") from exc
+        snap = _REGISTRY[key]
     else:
-        raise ServiceUnavailable(f"cannot resolve {uri!r}: expected snapshot://<name> or synth://?objects=..")
+        raise ServiceUnavailable(f"cannot resolve {uri!r}: expected snapshot://<name>, synth://?objects=.. or dump:///path")
     if u.fragment == "metagraph":
         key = ("meta", id(snap))
         if key not in _REGISTRY:
