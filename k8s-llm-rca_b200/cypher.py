@@ -12,6 +12,13 @@ the engine executes:
   State     MATCH (n:K)-[r:HasState]->(s:KK) WHERE n.id = .. AND      S5/S5' analyze_root_cause.py:51-79
             r.tmin <= .. AND r.tmax > ..
 
+A Chain statement may be written the way an assistant writes it rather than the way the generator does: one long
+pattern or comma-separated ones, hops without a direction (the labels / kinds decide which way each relationship is
+stored), unnamed nodes and relationships, `{prop: value}` maps, RETURN *, comments.  Its WHERE may hold any predicate:
+`r.key = ..` picks the step's edge types, predicates on the seed node written before its LIMIT choose the seeds, a
+kind test such as `pod.kind2 = 'Pod'` stands in for a label, and whatever is left (IN, STARTS WITH, =~, IS NULL,
+type(), labels(), toLower() ...) is evaluated on the finished rows, host side.
+
 Anything that does not parse, or parses but is not one of these shapes, raises CypherSyntaxError -
 the exception the reference's retry loop catches (test_all.py:109).
 """
@@ -35,13 +42,14 @@ _KEYWORDS = {"MATCH", "WHERE", "WITH", "RETURN", "LIMIT", "DISTINCT", "AND", "OR
              "CONTAINS", "AS", "STARTS", "ENDS", "TRUE", "FALSE", "OPTIONAL", "ORDER", "BY", "SKIP", "UNWIND",
              "CREATE", "MERGE", "DELETE", "SET", "CALL"}
 _TOKEN = re.compile(r"""
-    (?P<ws>\s+|//[^\n]*)
+    (?P<ws>\s+|//[^\n]*|/\*.*?\*/)
   | (?P<num>\d+\.\d+|\d+(?!\.\d))
   | (?P<str>'(?:[^'\\]|\\.)*'|"(?:[^"\\]|\\.)*")
   | (?P<param>\$[A-Za-z_][A-Za-z_0-9]*)
   | (?P<ident>[A-Za-z_][A-Za-z_0-9]*|`[^`]+`)
-  | (?P<op><>|<=|>=|->|<-|\.\.|[()\[\]{},.:;=<>\-*|+])
-""", re.X)
+  | (?P<op><>|<=|>=|=~|->|<-|\.\.|[()\[\]{},.:;=<>\-*|+])
+""", re.X | re.S)
+_AGGREGATES = {"count", "collect", "sum", "avg", "min", "max"}
 _ESC = {"n": "\n", "t": "\t", "r": "\r", "\\": "\\", "'": "'", '"': '"', "b": "\b", "f": "\f"}
 
 
@@ -219,6 +227,8 @@ class Parser:
         return clauses
 
     def ret_item(self):
+        if self.accept("op", "*"):                   # RETURN *: every named variable in scope (resolved per row)
+            return (("star",), None, "*")
         start = self.peek()[2]
         e = self.expr()
         end = self.peek()[2]
@@ -324,6 +334,9 @@ class Parser:
         if t[0] == "op" and t[1] in ("=", "<>", "<", "<=", ">", ">="):
             self.i += 1
             return ("cmp", t[1], a, self.unary())
+        if t[0] == "op" and t[1] == "=~":
+            self.i += 1
+            return ("cmp", "regex", a, self.unary())
         if self.accept("kw", "IN"):
             return ("cmp", "in", a, self.unary())
         if self.accept("kw", "CONTAINS"):
@@ -398,6 +411,8 @@ class Parser:
                     self.expect("op", ")")
                     return ("quant", name, var, lst, pred)
                 args = []
+                if name in _AGGREGATES:
+                    raise _unsupported(f"aggregation ({t[1]}(...)): this executor returns the matched rows themselves")
                 if not self.at("op", ")"):
                     args.append(self.expr())
                     while self.accept("op", ","):
@@ -515,17 +530,62 @@ def eval_expr(e, env, params):
                 return a.startswith(b)
             if op == "endswith":
                 return a.endswith(b)
+            if op == "regex":                        # =~ matches the WHOLE string
+                return re.fullmatch(b, a, re.S) is not None
             return {"<": a < b, "<=": a <= b, ">": a > b, ">=": a >= b}[op]
-        except TypeError:
+        except (TypeError, AttributeError, re.error):
             return None
     if k == "call":
         name, args = e[1], [eval_expr(x, env, params) for x in e[2]]
-        if name == "size":
-            return None if args[0] is None else len(args[0])
-        if name in ("tolower", "toupper"):
-            return None if args[0] is None else (args[0].lower() if name == "tolower" else args[0].upper())
-        raise CypherSyntaxError(f"Unknown function '{name}'")
+        fn = _FUNCTIONS.get(name)
+        if fn is None:
+            raise CypherSyntaxError(f"Unknown function '{name}'")
+        if len(args) not in fn[0]:
+            raise CypherSyntaxError(f"Insufficient parameters for function '{name}'" if len(args) < min(fn[0])
+                                    else f"Too many parameters for function '{name}'")
+        if name == "coalesce":
+            return next((a for a in args if a is not None), None)
+        if name == "exists":
+            return args[0] is not None
+        if args and args[0] is None:
+            return None
+        try:
+            return fn[1](*args)
+        except (TypeError, ValueError, AttributeError, IndexError):
+            return None
     raise CypherSyntaxError(f"Expression of kind {k!r} is not supported here")
+
+
+def _to_int(v):
+    return int(float(v)) if isinstance(v, str) else int(v)
+
+
+def _to_bool(v):
+    if isinstance(v, str):
+        return {"true": True, "false": False}.get(v.strip().lower())
+    return bool(v)
+
+
+# scalar functions an LLM-written statement is likely to wrap a property in: name -> (arities, implementation);
+# a null first argument gives null (handled by the caller), an argument of the wrong type gives null as well
+_FUNCTIONS = {
+    "size": ((1,), len), "length": ((1,), len),
+    "tolower": ((1,), lambda v: v.lower()), "toupper": ((1,), lambda v: v.upper()),
+    "trim": ((1,), lambda v: v.strip()), "ltrim": ((1,), lambda v: v.lstrip()), "rtrim": ((1,), lambda v: v.rstrip()),
+    "tostring": ((1,), lambda v: ("true" if v else "false") if isinstance(v, bool) else str(v)),
+    "tointeger": ((1,), _to_int), "tofloat": ((1,), float), "toboolean": ((1,), _to_bool),
+    "replace": ((3,), lambda v, a, b: v.replace(a, b)), "split": ((2,), lambda v, d: v.split(d)),
+    "substring": ((2, 3), lambda v, a, n=None: v[a:] if n is None else v[a:a + n]),
+    "left": ((2,), lambda v, n: v[:n]), "right": ((2,), lambda v, n: v[len(v) - n:] if n else ""),
+    "head": ((1,), lambda v: v[0] if v else None), "last": ((1,), lambda v: v[-1] if v else None),
+    "abs": ((1,), abs), "coalesce": (tuple(range(1, 33)), None),
+    "exists": ((1,), lambda v: True),                # exists(n.p): the null case is answered below
+    "type": ((1,), lambda r: r.type), "id": ((1,), lambda x: x.id), "elementid": ((1,), lambda x: x.element_id),
+    "labels": ((1,), lambda n: sorted(n.labels)), "keys": ((1,), lambda x: sorted(x.keys())),
+    "properties": ((1,), lambda x: dict(x.items())),
+    "startnode": ((1,), lambda r: r.start_node), "endnode": ((1,), lambda r: r.end_node),
+    "nodes": ((1,), lambda p: list(p.nodes)), "relationships": ((1,), lambda p: list(p.relationships)),
+}
 
 
 def conjuncts(e):
@@ -569,8 +629,9 @@ class ChainStep:
     rel_var: str | None
     rel_types: list
     key: object                    # literal value of r.key, or None
-    start_var: str
+    start_var: str                 # as stored: start -> end (undirected: as written, either way round may match)
     end_var: str
+    undirected: bool = False
 
 
 @dataclass
@@ -584,6 +645,8 @@ class ChainPlan:
     ret: Clause
     unique: list = field(default_factory=list)   # groups of step indices written in ONE MATCH clause: Cypher binds
                                                  # no relationship twice within a clause (across clauses it may)
+    residual: list = field(default_factory=list) # predicates evaluated on the finished rows (host side)
+    hints: dict = field(default_factory=dict)    # variable -> [(property, value)]: equality tests that may name its kind
 
 
 @dataclass
@@ -804,12 +867,14 @@ def _compile_state(p, where, ret, params):
 
 
 def _compile_chain(clauses, params):
-    labels, hops, preds, seed_limit, limited_vars = {}, [], [], None, None
+    labels, hops, preds, seed_limit, limited_vars, limit_at = {}, [], [], None, None, None
     first_vars = None
+    anon = [0]
 
-    def note(n):
-        if n.var is None:
-            raise _unsupported("anonymous nodes in typed patterns")
+    def note(n, ci):
+        if n.var is None:                            # '()' or '(:Pod)': a hidden variable (RETURN * does not list it)
+            n.var = f" anon{anon[0]}"
+            anon[0] += 1
         if len(n.labels) > 1:
             raise _unsupported("multi-label node patterns")
         if n.labels:
@@ -818,41 +883,42 @@ def _compile_chain(clauses, params):
             labels[n.var] = n.labels[0]
         labels.setdefault(n.var, None)
         for k, v in n.props.items():
-            preds.append(("cmp", "=", ("prop", ("var", n.var), k), v))
+            preds.append((ci, ("cmp", "=", ("prop", ("var", n.var), k), v)))
 
     clause_of = []                                   # per hop: index of the MATCH clause it was written in
     for ci, c in enumerate(clauses[:-1]):
         if c.kind == "MATCH":
-          for p in c.patterns:                       # 'MATCH p1, p2' = both patterns in one clause
-            if p.path_var:
-                raise _unsupported("path variables over typed patterns")
-            for n in p.nodes:
-                note(n)
-            if first_vars is None:
-                first_vars = [n.var for n in p.nodes]
-            for i, r in enumerate(p.rels):
-                if r.varlen:
-                    raise _unsupported("variable-length hops inside typed patterns")
-                if r.direction == "und":
-                    raise _unsupported("undirected typed hops")
-                if not r.types:
-                    raise _unsupported("untyped hops mixed with typed ones")
-                a, b = p.nodes[i].var, p.nodes[i + 1].var
-                start, end = (a, b) if r.direction == "out" else (b, a)
-                key = r.props.get("key")
-                hops.append(ChainStep(r.var, list(r.types), key, start, end))
-                clause_of.append(ci)
-                for k, v in r.props.items():
-                    if k != "key":
-                        raise _unsupported("relationship property maps other than {key: ...}")
-          preds.extend(conjuncts(c.where))
+            for p in c.patterns:                     # 'MATCH p1, p2' = both patterns in one clause
+                if p.path_var:
+                    raise _unsupported("path variables over typed patterns")
+                for n in p.nodes:
+                    note(n, ci)
+                if first_vars is None:
+                    first_vars = [n.var for n in p.nodes]
+                for i, r in enumerate(p.rels):
+                    if r.varlen:
+                        raise _unsupported("variable-length hops inside typed patterns")
+                    if not r.types:
+                        raise _unsupported("untyped hops mixed with typed ones")
+                    a, b = p.nodes[i].var, p.nodes[i + 1].var
+                    start, end = (b, a) if r.direction == "in" else (a, b)
+                    hops.append(ChainStep(r.var, list(r.types), r.props.get("key"), start, end, r.direction == "und"))
+                    clause_of.append(ci)
+                    for k, v in r.props.items():
+                        if k != "key":
+                            if r.var is None:
+                                raise _unsupported("property maps other than {key: ...} on an unnamed relationship")
+                            preds.append((ci, ("cmp", "=", ("prop", ("var", r.var), k), v)))
+            preds.extend((ci, x) for x in conjuncts(c.where))
         elif c.kind == "WITH":
             if c.limit is not None:
                 if seed_limit is not None:
                     raise _unsupported("more than one WITH ... LIMIT")
-                seed_limit = c.limit
+                seed_limit, limit_at = c.limit, ci
                 limited_vars = [it[0][1] for it in c.items if it[0][0] == "var"]
             for it in c.items:
+                if it[0] == ("star",):
+                    continue
                 if it[0][0] != "var" or (it[1] and it[1] != it[0][1]):
                     raise _unsupported("WITH items other than plain variables")
     if not hops:
@@ -861,28 +927,41 @@ def _compile_chain(clauses, params):
     if any(v not in used for v in labels):
         raise _unsupported("patterns that are not connected to the others (cartesian products)")
 
+    # Predicates: `r.key = <literal>` selects the step's edge types; predicates over the seed alone written before
+    # its LIMIT choose the seeds; everything else is evaluated on the finished rows (`residual`).
     rel_vars = {h.rel_var: h for h in hops if h.rel_var}
-    seed_preds, seed_var = [], None
-    for c in preds:
-        if c[0] == "cmp" and c[1] == "=" and _is_prop_of(c[2]) and c[2][1][1] in rel_vars and c[2][2] == "key":
+    single, residual = [], []
+    for ci, c in preds:
+        if c[0] == "cmp" and c[1] == "=" and _is_prop_of(c[2]) and c[2][1][1] in rel_vars and c[2][2] == "key" \
+                and c[3][0] in ("lit", "param") and rel_vars[c[2][1][1]].key is None:
             rel_vars[c[2][1][1]].key = c[3]
             continue
         vars_ = _vars_of(c)
+        unknown = [v for v in vars_ if v not in labels and v not in rel_vars]
+        if unknown:
+            raise CypherSyntaxError(f"Variable `{unknown[0]}` not defined")
         if len(vars_) == 1 and next(iter(vars_)) in labels:
-            v = next(iter(vars_))
-            if seed_var not in (None, v):
-                raise _unsupported("property predicates on more than one node variable")
-            seed_var = v
-            seed_preds.append(c)
-            continue
-        raise _unsupported("this WHERE predicate in a typed pattern query")
-    if seed_var is None:
-        if limited_vars:
-            seed_var = limited_vars[0]
+            single.append((ci, next(iter(vars_)), c))
         else:
-            seed_var = first_vars[0]
-    if seed_limit is not None and limited_vars and seed_var not in limited_vars:
-        raise _unsupported("WITH ... LIMIT on a variable other than the filtered one")
+            residual.append(c)
+    if limited_vars:
+        seed_var = limited_vars[0]
+    else:
+        def selective(c):                            # the lookups the engine answers itself (message arena, id table)
+            return c[0] == "cmp" and _is_prop_of(c[2]) and ((c[1] == "contains" and c[2][2] == "message") or
+                                                            (c[1] == "=" and c[2][2] == "id"))
+        seed_var = next((v for _, v, c in single if selective(c)), None) or \
+            next((v for _, v, _ in single), None) or first_vars[0]
+    if seed_var not in labels:
+        raise CypherSyntaxError(f"Variable `{seed_var}` not defined")
+    seed_where, hints = None, {}
+    for ci, v, c in single:
+        if v == seed_var and (limit_at is None or ci < limit_at):
+            seed_where = c if seed_where is None else ("and", seed_where, c)
+            continue
+        residual.append(c)
+        if c[0] == "cmp" and c[1] == "=" and _is_prop_of(c[2], v) and c[3][0] in ("lit", "param"):
+            hints.setdefault(v, []).append((c[2][2], _lit(c[3], params)))   # `pod.kind2 = 'Pod'` names the kind
     for h in hops:
         if h.key is not None:
             h.key = _lit(h.key, params)
@@ -901,21 +980,18 @@ def _compile_chain(clauses, params):
         if h.start_var in bound and h.end_var in bound:
             raise _unsupported("patterns that close a cycle")
         if h.start_var == cur:
-            walk.append((h.start_var, h.end_var, "out"))
+            walk.append((h.start_var, h.end_var, "und" if h.undirected else "out"))
             cur = h.end_var
         else:
-            walk.append((h.end_var, h.start_var, "in"))
+            walk.append((h.end_var, h.start_var, "und" if h.undirected else "in"))
             cur = h.start_var
         bound.add(cur)
         steps.append(h)
-    seed_where = None
-    for c in seed_preds:
-        seed_where = c if seed_where is None else ("and", seed_where, c)
     groups = {}
     for i, h in enumerate(steps):
         groups.setdefault(clause_of[next(j for j, x in enumerate(hops) if x is h)], []).append(i)
     unique = [g for g in groups.values() if len(g) > 1]
-    return ChainPlan(seed_var, seed_where, seed_limit, labels, steps, walk, clauses[-1], unique)
+    return ChainPlan(seed_var, seed_where, seed_limit, labels, steps, walk, clauses[-1], unique, residual, hints)
 
 
 def _vars_of(e):

@@ -182,12 +182,18 @@ class QueryRunner:
 
     def _project(self, ret, envs, params):
         """RETURN items over a list of environments (var -> entity): DISTINCT, ORDER BY, SKIP and LIMIT applied."""
-        keys = [alias or src for (_, alias, src) in ret.items]
-        aliases = {alias: i for i, (_, alias, _) in enumerate(ret.items) if alias}
+        items, star = ret.items, any(e == ("star",) for (e, _, _) in ret.items)
+        keys = [alias or src for (_, alias, src) in items]
+        aliases = {alias: i for i, (_, alias, _) in enumerate(items) if alias}
         out, seen, sort_keys = [], set(), []
         stop_at = None if ret.order else (None if ret.limit is None else ret.skip + ret.limit)
         for env in envs:
-            vals = tuple(cy.eval_expr(e, env, params) for (e, _, _) in ret.items)
+            if star:                                 # RETURN *: the named variables of the row, in alphabetical order
+                names = sorted(v for v in env if not v.startswith(" "))
+                items = [(("var", v), None, v) for v in names] + [it for it in ret.items if it[0] != ("star",)]
+                keys = [alias or src for (_, alias, src) in items]
+                star = False
+            vals = tuple(cy.eval_expr(e, env, params) for (e, _, _) in items)
             if ret.distinct:
                 try:
                     if vals in seen:
@@ -330,35 +336,40 @@ class QueryRunner:
         for lab in plan.labels.values():
             if lab is not None and lab not in self._label:
                 return []
-        want = {v: (self._label[lab] if lab is not None else None) for v, lab in plan.labels.items()}
-        # candidate edge types per step, then every combination that forms one walk
-        cands = []
-        for st, (frm, to, d) in zip(plan.steps, plan.walk):
-            c = [t for t, e in enumerate(s.etypes)
-                 if e.rel_type in st.rel_types and (st.key is None or e.key == st.key)
-                 and want[st.start_var] in (None, e.src_kind) and want[st.end_var] in (None, e.dst_kind)]
-            cands.append(c)
+        # kinds a variable may be of: its label, else what an equality test on a per-kind constant property leaves
+        want = {v: ({self._label[lab]} if lab is not None else None) for v, lab in plan.labels.items()}
+        for v, tests in plan.hints.items():
+            for prop, value in tests:
+                if any(prop in kc for kc in self._kconst):
+                    ks = {k for k in range(s.n_kinds) if prop not in self._kconst[k] or self._kconst[k][prop] == value}
+                    want[v] = ks if want[v] is None else want[v] & ks
+        # candidate edge types per step, then every combination (and orientation) that forms one walk
+        cands = [[t for t, e in enumerate(s.etypes) if e.rel_type in st.rel_types and (st.key is None or e.key == st.key)]
+                 for st in plan.steps]
         combos = []
+
+        def allowed(v, kind):
+            return want[v] is None or kind in want[v]
 
         def rec(i, cur_kind, acc):
             if i == len(plan.steps):
                 combos.append(list(acc))
                 return
-            d = plan.walk[i][2]
+            frm, to, d0 = plan.walk[i]
             for t in cands[i]:
                 e = s.etypes[t]
-                near, far = (e.src_kind, e.dst_kind) if d == "out" else (e.dst_kind, e.src_kind)
-                if cur_kind is not None and near != cur_kind:
-                    continue
-                acc.append((t, near))
-                rec(i + 1, far, acc)
-                acc.pop()
-        rec(0, want[plan.seed_var], [])
+                for d in (("out", "in") if d0 == "und" else (d0,)):
+                    near, far = (e.src_kind, e.dst_kind) if d == "out" else (e.dst_kind, e.src_kind)
+                    if (cur_kind is not None and near != cur_kind) or not allowed(frm, near) or not allowed(to, far):
+                        continue
+                    acc.append((t, near, d))
+                    rec(i + 1, far, acc)
+                    acc.pop()
+        rec(0, None, [])
         col = {plan.seed_var: 0}
         for i, (_, to, _) in enumerate(plan.walk):
             col[to] = i + 1
         L = len(plan.steps)
-        dirs = [d for (_, _, d) in plan.walk]
         seeds_of = {k: self._seed_nodes(plan, k, params) for k in sorted({c[0][1] for c in combos})}
         if plan.seed_limit is not None and seeds_of:
             # WITH <seed> LIMIT n: which rows survive is unspecified in Cypher; the lowest node ids here
@@ -369,7 +380,10 @@ class QueryRunner:
             seeds = seeds_of[combo[0][1]]
             if len(seeds) == 0:
                 continue
-            rows = self.backend.chain(seeds, [t for t, _ in combo], dirs)
+            rows = self.backend.chain(seeds, [t for t, _, _ in combo], [d for _, _, d in combo])
+            for i, (t, _, d) in enumerate(combo):   # an undirected hop matches a self-loop once, not once per orientation
+                if plan.walk[i][2] == "und" and d == "in" and s.etypes[t].src_kind == s.etypes[t].dst_kind and len(rows):
+                    rows = rows[rows[:, i] != rows[:, i + 1]]
             if len(rows):
                 all_rows.append(rows)
         if not all_rows:
@@ -386,7 +400,8 @@ class QueryRunner:
                 for i, st in enumerate(plan.steps):
                     if st.rel_var:
                         env[st.rel_var] = Relationship(s, r[L + 1 + i])
-                yield env
+                if all(cy.eval_expr(c, env, params) is True for c in plan.residual):
+                    yield env
         return self._project(plan.ret, envs(), params)
 
     # -- S5 / S5'

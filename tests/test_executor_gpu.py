@@ -111,3 +111,34 @@ def test_query_battery_gpu_equals_oracle(executors, snap_1k):
     with pytest.raises(Exception) as ei:
         state.run_query("MATCH (n:Pod RETURN n")
     assert type(ei.value).__name__ == "CypherSyntaxError"
+
+
+def test_assistant_written_variants_of_the_instance_query_on_the_gpu(executors, snap_1k):
+    """The shapes of tests/test_cypher_variants.py (one pattern, no directions, unnamed parts, extra predicates,
+    RETURN *) through the GPU executor, row for row against the oracle-backed runner."""
+    _, state = executors
+    ostate = oracle_executor(snap_1k)
+
+    def same(a, b):
+        return sorted(map(repr, map(record_key, a))) == sorted(map(repr, map(record_key, b))) and \
+            [r.keys() for r in a[:1]] == [r.keys() for r in b[:1]]
+    tails = [
+        "MATCH (evt:EVENT)<-[r1:HasEvent]-(event:Event)-[r2:ReferInternal {key: 'involvedObject_uid'}]->(pod:Pod)"
+        "-[r3:ReferInternal]->(x) WHERE evt.message CONTAINS $m RETURN *",
+        "MATCH (evt:EVENT)-[r1:HasEvent]-(event:Event)-[r2:ReferInternal]-(pod:Pod)-[r3:ReferInternal]-(x:ConfigMap) "
+        "WHERE evt.message CONTAINS $m AND r2.key = 'involvedObject_uid' RETURN event, r1, evt, r2, pod, r3, x",
+        "MATCH (evt:EVENT)<-[:HasEvent]-(:Event)-[:ReferInternal {key: 'involvedObject_uid'}]->(pod:Pod)-[r3:ReferInternal]->(x) "
+        "WHERE evt.message CONTAINS $m AND x.isNative = 'true' AND NOT x.kind2 IN ['Namespace', 'Node'] RETURN pod, r3, x",
+        "/* claims and what binds them */ MATCH (evt:EVENT) WHERE evt.message CONTAINS $m WITH evt LIMIT 1 "
+        "MATCH (event:Event)-[r1:HasEvent]->(evt), (event)-[r2:ReferInternal]->(pod:Pod), (pod)-[r3:ReferInternal]->(c), (pv)-[r4:ReferInternal]->(c) "
+        "WHERE r2.key = 'involvedObject_uid' AND c.kind2 = 'PersistentVolumeClaim' AND type(r4) = 'ReferInternal' AND pv.kind2 = 'PersistentVolume' "
+        "RETURN pod, c, pv, r4",
+    ]
+    rows = 0
+    for i in range(0, len(snap_1k.props.msgs), 7):
+        par = {"m": snap_1k.props.msgs[i]}
+        for q in tails:
+            a, b = state.run_query(q, par), ostate.run_query(q, par)
+            assert same(a, b), q
+            rows += len(a)
+    assert rows > 50
