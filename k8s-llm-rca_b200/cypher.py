@@ -435,13 +435,23 @@ def parse(text):
 _STR_LIT = re.compile(r"""'(?:[^'\\]|\\.)*'|"(?:[^"\\]|\\.)*["]""")
 _RETURN_KW = re.compile(r"\bRETURN\b", re.I)
 _SKELETONS = {}
+# ... and compiled once per skeleton and per set of VALUES the compilation looked at (`_lit` notes every parameter it
+# resolves: relationship keys, kinds - the same from incident to incident; the message, which stays an expression of
+# the plan, is not among them).  A state statement's id and timestamps are resolved per call (StatePlan.late).
+_PLANS = {}
+_noted = None                                        # the (name, value) pairs `_lit` resolved during one compilation
 
 
-def parse_shared(text):
-    """-> (clauses, {parameter name: literal value}).  Falls back to a plain parse (and its error
-    messages, which quote the text) whenever lifting is not clearly safe."""
+def parse_shared(text, with_skeleton=False):
+    """-> (clauses, {parameter name: literal value}) [, skeleton text or None].  Falls back to a plain parse (and
+    its error messages, which quote the text) whenever lifting is not clearly safe."""
+    out = _parse_shared(text)
+    return out if with_skeleton else out[:2]
+
+
+def _parse_shared(text):
     if not isinstance(text, str) or "'" not in text and '"' not in text or "`" in text or "$__s" in text:
-        return parse(text), {}
+        return parse(text), {}, None
     lits = []
 
     def lift(m):
@@ -453,17 +463,18 @@ def parse_shared(text):
     for last_ret in _RETURN_KW.finditer(skel):
         pass
     if last_ret is not None and "$__s" in skel[last_ret.end():]:
-        return parse(text), {}                           # a literal in RETURN names its column: keep the text
+        return parse(text), {}, None                     # a literal in RETURN names its column: keep the text
     clauses = _SKELETONS.get(skel)
     if clauses is None:
         try:
             clauses = Parser(skel).parse()
         except CypherSyntaxError:
-            return parse(text), {}                       # report the error against the statement as written
+            return parse(text), {}, None                 # report the error against the statement as written
         if len(_SKELETONS) >= 512:
             _SKELETONS.clear()
+            _PLANS.clear()
         _SKELETONS[skel] = clauses
-    return clauses, {f"__s{i}": _unquote(v) for i, v in enumerate(lits)}
+    return clauses, {f"__s{i}": _unquote(v) for i, v in enumerate(lits)}, skel
 
 
 # ------------------------------------------------------------------------------------------ evaluation
@@ -659,6 +670,13 @@ class StatePlan:
     lo: str                        # r.tmin <= lo
     hi: str                        # r.tmax >  hi
     ret: Clause
+    late: tuple = ()               # the expressions entity_id, lo and hi came from (a plan kept per skeleton is bound
+                                   # to each statement's own values: bound())
+
+    def bound(self, params):
+        e, lo, hi = self.late
+        return StatePlan(self.entity_var, self.entity_label, self.state_var, self.state_label, _late(e, params),
+                         _late(lo, params), _late(hi, params), self.ret, self.late)
 
 
 def _lit(e, params):
@@ -668,10 +686,22 @@ def _lit(e, params):
     if e[0] == "param":
         if e[1] not in params:
             raise CypherSyntaxError(f"Expected parameter(s): {e[1]}", "Neo.ClientError.Statement.ParameterMissing")
+        if _noted is not None:
+            _noted.append((e[1], params[e[1]]))
         return params[e[1]]
     if e[0] == "list":
         return [_lit(x, params) for x in e[1]]
     raise CypherSyntaxError("Only literals and parameters are supported on the right-hand side of this predicate")
+
+
+def _late(e, params):
+    """_lit for a value that is bound per statement: it does not make the plan specific to the value."""
+    global _noted
+    keep, _noted = _noted, None
+    try:
+        return _lit(e, params)
+    finally:
+        _noted = keep
 
 
 def _is_prop_of(e, var=None):
@@ -687,13 +717,32 @@ def compile_query(text, parameters=None, bind=None):
     """Parse `text` and recognise its shape.  Returns one of the *Plan dataclasses.
     bind: a dict that receives the string literals lifted out of the text (see parse_shared); a caller that
     evaluates the plan's expressions later must pass the dict it evaluates with."""
+    global _noted
     params = dict(parameters or {})
     if bind is None:
-        clauses = parse(text)
-    else:
-        clauses, lifted = parse_shared(text)
-        params.update(lifted)
-        bind.update(lifted)
+        return _compile_clauses(parse(text), params)
+    clauses, lifted, skel = _parse_shared(text)
+    params.update(lifted)
+    bind.update(lifted)
+    if skel is None:
+        return _compile_clauses(clauses, params)
+    variants = _PLANS.setdefault(skel, [])
+    absent = _PLANS                                  # a value no parameter has
+    for looked_at, plan in variants:
+        if all(params.get(n, absent) == v for n, v in looked_at):
+            return plan.bound(params) if isinstance(plan, StatePlan) else plan
+    _noted = []
+    try:
+        plan = _compile_clauses(clauses, params)
+        looked_at = _noted
+    finally:
+        _noted = None
+    if len(variants) < 64:
+        variants.append((looked_at, plan))
+    return plan
+
+
+def _compile_clauses(clauses, params):
     matches = [c for c in clauses if c.kind == "MATCH"]
     ret = clauses[-1]
     if not matches:
@@ -854,16 +903,17 @@ def _compile_state(p, where, ret, params):
         if c[0] != "cmp":
             raise _unsupported("this predicate in a state query")
         if _is_prop_of(c[2], a.var) and c[2][2] == "id" and c[1] == "=":
-            ent_id = _lit(c[3], params)
+            ent_id = c[3]
         elif _is_prop_of(c[2], r.var) and c[2][2] == "tmin" and c[1] == "<=":
-            lo = _lit(c[3], params)
+            lo = c[3]
         elif _is_prop_of(c[2], r.var) and c[2][2] == "tmax" and c[1] == ">":
-            hi = _lit(c[3], params)
+            hi = c[3]
         else:
             raise _unsupported("this predicate in a state query")
     if ent_id is None or lo is None or hi is None:
         raise _unsupported("state queries without id, tmin <= and tmax > predicates")
-    return StatePlan(a.var, a.labels[0], b.var, b.labels[0] if b.labels else None, ent_id, lo, hi, ret)
+    return StatePlan(a.var, a.labels[0], b.var, b.labels[0] if b.labels else None, _late(ent_id, params),
+                     _late(lo, params), _late(hi, params), ret, (ent_id, lo, hi))
 
 
 def _compile_chain(clauses, params):

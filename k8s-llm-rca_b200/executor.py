@@ -146,29 +146,31 @@ class QueryRunner:
         self._label = {k.label: i for i, k in enumerate(snap.kinds)}
         self._kconst = [snap.props.kind_const_props(k) for k in range(snap.n_kinds)]
         self._varlen_cache = {}
+        self._chain_rt = {}
 
     # -- public
     def run(self, query, parameters=None):
         params = dict(parameters or {})
+        # A snapshot never changes, so the answer to a metapath statement is a function of its text and parameters:
+        # the ladder of find_metapath asks the same few (srcKind, destKind, intermediateKinds) questions for incident
+        # after incident.  The rows are kept (entities are immutable views of the snapshot); every call still gets
+        # its own list.
+        try:
+            key = (query, tuple(sorted((k, tuple(v) if isinstance(v, list) else v) for k, v in params.items())))
+            hit = self._varlen_cache.get(key)
+        except TypeError:
+            key, hit = None, None
+        if hit is not None:
+            return list(hit)
         plan = cy.compile_query(query, params, bind=params)
         if isinstance(plan, cy.NodeScanPlan):
             return self._node_scan(plan, params)
         if isinstance(plan, cy.VarLenPlan):
-            # A snapshot never changes, so the answer to a metapath statement is a function of its text and parameters:
-            # the ladder of find_metapath asks the same few (srcKind, destKind, intermediateKinds) questions for incident
-            # after incident.  The rows are kept (entities are immutable views of the snapshot); every call still gets
-            # its own list.
-            try:
-                key = (query, tuple(sorted((k, tuple(v) if isinstance(v, list) else v) for k, v in params.items())))
-                hit = self._varlen_cache.get(key)
-            except TypeError:
-                key, hit = None, None
-            if hit is None:
-                hit = self._varlen(plan, params)
-                if key is not None:
-                    if len(self._varlen_cache) >= 256:
-                        self._varlen_cache.pop(next(iter(self._varlen_cache)))
-                    self._varlen_cache[key] = hit
+            hit = self._varlen(plan, params)
+            if key is not None:
+                if len(self._varlen_cache) >= 256:
+                    self._varlen_cache.pop(next(iter(self._varlen_cache)))
+                self._varlen_cache[key] = hit
             return list(hit)
         if isinstance(plan, cy.ChainPlan):
             return self._chain(plan, params)
@@ -331,50 +333,69 @@ class QueryRunner:
         hit = [v for v in range(lo, hi) if cy.eval_expr(w, {plan.seed_var: Node(s, v)}, params) is True]
         return np.array(hit, dtype=np.int32)
 
+    def _chain_shape(self, plan):
+        """What of a chain plan depends on the snapshot alone: the kinds each variable may be of, every combination
+        (and orientation) of edge types that forms one walk, the row column of each variable.  None: no such walk.
+        Kept per plan object - the front end hands out one plan per statement skeleton (cypher._PLANS)."""
+        hit = self._chain_rt.get(id(plan))
+        if hit is not None and hit[0] is plan:
+            return hit[1]
+        s = self.snap
+        shape = None
+        if all(lab is None or lab in self._label for lab in plan.labels.values()):
+            # kinds a variable may be of: its label, else what an equality test on a per-kind constant property leaves
+            want = {v: ({self._label[lab]} if lab is not None else None) for v, lab in plan.labels.items()}
+            for v, tests in plan.hints.items():
+                for prop, value in tests:
+                    if any(prop in kc for kc in self._kconst):
+                        ks = {k for k in range(s.n_kinds) if prop not in self._kconst[k] or self._kconst[k][prop] == value}
+                        want[v] = ks if want[v] is None else want[v] & ks
+            cands = [[t for t, e in enumerate(s.etypes) if e.rel_type in st.rel_types and (st.key is None or e.key == st.key)]
+                     for st in plan.steps]
+            combos = []
+
+            def allowed(v, kind):
+                return want[v] is None or kind in want[v]
+
+            def rec(i, cur_kind, acc):
+                if i == len(plan.steps):
+                    combos.append(list(acc))
+                    return
+                frm, to, d0 = plan.walk[i]
+                for t in cands[i]:
+                    e = s.etypes[t]
+                    for d in (("out", "in") if d0 == "und" else (d0,)):
+                        near, far = (e.src_kind, e.dst_kind) if d == "out" else (e.dst_kind, e.src_kind)
+                        if (cur_kind is not None and near != cur_kind) or not allowed(frm, near) or not allowed(to, far):
+                            continue
+                        acc.append((t, near, d))
+                        rec(i + 1, far, acc)
+                        acc.pop()
+            rec(0, None, [])
+            col = {plan.seed_var: 0}
+            for i, (_, to, _) in enumerate(plan.walk):
+                col[to] = i + 1
+            shape = (combos, col)
+        if len(self._chain_rt) >= 256:
+            self._chain_rt.clear()
+        self._chain_rt[id(plan)] = (plan, shape)
+        return shape
+
     def _chain(self, plan, params):
         s = self.snap
-        for lab in plan.labels.values():
-            if lab is not None and lab not in self._label:
-                return []
-        # kinds a variable may be of: its label, else what an equality test on a per-kind constant property leaves
-        want = {v: ({self._label[lab]} if lab is not None else None) for v, lab in plan.labels.items()}
-        for v, tests in plan.hints.items():
-            for prop, value in tests:
-                if any(prop in kc for kc in self._kconst):
-                    ks = {k for k in range(s.n_kinds) if prop not in self._kconst[k] or self._kconst[k][prop] == value}
-                    want[v] = ks if want[v] is None else want[v] & ks
-        # candidate edge types per step, then every combination (and orientation) that forms one walk
-        cands = [[t for t, e in enumerate(s.etypes) if e.rel_type in st.rel_types and (st.key is None or e.key == st.key)]
-                 for st in plan.steps]
-        combos = []
-
-        def allowed(v, kind):
-            return want[v] is None or kind in want[v]
-
-        def rec(i, cur_kind, acc):
-            if i == len(plan.steps):
-                combos.append(list(acc))
-                return
-            frm, to, d0 = plan.walk[i]
-            for t in cands[i]:
-                e = s.etypes[t]
-                for d in (("out", "in") if d0 == "und" else (d0,)):
-                    near, far = (e.src_kind, e.dst_kind) if d == "out" else (e.dst_kind, e.src_kind)
-                    if (cur_kind is not None and near != cur_kind) or not allowed(frm, near) or not allowed(to, far):
-                        continue
-                    acc.append((t, near, d))
-                    rec(i + 1, far, acc)
-                    acc.pop()
-        rec(0, None, [])
-        col = {plan.seed_var: 0}
-        for i, (_, to, _) in enumerate(plan.walk):
-            col[to] = i + 1
+        shape = self._chain_shape(plan)
+        if shape is None:
+            return []
+        combos, col = shape
         L = len(plan.steps)
         seeds_of = {k: self._seed_nodes(plan, k, params) for k in sorted({c[0][1] for c in combos})}
         if plan.seed_limit is not None and seeds_of:
             # WITH <seed> LIMIT n: which rows survive is unspecified in Cypher; the lowest node ids here
-            keep = np.sort(np.concatenate(list(seeds_of.values())))[:plan.seed_limit]
-            seeds_of = {k: v[np.isin(v, keep)] for k, v in seeds_of.items()}
+            if len(seeds_of) == 1:
+                seeds_of = {k: np.sort(v)[:plan.seed_limit] for k, v in seeds_of.items()}
+            else:
+                keep = np.sort(np.concatenate(list(seeds_of.values())))[:plan.seed_limit]
+                seeds_of = {k: v[np.isin(v, keep)] for k, v in seeds_of.items()}
         all_rows = []
         for combo in combos:
             seeds = seeds_of[combo[0][1]]

@@ -188,3 +188,33 @@ def test_shared_parse_lifts_string_literals_and_falls_back_when_unsafe():
     with pytest.raises(cy.CypherSyntaxError) as ei:
         cy.compile_query("MATCH (n:Pod) WHERE n.id = 'abc' RETURN", None, bind={})
     assert "__s0" not in str(ei.value)
+
+
+def test_plans_are_kept_per_skeleton_and_per_value_the_compilation_looked_at():
+    """Statements that differ in the message alone share one compiled plan; a different relationship key is a
+    different plan; a state statement is bound to its own id and timestamps every time."""
+    def s4(msg, key):
+        return TEMPLATE_EXAMPLE.replace("spec_volumes_configMap_name", key).replace('configmap "es-gen-white-list-configmap" not found', msg)
+    b1, b2, b3 = {}, {}, {}
+    p1 = cy.compile_query(s4("first message", "spec_volumes_configMap_name"), {}, bind=b1)
+    p2 = cy.compile_query(s4("second message", "spec_volumes_configMap_name"), {}, bind=b2)
+    p3 = cy.compile_query(s4("second message", "spec_containers_envFrom_configMapRef_name"), {}, bind=b3)
+    assert p1 is p2 and p3 is not p1
+    assert [s.key for s in p3.steps][-1] == "spec_containers_envFrom_configMapRef_name"
+    assert [s.key for s in p1.steps][-1] == "spec_volumes_configMap_name"
+    # the message stays an expression of the shared plan, evaluated with each statement's own literals
+    assert cy.eval_expr(p1.seed_where[3], {}, b1) != cy.eval_expr(p2.seed_where[3], {}, b2)
+    assert "second message" in cy.eval_expr(p2.seed_where[3], {}, b2)
+    q = S5.replace("66637a34-b552-448f-9da6-976aa7462533", "{id}").replace("2020-12-11 06:35:02.011", "{ts}")
+    a = cy.compile_query(q.format(id="a" * 8, ts="2020-12-11 06:35:02.011"), {}, bind={})
+    b = cy.compile_query(q.format(id="b" * 8, ts="2021-01-01 00:00:00.000"), {}, bind={})
+    assert (a.entity_id, a.lo, a.hi) == ("a" * 8, "2020-12-11 06:35:02.011", "2020-12-11 06:35:02.011")
+    assert (b.entity_id, b.lo, b.hi) == ("b" * 8, "2021-01-01 00:00:00.000", "2021-01-01 00:00:00.000")
+    # parameters the caller passes count like literals: another kind, another plan
+    v1 = cy.compile_query(S3.format(arrow="-"), {"srcKind": "Pod", "destKind": "nfs", "intermediateKinds": []}, bind={})
+    v2 = cy.compile_query(S3.format(arrow="-"), {"srcKind": "Pod", "destKind": "Node", "intermediateKinds": []}, bind={})
+    v3 = cy.compile_query(S3.format(arrow="-"), {"srcKind": "Pod", "destKind": "Node", "intermediateKinds": ["PersistentVolume"]}, bind={})
+    assert (v1.dest_kind, v2.dest_kind, v3.inter_kinds) == ("nfs", "Node", ["PersistentVolume"]) and v2.inter_kinds == []
+    # a missing parameter is still reported, however often the skeleton was compiled before
+    with pytest.raises(cy.CypherSyntaxError):
+        cy.compile_query(S3.format(arrow="-"), {"srcKind": "Pod"}, bind={})
