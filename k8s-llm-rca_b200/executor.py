@@ -115,6 +115,15 @@ class GpuBackend:
         res = self.engine.expand(E.chain_plan(etypes, dirs), np.ascontiguousarray(seeds, dtype=np.int32))
         return res.rows(len(etypes))
 
+    def chain_many(self, jobs):
+        """[(seeds, etypes, dirs)] -> [rows]: the walks of one statement in one submission (rca_expand_many) - one
+        synchronisation however many combinations of edge types the statement's pattern allows."""
+        if len(jobs) == 1:
+            return [self.chain(*jobs[0])]
+        plans = [E.chain_plan(et, d) for _, et, d in jobs]
+        res = self.engine.expand_many(plans, [np.ascontiguousarray(sd, dtype=np.int32) for sd, _, _ in jobs])
+        return [r.rows(len(et)) for r, (_, et, _) in zip(res, jobs)]
+
     def states(self, nodes, tmin_le, tmax_gt, state_kind=None):
         return self.engine.state_lookup(nodes, tmin_le, ts_hi=tmax_gt, state_kind=state_kind)
 
@@ -397,11 +406,13 @@ class QueryRunner:
                 keep = np.sort(np.concatenate(list(seeds_of.values())))[:plan.seed_limit]
                 seeds_of = {k: v[np.isin(v, keep)] for k, v in seeds_of.items()}
         all_rows = []
-        for combo in combos:
-            seeds = seeds_of[combo[0][1]]
-            if len(seeds) == 0:
-                continue
-            rows = self.backend.chain(seeds, [t for t, _, _ in combo], [d for _, _, d in combo])
+        live = [combo for combo in combos if len(seeds_of[combo[0][1]])]
+        jobs = [(seeds_of[combo[0][1]], [t for t, _, _ in combo], [d for _, _, d in combo]) for combo in live]
+        if hasattr(self.backend, "chain_many"):
+            answers = self.backend.chain_many(jobs) if jobs else []
+        else:
+            answers = [self.backend.chain(*job) for job in jobs]
+        for combo, rows in zip(live, answers):
             for i, (t, _, d) in enumerate(combo):   # an undirected hop matches a self-loop once, not once per orientation
                 if plan.walk[i][2] == "und" and d == "in" and s.etypes[t].src_kind == s.etypes[t].dst_kind and len(rows):
                     rows = rows[rows[:, i] != rows[:, i + 1]]
