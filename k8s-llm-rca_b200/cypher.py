@@ -1000,8 +1000,15 @@ def _compile_chain(clauses, params):
         def selective(c):                            # the lookups the engine answers itself (message arena, id table)
             return c[0] == "cmp" and _is_prop_of(c[2]) and ((c[1] == "contains" and c[2][2] == "message") or
                                                             (c[1] == "=" and c[2][2] == "id"))
+        # ... else an END of the line of hops (the engine walks a line from one end), one with a predicate if any
+        degree = {}
+        for h in hops:
+            for v in (h.start_var, h.end_var):
+                degree[v] = degree.get(v, 0) + 1
+        ends = [v for v in labels if degree.get(v) == 1]
         seed_var = next((v for _, v, c in single if selective(c)), None) or \
-            next((v for _, v, _ in single), None) or first_vars[0]
+            next((v for _, v, _ in single if v in ends), None) or \
+            (first_vars[0] if first_vars[0] in ends or not ends else ends[0])
     if seed_var not in labels:
         raise CypherSyntaxError(f"Variable `{seed_var}` not defined")
     seed_where, hints = None, {}
