@@ -25,6 +25,7 @@ the exception the reference's retry loop catches (test_all.py:109).
 from __future__ import annotations
 
 import re
+import threading
 from dataclasses import dataclass, field
 
 
@@ -439,7 +440,7 @@ _SKELETONS = {}
 # resolves: relationship keys, kinds - the same from incident to incident; the message, which stays an expression of
 # the plan, is not among them).  A state statement's id and timestamps are resolved per call (StatePlan.late).
 _PLANS = {}
-_noted = None                                        # the (name, value) pairs `_lit` resolved during one compilation
+_tls = threading.local()                             # .noted: the (name, value) pairs `_lit` resolved during one compilation
 
 
 def parse_shared(text, with_skeleton=False):
@@ -686,8 +687,9 @@ def _lit(e, params):
     if e[0] == "param":
         if e[1] not in params:
             raise CypherSyntaxError(f"Expected parameter(s): {e[1]}", "Neo.ClientError.Statement.ParameterMissing")
-        if _noted is not None:
-            _noted.append((e[1], params[e[1]]))
+        noted = getattr(_tls, "noted", None)
+        if noted is not None:
+            noted.append((e[1], params[e[1]]))
         return params[e[1]]
     if e[0] == "list":
         return [_lit(x, params) for x in e[1]]
@@ -696,12 +698,11 @@ def _lit(e, params):
 
 def _late(e, params):
     """_lit for a value that is bound per statement: it does not make the plan specific to the value."""
-    global _noted
-    keep, _noted = _noted, None
+    keep, _tls.noted = getattr(_tls, "noted", None), None
     try:
         return _lit(e, params)
     finally:
-        _noted = keep
+        _tls.noted = keep
 
 
 def _is_prop_of(e, var=None):
@@ -717,7 +718,6 @@ def compile_query(text, parameters=None, bind=None):
     """Parse `text` and recognise its shape.  Returns one of the *Plan dataclasses.
     bind: a dict that receives the string literals lifted out of the text (see parse_shared); a caller that
     evaluates the plan's expressions later must pass the dict it evaluates with."""
-    global _noted
     params = dict(parameters or {})
     if bind is None:
         return _compile_clauses(parse(text), params)
@@ -729,14 +729,17 @@ def compile_query(text, parameters=None, bind=None):
     variants = _PLANS.setdefault(skel, [])
     absent = _PLANS                                  # a value no parameter has
     for looked_at, plan in variants:
-        if all(params.get(n, absent) == v for n, v in looked_at):
+        try:
+            same = all(params.get(n, absent) == v for n, v in looked_at)
+        except (TypeError, ValueError):              # a parameter value that does not compare to a plain truth value
+            same = False
+        if same:
             return plan.bound(params) if isinstance(plan, StatePlan) else plan
-    _noted = []
+    _tls.noted = looked_at = []
     try:
         plan = _compile_clauses(clauses, params)
-        looked_at = _noted
     finally:
-        _noted = None
+        _tls.noted = None
     if len(variants) < 64:
         variants.append((looked_at, plan))
     return plan
