@@ -460,6 +460,11 @@ def _parse_shared(text):
         return f"$__s{len(lits) - 1}"
 
     skel = _STR_LIT.sub(lift, text)
+    if "/*" in skel or "//" in skel:
+        # a comment: a quote inside it is not a literal, and the lifting above cannot tell.  (A comment's opener always
+        # survives in the skeleton - it stands before any quote of the comment - while `//` inside a real literal,
+        # a URL in a message, has been lifted out and does not get here.)
+        return parse(text), {}, None
     last_ret = None
     for last_ret in _RETURN_KW.finditer(skel):
         pass

@@ -218,3 +218,15 @@ def test_plans_are_kept_per_skeleton_and_per_value_the_compilation_looked_at():
     # a missing parameter is still reported, however often the skeleton was compiled before
     with pytest.raises(cy.CypherSyntaxError):
         cy.compile_query(S3.format(arrow="-"), {"srcKind": "Pod"}, bind={})
+
+
+def test_a_quote_inside_a_comment_is_not_a_string_literal():
+    q = "/* the pod's claim */ MATCH (n1:Pod) WHERE n1.id = 'abc' // it's here\nRETURN n1 LIMIT 1"
+    p = cy.compile_query(q, {}, bind={})
+    assert isinstance(p, cy.NodeScanPlan) and p.id_equals == "abc"
+
+
+def test_a_url_in_a_literal_still_shares_its_plan():
+    q = "MATCH (evt:EVENT) WHERE evt.message CONTAINS 'pull http://registry/{}' WITH evt LIMIT 1 MATCH (e:Event)-[r:HasEvent]->(evt) RETURN e"
+    a, b = cy.compile_query(q.format("a"), {}, bind={}), cy.compile_query(q.format("b"), {}, bind={})
+    assert a is b
