@@ -210,3 +210,41 @@ def test_what_is_not_supported_says_so(snap_small, text, fragment):
     with pytest.raises(cy.CypherSyntaxError) as ei:
         ex.run_query(text)
     assert fragment in str(ei.value)
+
+
+def test_the_reference_statements_against_the_same_brute_force_matcher(snap_small):
+    """S2, S3c and S3d as the reference writes them, three ways: text through the runner, the property-graph oracle
+    called directly, and the brute-force matcher above - which shares code with neither."""
+    from oracle.cypher_oracle import PGOracle
+    from test_cypher import S2, S3C, S3D
+    nodes, rels = snap_small.to_property_graph()
+    ex, pg = oracle_executor(snap_small), PGOracle(nodes, rels)
+    types = sorted({r["type"] for r in rels})
+    # S2: two clauses that share n1
+    for m in snap_small.props.msgs[::5]:
+        envs = brute(nodes, rels, [[("n1", "Event", "s1", ["HasEvent"], "out", "N1", "EVENT")],
+                                   [("n1", "Event", "r1", ["ReferInternal"], "out", "n2", None)]],
+                     lambda e: m in nodes[e["N1"]]["props"]["message"] and rels[e["r1"][1]]["props"]["key"] == "involvedObject_uid")
+        want = {nodes[e["n2"]]["props"].get("kind2") for e in envs}
+        assert len(want) <= 5                                            # LIMIT 5 cuts nothing here: sets compare
+        assert {r["n2.kind2"] for r in ex.run_query(S2, {"message": m})} == want == set(pg.src_kinds(m))
+    # S3c / S3d on the schema graph, where the reference runs them (its nodes carry `kind`)
+    meta = snap_small.derive_metagraph()
+    nodes, rels = meta.to_property_graph()
+    ex, pg = oracle_executor(meta), PGOracle(nodes, rels)
+    types = sorted({r["type"] for r in rels})
+    kind = lambda v: nodes[v]["props"].get("kind")
+    rows1 = rows2 = 0
+    for src, dst in (("Pod", "Node"), ("Pod", "Pod"), ("PersistentVolume", "PersistentVolumeClaim"), ("Pod", "Service"),
+                     ("ConfigMap", "Secret")):
+        par = {"srcKind": src, "destKind": dst}
+        one = brute(nodes, rels, [[("n1", None, "r1", types, "und", "n2", None)]],
+                    lambda e: kind(e["n1"]) == src and kind(e["n2"]) == dst)
+        want1 = sorted(((e["n1"], e["n2"]), (e["r1"][1],)) for e in one)
+        assert sorted(r["path"].key() for r in ex.run_query(S3C, par)) == want1 == pg.single_hop(src, dst)
+        two = brute(nodes, rels, [[("n1", None, "r1", types, "und", "n2", None), ("n2", None, "r2", types, "und", "n3", None)]],
+                    lambda e: kind(e["n1"]) == src and kind(e["n2"]) == "Namespace" and kind(e["n3"]) == dst)
+        want2 = sorted(((e["n1"], e["n2"], e["n3"]), (e["r1"][1], e["r2"][1])) for e in two)
+        assert sorted(r["path"].key() for r in ex.run_query(S3D, par)) == want2 == pg.via_kind(src, dst)
+        rows1, rows2 = rows1 + len(want1), rows2 + len(want2)
+    assert rows1 and rows2                                                 # each rung had rows in one of the cases at least
