@@ -326,21 +326,31 @@ class QueryRunner:
     def _seed_nodes(self, plan, kind, params):
         s = self.snap
         lo, hi = s.kind_range(kind)
-        w = plan.seed_where
-        if w is None:
+        if plan.seed_where is None:
             return np.arange(lo, hi, dtype=np.int32)
-        # fast path: <seed>.message CONTAINS <text> over the message arena
-        if w[0] == "cmp" and w[1] == "contains" and w[2] == ("prop", ("var", plan.seed_var), "message"):
-            text = cy.eval_expr(w[3], {}, params)
-            if text is None:
-                return np.zeros(0, np.int32)
-            hit = [v for v in self.backend.contains([text]).get(0, []) if lo <= v < hi]
-            return np.array(sorted(hit), dtype=np.int32)
-        if w[0] == "cmp" and w[1] == "=" and w[2] == ("prop", ("var", plan.seed_var), "id"):
-            val = cy.eval_expr(w[3], {}, params)
-            return np.array(sorted(s.props.find_by_id(kind, val)), dtype=np.int32)
-        hit = [v for v in range(lo, hi) if cy.eval_expr(w, {plan.seed_var: Node(s, v)}, params) is True]
-        return np.array(hit, dtype=np.int32)
+        # the conjunct the engine answers itself picks the candidates - <seed>.message CONTAINS <text> over the message
+        # arena, <seed>.id = <string> over the id table - and whatever else the statement asks of the seed is
+        # evaluated on those few, not on every node of the kind
+        parts = cy.conjuncts(plan.seed_where)
+        cand, rest = None, parts
+        for j, w in enumerate(parts):
+            if w[0] == "cmp" and w[1] == "contains" and w[2] == ("prop", ("var", plan.seed_var), "message") \
+                    and not cy._vars_of(w[3]):
+                text = cy.eval_expr(w[3], {}, params)
+                if text is None:
+                    return np.zeros(0, np.int32)
+                cand = sorted(v for v in self.backend.contains([text]).get(0, []) if lo <= v < hi)
+            elif w[0] == "cmp" and w[1] == "=" and w[2] == ("prop", ("var", plan.seed_var), "id") and not cy._vars_of(w[3]):
+                cand = sorted(s.props.find_by_id(kind, cy.eval_expr(w[3], {}, params)))
+            else:
+                continue
+            rest = parts[:j] + parts[j + 1:]
+            break
+        if cand is None:
+            cand = range(lo, hi)
+        if rest:
+            cand = [v for v in cand if all(cy.eval_expr(w, {plan.seed_var: Node(s, v)}, params) is True for w in rest)]
+        return np.array(list(cand), dtype=np.int32)
 
     def _chain_shape(self, plan):
         """What of a chain plan depends on the snapshot alone: the kinds each variable may be of, every combination

@@ -248,3 +248,22 @@ def test_the_reference_statements_against_the_same_brute_force_matcher(snap_smal
         assert sorted(r["path"].key() for r in ex.run_query(S3D, par)) == want2 == pg.via_kind(src, dst)
         rows1, rows2 = rows1 + len(want1), rows2 + len(want2)
     assert rows1 and rows2                                                 # each rung had rows in one of the cases at least
+
+
+def test_more_than_one_predicate_on_the_seed(world):
+    """`evt.message CONTAINS .. AND evt.timestamp >= ..`: the text lookup picks the candidates, the rest filters them."""
+    snap, nodes, rels, ex, m = world
+    evt = next(v for v in range(len(nodes)) if "EVENT" in nodes[v]["labels"] and m in nodes[v]["props"]["message"])
+    ts = nodes[evt]["props"]["timestamp"]
+    q = ("MATCH (evt:EVENT) WHERE evt.message CONTAINS $m AND evt.timestamp {op} $ts WITH evt LIMIT 1 "
+         "MATCH (event:Event)-[r1:HasEvent]->(evt) RETURN evt, event")
+    calls = []
+    inner = ex.runner.backend.contains
+    ex.runner.backend.contains = lambda texts: (calls.append(texts), inner(texts))[1]
+    try:
+        hit = ex.run_query(q.format(op=">="), {"m": m, "ts": ts})
+        miss = ex.run_query(q.format(op=">"), {"m": m, "ts": ts})
+    finally:
+        ex.runner.backend.contains = inner
+    assert [r["evt"].id for r in hit] == [evt] and miss == []
+    assert len(calls) == 2                                               # answered through the message arena both times
